@@ -1,0 +1,315 @@
+/*
+ * paddle_ray_b200.h -- C ABI of the B200-native data-parallel step tail.
+ *
+ * Every entry point replaces one operator / binding of the reference on the path
+ *   EagerReducer bucket sync -> check_finite_and_unscale -> squared_l2_norm clip -> adam(w)
+ * and keeps that operator's argument order and meaning.  Citations ("ref:") are relative
+ * to the reference tree (Rayman96/Paddle_ray).
+ *
+ * Conventions
+ *  - Tensors are passed as PRB_Tensor {data, numel, dtype, device}; lists as pointer+count;
+ *    optional tensors as NULL.  dtype codes are phi::DataType's
+ *    (ref: paddle/phi/common/data_type.h:37-70).  device = -1 means host memory,
+ *    >= 0 a CUDA device ordinal.
+ *  - `Scalar` attributes are double, `float` attributes float, bool attributes int32_t.
+ *  - In-place outputs alias inputs exactly as the YAML `inplace:` maps of the reference say;
+ *    a distinct output buffer is honoured by a device copy first.
+ *  - All work is enqueued on `stream` (a cudaStream_t passed as void*); nothing synchronises
+ *    the device unless documented.  The caller owns every buffer.
+ *  - Every function returns a PRB_Status; prb_last_error_message() returns the thread-local
+ *    text of the last failure.  Nothing throws across the ABI.
+ *  - There is no CPU fallback: on a machine without a usable CUDA device every compute entry
+ *    point fails with PRB_EXTERNAL.
+ */
+#ifndef PADDLE_RAY_B200_H_
+#define PADDLE_RAY_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ref: paddle/phi/backends/device_ext.h:55-62 (C_Status) + PADDLE_ENFORCE categories */
+typedef enum PRB_Status {
+  PRB_SUCCESS = 0,
+  PRB_INVALID_ARGUMENT = 1,    /* errors::InvalidArgument */
+  PRB_PRECONDITION_NOT_MET = 2, /* errors::PreconditionNotMet */
+  PRB_OUT_OF_RANGE = 3,        /* errors::OutOfRange */
+  PRB_UNIMPLEMENTED = 4,       /* errors::Unimplemented */
+  PRB_EXTERNAL = 5             /* errors::External: CUDA / NCCL failure */
+} PRB_Status;
+
+/* ref: paddle/phi/common/data_type.h:37-70 */
+typedef enum PRB_DataType {
+  PRB_BOOL = 1,
+  PRB_INT32 = 7,
+  PRB_INT64 = 9,
+  PRB_FLOAT32 = 10,
+  PRB_FLOAT64 = 11,
+  PRB_FLOAT16 = 15,
+  PRB_BFLOAT16 = 16
+} PRB_DataType;
+
+typedef struct PRB_Tensor {
+  void* data;
+  int64_t numel;
+  int32_t dtype;  /* PRB_DataType */
+  int32_t device; /* -1 = host, >= 0 = CUDA ordinal */
+} PRB_Tensor;
+
+const char* prb_last_error_message(void);
+const char* prb_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Optimizer kernels
+ * ---------------------------------------------------------------------------------------- */
+
+/* adamw_  ref: paddle/phi/kernels/adamw_kernel.h:22-49, gpu/adamw_kernel.cu:141-343,
+ *              paddle/phi/api/yaml/legacy_ops.yaml:68-77.
+ * beta1_pow/beta2_pow may live on the host (value captured at call time, updated on the host;
+ * ref :234-289) or on the device (read in-kernel, updated by a device kernel; ref :290-341).
+ * skip_update on the device is consumed on the device (no D2H sync) unless the beta-pows are on
+ * the host, in which case the flag is read back like the reference does (ref :177-187). */
+int32_t prb_adamw(const PRB_Tensor* param, const PRB_Tensor* grad, const PRB_Tensor* learning_rate,
+                  const PRB_Tensor* moment1, const PRB_Tensor* moment2, const PRB_Tensor* beta1_pow,
+                  const PRB_Tensor* beta2_pow, const PRB_Tensor* master_param /* optional */,
+                  const PRB_Tensor* skip_update /* optional */, double beta1, double beta2, double epsilon,
+                  float lr_ratio, float coeff, int32_t with_decay, int32_t lazy_mode,
+                  int64_t min_row_size_to_use_multithread, int32_t multi_precision,
+                  int32_t use_global_beta_pow, PRB_Tensor* param_out, PRB_Tensor* moment1_out,
+                  PRB_Tensor* moment2_out, PRB_Tensor* beta1_pow_out, PRB_Tensor* beta2_pow_out,
+                  PRB_Tensor* master_param_out /* optional */, void* stream);
+
+/* adam_  ref: paddle/phi/kernels/adam_kernel.h:22-45, gpu/adam_kernel.cu:128-266,
+ *             legacy_ops.yaml:45-55 */
+int32_t prb_adam(const PRB_Tensor* param, const PRB_Tensor* grad, const PRB_Tensor* learning_rate,
+                 const PRB_Tensor* moment1, const PRB_Tensor* moment2, const PRB_Tensor* beta1_pow,
+                 const PRB_Tensor* beta2_pow, const PRB_Tensor* master_param /* optional */,
+                 const PRB_Tensor* skip_update /* optional */, double beta1, double beta2, double epsilon,
+                 int32_t lazy_mode, int64_t min_row_size_to_use_multithread, int32_t multi_precision,
+                 int32_t use_global_beta_pow, PRB_Tensor* param_out, PRB_Tensor* moment1_out,
+                 PRB_Tensor* moment2_out, PRB_Tensor* beta1_pow_out, PRB_Tensor* beta2_pow_out,
+                 PRB_Tensor* master_param_out /* optional */, void* stream);
+
+/* merged_adam_  ref: paddle/phi/kernels/adam_kernel.h:47-68, gpu/adam_kernel.cu:268-366,
+ *                    legacy_ops.yaml:1090-1099.  One launch for the whole list (the reference
+ *                    loops over per-tensor launches); bit-equal to per-tensor prb_adam. */
+int32_t prb_merged_adam(const PRB_Tensor* param, const PRB_Tensor* grad, const PRB_Tensor* learning_rate,
+                        const PRB_Tensor* moment1, const PRB_Tensor* moment2, const PRB_Tensor* beta1_pow,
+                        const PRB_Tensor* beta2_pow, const PRB_Tensor* master_param /* optional list */,
+                        int64_t num, double beta1, double beta2, double epsilon, int32_t multi_precision,
+                        int32_t use_global_beta_pow, PRB_Tensor* param_out, PRB_Tensor* moment1_out,
+                        PRB_Tensor* moment2_out, PRB_Tensor* beta1_pow_out, PRB_Tensor* beta2_pow_out,
+                        PRB_Tensor* master_param_out /* optional list */, void* stream);
+
+/* fused_adam_  ref: paddle/phi/kernels/fused_adam_kernel.h:22-47, gpu/fused_adam_kernel.cu:263-486,
+ *                   legacy_ops.yaml:718-727.  One learning rate; tensor 0's beta-pows are applied
+ *                   to every tensor (ref :292-293,368-369); zero-length tensors are legal;
+ *                   chunk_size is accepted for signature parity and does not change results. */
+int32_t prb_fused_adam(const PRB_Tensor* params, const PRB_Tensor* grads, const PRB_Tensor* learning_rate,
+                       const PRB_Tensor* moments1, const PRB_Tensor* moments2, const PRB_Tensor* beta1_pows,
+                       const PRB_Tensor* beta2_pows, const PRB_Tensor* master_params /* optional list */,
+                       int64_t num, const PRB_Tensor* skip_update /* optional */, double beta1, double beta2,
+                       double epsilon, int32_t chunk_size, float weight_decay, int32_t use_adamw,
+                       int32_t multi_precision, int32_t use_global_beta_pow, PRB_Tensor* params_out,
+                       PRB_Tensor* moments1_out, PRB_Tensor* moments2_out, PRB_Tensor* beta1_pows_out,
+                       PRB_Tensor* beta2_pows_out, PRB_Tensor* master_params_out /* optional list */,
+                       void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * AMP + global-norm clip
+ * ---------------------------------------------------------------------------------------- */
+
+/* check_finite_and_unscale_  ref: paddle/phi/kernels/amp_kernel.h:24-29,
+ *                            gpu/amp_kernel.cu:27-82,267-348, legacy_ops.yaml:292-302.
+ * found_infinite: one bool on the device. */
+int32_t prb_check_finite_and_unscale(const PRB_Tensor* xs, int64_t num, const PRB_Tensor* scale,
+                                     PRB_Tensor* outs, PRB_Tensor* found_infinite, void* stream);
+
+/* update_loss_scaling_  ref: paddle/phi/kernels/amp_kernel.h:31-46, impl/amp_kernel_impl.h:38-180,
+ *                       gpu/amp_kernel.cu:84-146, legacy_ops.yaml:1708-1717.  All state on device. */
+int32_t prb_update_loss_scaling(const PRB_Tensor* xs, int64_t num, const PRB_Tensor* found_infinite,
+                                const PRB_Tensor* prev_loss_scaling, const PRB_Tensor* in_good_steps,
+                                const PRB_Tensor* in_bad_steps, int32_t incr_every_n_steps,
+                                int32_t decr_every_n_nan_or_inf, float incr_ratio, float decr_ratio,
+                                int32_t stop_update, PRB_Tensor* outs, PRB_Tensor* loss_scaling,
+                                PRB_Tensor* out_good_steps, PRB_Tensor* out_bad_steps, void* stream);
+
+/* squared_l2_norm  ref: paddle/phi/kernels/squared_l2_norm_kernel.h:21-24,
+ *                  gpu/squared_l2_norm_kernel.cu:23-35, legacy_ops.yaml:1504-1511.
+ * out: one element of x's dtype on the device.  Deterministic run to run
+ * (ref: test_squared_l2_norm_op.py:98-111).  Allocates per-call scratch from the library's
+ * workspace (grown with cudaMalloc when needed). */
+int32_t prb_squared_l2_norm(const PRB_Tensor* x, PRB_Tensor* out, void* stream);
+
+/* Multi-tensor form of the per-gradient loop in ClipGradByGlobalNorm._dygraph_clip
+ * (ref: python/paddle/nn/clip.py:643-736): per-tensor squared norms (typed like the op),
+ * their grouped sum, sqrt, clip = max_norm / max(norm, max_norm) (or the auto_skip_clip rule),
+ * then g *= T(clip) in place.  global_norm_out / clip_out: optional fp32 device scalars.
+ * use_mp_type mirrors _clip_by_global_norm_using_mp_type (ref: clip.py:179-202). */
+int32_t prb_clip_grad_by_global_norm(PRB_Tensor* grads, int64_t num, float clip_norm, int32_t auto_skip_clip,
+                                     int32_t use_mp_type, PRB_Tensor* global_norm_out /* optional */,
+                                     PRB_Tensor* clip_out /* optional */, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Bucket operators
+ * ---------------------------------------------------------------------------------------- */
+
+/* scale  ref: paddle/phi/kernels/scale_kernel.h:23-29, gpu/scale_kernel.cu:24-67, ops.yaml:1251-1262 */
+int32_t prb_scale(const PRB_Tensor* x, double scale, float bias, int32_t bias_after_scale, PRB_Tensor* out,
+                  void* stream);
+
+/* Dense 1-D concat / split of same-dtype tensors (what EagerGroup::ConcatTensors / SplitTensors
+ * do to a bucket).  ref: paddle/fluid/distributed/collective/reducer.cc:358-459,
+ * paddle/phi/kernels/funcs/concat_and_split_functor.cu:553-632,758-872.  Bit-exact byte moves. */
+int32_t prb_concat(const PRB_Tensor* ins, int64_t num, PRB_Tensor* out, void* stream);
+int32_t prb_split(const PRB_Tensor* in, PRB_Tensor* outs, int64_t num, void* stream);
+
+/* cast between float32 / bfloat16 / float16 (init-time helper: master weights are the fp32 cast of
+ * 16-bit parameters, ref: python/paddle/optimizer/optimizer.py:640-666). */
+int32_t prb_cast(const PRB_Tensor* x, PRB_Tensor* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Reducer (EagerReducer) and communicator (ProcessGroupNCCL, allreduce only)
+ * ---------------------------------------------------------------------------------------- */
+
+/* eager_assign_group_by_size  ref: reducer.cc:45-156, paddle/fluid/pybind/distributed_py.cc:64-77.
+ * Output: groups as a flat index list + per-group sizes (caller provides num-sized arrays). */
+int32_t prb_assign_group_by_size(const int64_t* numels, const int32_t* dtypes, const uint8_t* is_sparse,
+                                 int64_t num, const uint64_t* group_size_limits, int64_t num_limits,
+                                 const int64_t* tensor_indices, int64_t num_indices, int64_t* out_flat,
+                                 int64_t* out_group_sizes, int64_t* out_num_groups);
+
+typedef struct PRB_Comm PRB_Comm;
+typedef struct PRB_Reducer PRB_Reducer;
+
+#define PRB_UNIQUE_ID_BYTES 128
+/* ref: process_group_nccl.cc:559-571 (rank 0 creates the ncclUniqueId, peers fetch it from the store) */
+int32_t prb_comm_get_unique_id(uint8_t id[PRB_UNIQUE_ID_BYTES]);
+/* ref: process_group_nccl.cc:688-737 (communicator + dedicated comm stream per device) */
+int32_t prb_comm_init_rank(const uint8_t id[PRB_UNIQUE_ID_BYTES], int32_t nranks, int32_t rank, int32_t device,
+                           PRB_Comm** out);
+/* A communicator of one rank that needs no NCCL (nranks == 1). */
+int32_t prb_comm_init_single(int32_t device, PRB_Comm** out);
+int32_t prb_comm_destroy(PRB_Comm* comm);
+int32_t prb_comm_nranks(const PRB_Comm* comm);
+int32_t prb_comm_rank(const PRB_Comm* comm);
+void* prb_comm_stream(const PRB_Comm* comm);
+/* ref: ProcessGroupNCCL::AllReduce process_group_nccl.cc:841-865 (in place when out == in).
+ * op: 0 = sum, 1 = max.  Enqueued on `stream` (pass prb_comm_stream(comm) for the side stream). */
+int32_t prb_comm_all_reduce(PRB_Comm* comm, const PRB_Tensor* in, PRB_Tensor* out, int32_t op, void* stream);
+/* ref: ProcessGroupNCCL::Broadcast process_group_nccl.cc:867-... (init-time parameter sync) */
+int32_t prb_comm_broadcast(PRB_Comm* comm, PRB_Tensor* buf, int32_t root, void* stream);
+
+/* EagerReducer(tensors, group_indices, is_sparse, process_group, group_size_limits, find_unused)
+ * ref: reducer.h:88-142, reducer.cc:461-618, distributed_py.cc:1285-1315.
+ * `grads[i]` is the gradient buffer of parameter i (dense only).  Buckets live in one persistent
+ * arena owned by the reducer (no per-step allocation, unlike ref reducer.cc:359-360); segment
+ * starts inside a bucket are padded to 256 B (internal layout, never visible to the caller).
+ * prb_reducer_bucket_view exposes each parameter's slot so the optimizer can consume the reduced
+ * gradients straight from the arena.
+ * comm == NULL builds a host-only reducer: the hook/group state machine without any device work
+ * (used to validate ordering and error behaviour on machines without a GPU). */
+int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* group_flat,
+                           const int64_t* group_sizes, int64_t num_groups, PRB_Comm* comm,
+                           int32_t find_unused_parameters, PRB_Reducer** out);
+int32_t prb_reducer_destroy(PRB_Reducer* r);
+/* ref: EagerReducer::PrepareForBackward reducer.cc:669-728 */
+int32_t prb_reducer_prepare_for_backward(PRB_Reducer* r);
+/* The result of the reference's TraverseBackwardGraph (reducer.cc:620-667), which belongs to the
+ * host autograd engine: parameters that will receive no gradient in this backward.  Call after
+ * prepare_for_backward (requires find_unused_parameters).  Their bucket slots are zero-filled and
+ * they are marked ready together with the first real hook (ref :761-771,833-855).  Unlike the
+ * reference (ProcessUnusedDenseVars :941-1011: int32 bitmap allreduce + host sync + copy), the
+ * reduced slot is simply unpacked into the gradient buffer like any other -- no host sync. */
+int32_t prb_reducer_set_unused_vars(PRB_Reducer* r, const int64_t* var_indices, int64_t num);
+/* ref: EagerReducer::AddDistHook / MarkVarReady / MarkGroupReady reducer.cc:730-930.
+ * `stream` is the calc stream the gradient was produced on.  When a group (and every group
+ * before it) is complete: pack+scale on `stream`, event fence, allreduce on the comm stream
+ * (ref: FusedAllReduceSchedule :1037-1070).  When the last group is launched the reducer
+ * finalises (ref: FinalizeBackward :1013-1035): `stream` waits for the comm stream, and, unless
+ * unpack is disabled, reduced buckets are scattered back into the gradient buffers. */
+int32_t prb_reducer_mark_var_ready(PRB_Reducer* r, int64_t var_index, void* stream);
+/* Batch form (one ABI crossing for many hooks; the reference's hooks are C++ callbacks). */
+int32_t prb_reducer_mark_vars_ready(PRB_Reducer* r, const int64_t* var_indices, int64_t num, void* stream);
+/* 1 -> split reduced buckets back into the grads at finalize (reference behaviour, default);
+ * 0 -> leave them in the arena for prb_dp_step_tail to consume directly. */
+int32_t prb_reducer_set_unpack(PRB_Reducer* r, int32_t enabled);
+/* 1 when every group of the current backward has been launched and finalised. */
+int32_t prb_reducer_is_finalized(const PRB_Reducer* r);
+/* Device address / element offset of parameter i's slot inside the bucket arena. */
+int32_t prb_reducer_bucket_view(const PRB_Reducer* r, int64_t var_index, PRB_Tensor* out);
+/* Number of groups launched so far in this backward, and their order (for tests). */
+int32_t prb_reducer_launched_groups(const PRB_Reducer* r, int64_t* out_order, int64_t capacity, int64_t* out_num);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused step tail: unscale + inf/nan check + global-norm clip + Adam/AdamW in two passes
+ * (norm pass, update pass) over the reducer's bucket arena or over caller gradients.
+ * Composition of prb_check_finite_and_unscale, prb_clip_grad_by_global_norm and
+ * prb_merged_adam / prb_adamw with identical per-element arithmetic
+ * (ref: python/paddle/amp/grad_scaler.py:253-399,742-790; python/paddle/nn/clip.py:643-736;
+ *  python/paddle/optimizer/optimizer.py:983-1010; python/paddle/optimizer/adamw.py:390-470).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct PRB_TailConfig {
+  double beta1, beta2, epsilon;
+  float coeff;               /* weight decay coefficient (AdamW) */
+  int32_t use_adamw;         /* 1: adamw (decay line present), 0: adam */
+  int32_t multi_precision;   /* master params present */
+  int32_t use_amp;           /* 1: unscale by 1/loss_scale and check finiteness */
+  int32_t use_clip;          /* 1: ClipGradByGlobalNorm */
+  float clip_norm;
+  int32_t auto_skip_clip;
+  int32_t use_mp_type;       /* clip norm in fp32 for 16-bit grads (ref: clip.py:179-202) */
+  int32_t write_back_grads;  /* 1: store the unscaled/clipped gradient back (reference-visible grads) */
+  int32_t zero_grads;        /* 1: clear_grad(set_to_zero=True) folded in (ref: optimizer.py:1333-1381) */
+} PRB_TailConfig;
+
+/* Per-tensor attributes follow adamw_: lr_ratio[i], with_decay[i] (NULL = 1.0 / all decayed).
+ * found_inf (bool, device), global_norm/clip (fp32, device) are outputs (optional except found_inf
+ * when use_amp).  beta-pows live on the device and are advanced on the device unless found_inf. */
+int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor* params, PRB_Tensor* grads,
+                         const PRB_Tensor* learning_rate, const PRB_Tensor* moments1,
+                         const PRB_Tensor* moments2, PRB_Tensor* beta1_pow, PRB_Tensor* beta2_pow,
+                         const PRB_Tensor* master_params /* optional list */, int64_t num,
+                         const float* lr_ratio /* optional [num] host */,
+                         const uint8_t* with_decay /* optional [num] host */,
+                         const PRB_Tensor* loss_scale /* fp32 device scalar, required if use_amp */,
+                         PRB_Tensor* found_inf, PRB_Tensor* global_norm_out, PRB_Tensor* clip_out,
+                         void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Runtime helpers for the torch-free Python host (thin wrappers over the CUDA runtime).
+ * ---------------------------------------------------------------------------------------- */
+int32_t prb_device_count(int32_t* out);
+int32_t prb_set_device(int32_t device);
+int32_t prb_device_info(int32_t device, int32_t* sm_count, int64_t* l2_bytes, int64_t* total_mem, char name[128]);
+int32_t prb_malloc(int64_t bytes, void** out);
+int32_t prb_free(void* ptr);
+int32_t prb_host_alloc(int64_t bytes, void** out); /* pinned */
+int32_t prb_host_free(void* ptr);
+int32_t prb_memcpy_h2d(void* dst, const void* src, int64_t bytes, void* stream);
+int32_t prb_memcpy_d2h(void* dst, const void* src, int64_t bytes, void* stream);
+int32_t prb_memcpy_d2d(void* dst, const void* src, int64_t bytes, void* stream);
+int32_t prb_memset(void* dst, int32_t value, int64_t bytes, void* stream);
+int32_t prb_stream_create(int32_t high_priority, void** out);
+int32_t prb_stream_destroy(void* stream);
+int32_t prb_stream_synchronize(void* stream);
+int32_t prb_device_synchronize(void);
+int32_t prb_event_create(void** out);
+int32_t prb_event_destroy(void* event);
+int32_t prb_event_record(void* event, void* stream);
+int32_t prb_event_synchronize(void* event);
+int32_t prb_event_elapsed_ms(void* start, void* stop, float* out_ms);
+int32_t prb_stream_wait_event(void* stream, void* event);
+/* Busy kernel of roughly `microseconds` on `stream` (synthetic backward producer for overlap runs). */
+int32_t prb_spin(int64_t microseconds, void* stream);
+/* Writes `bytes` of scratch to evict L2 between timed iterations. */
+int32_t prb_flush_l2(void* stream);
+/* Number of kernels this library has launched since load (bench.py's gpu_launches). */
+int64_t prb_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PADDLE_RAY_B200_H_ */

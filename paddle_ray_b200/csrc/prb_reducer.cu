@@ -1,0 +1,561 @@
+// Bucket assignment, the reducer state machine and the NCCL communicator.
+//
+//   ref: Eager_AssignGroupBySize   paddle/fluid/distributed/collective/reducer.cc:45-156
+//        EagerReducer              reducer.h:88-142, reducer.cc:461-1070
+//        ProcessGroupNCCL          process_group_nccl.cc:559-571,658-667,688-789,841-865
+//
+// B200-first differences from the reference (none changes a result):
+//  * one persistent bucket arena, allocated once (the reference allocates a fresh bucket per group
+//    per step, reducer.cc:359-360), segment starts padded to 256 B so pack/unpack are pure
+//    256-bit vector passes;
+//  * pack and the 1/nranks scale are ONE kernel (the reference runs concat, then scale_);
+//  * NCCL is loaded at run time (dlopen), so the library also loads where NCCL is absent and a
+//    single-rank communicator needs no NCCL at all.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <map>
+#include <mutex>
+#include <vector>
+
+#include "prb_bucket.cuh"
+
+namespace prb {
+namespace {
+
+// ---------------------------------------------------------------- NCCL dynload
+struct NcclApi {
+  void* handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  ncclResult_t (*GetVersion)(int*) = nullptr;
+};
+NcclApi g_nccl;
+std::mutex g_nccl_mu;
+
+int32_t load_nccl() {
+  std::lock_guard<std::mutex> lk(g_nccl_mu);
+  if (g_nccl.handle) return PRB_SUCCESS;
+  const char* env = getenv("PRB_NCCL_LIB");
+  const char* names[] = {env, "libnccl.so.2", "libnccl.so"};
+  void* h = nullptr;
+  for (const char* n : names) {
+    if (n == nullptr || *n == 0) continue;
+    h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (h) break;
+  }
+  PRB_ENFORCE(h != nullptr, PRB_EXTERNAL, "cannot load NCCL (libnccl.so.2): %s", dlerror());
+#define PRB_SYM(field, name)                                                   \
+  g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(dlsym(h, name));     \
+  PRB_ENFORCE(g_nccl.field != nullptr, PRB_EXTERNAL, "NCCL symbol %s not found", name)
+  PRB_SYM(GetUniqueId, "ncclGetUniqueId");
+  PRB_SYM(CommInitRank, "ncclCommInitRank");
+  PRB_SYM(CommDestroy, "ncclCommDestroy");
+  PRB_SYM(AllReduce, "ncclAllReduce");
+  PRB_SYM(Broadcast, "ncclBroadcast");
+  PRB_SYM(GetErrorString, "ncclGetErrorString");
+  PRB_SYM(GetVersion, "ncclGetVersion");
+#undef PRB_SYM
+  g_nccl.handle = h;
+  return PRB_SUCCESS;
+}
+
+#define PRB_NCCL(expr)                                                                               \
+  do {                                                                                               \
+    ncclResult_t _r = (expr);                                                                        \
+    if (_r != ncclSuccess)                                                                           \
+      PRB_FAIL(PRB_EXTERNAL, "NCCL error at %s:%d: %s", __FILE__, __LINE__, g_nccl.GetErrorString(_r)); \
+  } while (0)
+
+int32_t nccl_dtype(int32_t dt, ncclDataType_t* out) {
+  switch (dt) {  // ref paddle/phi/core/utils/data_type.h:224-234
+    case PRB_FLOAT32: *out = ncclFloat; return PRB_SUCCESS;
+    case PRB_FLOAT64: *out = ncclDouble; return PRB_SUCCESS;
+    case PRB_FLOAT16: *out = ncclHalf; return PRB_SUCCESS;
+    case PRB_BFLOAT16: *out = ncclBfloat16; return PRB_SUCCESS;
+    case PRB_INT32: *out = ncclInt32; return PRB_SUCCESS;
+    case PRB_INT64: *out = ncclInt64; return PRB_SUCCESS;
+    default: PRB_FAIL(PRB_INVALID_ARGUMENT, "no NCCL type for dtype %s", dtype_name(dt));
+  }
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+}  // namespace prb
+
+using namespace prb;
+
+struct PRB_Comm {
+  int nranks = 1, rank = 0, device = 0;
+  ncclComm_t comm = nullptr;
+  cudaStream_t stream = nullptr;  // dedicated high-priority comm stream (ref process_group_nccl.cc:688-737)
+};
+
+namespace {
+struct Group {
+  std::vector<int64_t> vars;
+  std::vector<int64_t> slot_off;  // element offset of each var inside the group's region (256-B padded)
+  int64_t length = 0;             // padded element count handed to the allreduce
+  int32_t dtype = 0;
+  size_t arena_off = 0;           // byte offset of the region inside the arena
+  int64_t pending = 0;
+  cudaEvent_t ready = nullptr;    // recorded on the calc stream after pack
+  cudaEvent_t done = nullptr;     // recorded on the comm stream after allreduce (+unpack)
+  bool has_unused = false;
+};
+}  // namespace
+
+struct PRB_Reducer {
+  std::vector<PRB_Tensor> grads;
+  std::vector<Group> groups;
+  std::vector<std::pair<int64_t, int64_t>> locator;  // var -> (group, slot)   (ref reducer.h:82-86)
+  PRB_Comm* comm = nullptr;
+  char* arena = nullptr;
+  size_t arena_bytes = 0;
+  size_t next_group = 0;
+  std::vector<uint8_t> ready;
+  std::vector<uint8_t> unused;
+  std::vector<int64_t> unused_list;
+  bool has_marked_unused = false;
+  bool need_finalize = false;
+  bool grad_need_hooks = false;
+  bool finalized = false;
+  bool unpack = true;
+  bool find_unused = false;
+  bool dry = false;  // host-only: state machine without device work (comm == NULL)
+  std::vector<int64_t> launched;
+};
+
+namespace {
+
+int32_t group_tables(PRB_Reducer* r, Group& g, bool for_unpack, cudaStream_t stream, DeviceTable* tab) {
+  std::vector<MapDesc> descs;
+  std::vector<int64_t> numels;
+  const int es = dtype_size(g.dtype);
+  for (size_t s = 0; s < g.vars.size(); ++s) {
+    const int64_t v = g.vars[s];
+    if (!for_unpack && r->unused[v]) continue;  // slot is zero-filled instead (ref reducer.cc:833-855)
+    MapDesc d{};
+    char* slot = r->arena + g.arena_off + (size_t)g.slot_off[s] * es;
+    d.src = for_unpack ? (const void*)slot : (const void*)r->grads[v].data;
+    d.dst = for_unpack ? r->grads[v].data : (void*)slot;
+    d.aligned = map_aligned(d.src, d.dst, es) ? 1 : 0;
+    descs.push_back(d);
+    numels.push_back(r->grads[v].numel);
+  }
+  return get_table(descs.data(), sizeof(MapDesc), (int)descs.size(), numels.data(), kMapChunk, stream, tab);
+}
+
+// ref: FusedAllReduceSchedule reducer.cc:1037-1070 ("concat > div_nranks > allreduce > split")
+int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
+  Group& g = r->groups[gi];
+  if (r->dry) {
+    r->launched.push_back((int64_t)gi);
+    return PRB_SUCCESS;
+  }
+  PRB_Comm* c = r->comm;
+  const int es = dtype_size(g.dtype);
+  char* region = r->arena + g.arena_off;
+  if (g.has_unused) {
+    for (size_t s = 0; s < g.vars.size(); ++s)
+      if (r->unused[g.vars[s]])
+        PRB_CUDA(cudaMemsetAsync(region + (size_t)g.slot_off[s] * es, 0, (size_t)r->grads[g.vars[s]].numel * es, calc));
+  }
+  // pack + scale_(bucket, 1.0/nranks, 0.0, false) in one pass, calc stream
+  DeviceTable pack;
+  PRB_TRY(group_tables(r, g, false, calc, &pack));
+  PRB_TRY(launch_scale(g.dtype, pack, 1.0 / (double)c->nranks, 0.0f, false, calc));
+  if (c->nranks > 1) {
+    // SyncDefaultStream: comm stream waits for the calc stream (ref process_group_nccl.cc:658-667)
+    PRB_CUDA(cudaEventRecord(g.ready, calc));
+    PRB_CUDA(cudaStreamWaitEvent(c->stream, g.ready, 0));
+    ncclDataType_t nt;
+    PRB_TRY(nccl_dtype(g.dtype, &nt));
+    PRB_NCCL(g_nccl.AllReduce(region, region, (size_t)g.length, nt, ncclSum, c->comm, c->stream));
+    if (r->unpack) {  // the reference also splits on the comm stream (reducer.cc:1062-1069)
+      DeviceTable un;
+      PRB_TRY(group_tables(r, g, true, c->stream, &un));
+      PRB_TRY(launch_copy(es, un, c->stream));
+    }
+    PRB_CUDA(cudaEventRecord(g.done, c->stream));
+  } else if (r->unpack) {
+    DeviceTable un;
+    PRB_TRY(group_tables(r, g, true, calc, &un));
+    PRB_TRY(launch_copy(es, un, calc));
+  }
+  r->launched.push_back((int64_t)gi);
+  return PRB_SUCCESS;
+}
+
+// ref: FinalizeBackward reducer.cc:1013-1035 -- task->Synchronize(): calc stream waits on comm events
+int32_t finalize(PRB_Reducer* r, cudaStream_t calc) {
+  r->need_finalize = false;
+  r->grad_need_hooks = false;
+  if (!r->dry && r->comm->nranks > 1)
+    for (Group& g : r->groups) PRB_CUDA(cudaStreamWaitEvent(calc, g.done, 0));
+  r->finalized = true;
+  return PRB_SUCCESS;
+}
+
+int32_t mark_group_ready(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
+  // ref: MarkGroupReady reducer.cc:903-930
+  PRB_ENFORCE(gi >= r->next_group, PRB_PRECONDITION_NOT_MET,
+              "The index of the incoming group must be greater than or equal to the previously synchronized group "
+              "index, expect it to greater than or equal to %zu, but got %zu.",
+              r->next_group, gi);
+  if (gi > r->next_group) return PRB_SUCCESS;  // launched later, strictly in order
+  for (; r->next_group < r->groups.size() && r->groups[r->next_group].pending == 0; ++r->next_group)
+    PRB_TRY(schedule_group(r, r->next_group, calc));
+  return PRB_SUCCESS;
+}
+
+int32_t mark_var_ready_impl(PRB_Reducer* r, int64_t v, bool is_used, cudaStream_t calc) {
+  // ref: MarkVarReady reducer.cc:774-901
+  PRB_ENFORCE(!r->ready[v], PRB_PRECONDITION_NOT_MET,
+              "Error happened, when parameter[%lld] has been ready before. Please set find_unused_parameters=True "
+              "to traverse backward graph in each step to prepare reduce in advance.",
+              (long long)v);
+  r->ready[v] = 1;
+  r->need_finalize = true;
+  (void)is_used;
+  const size_t gi = (size_t)r->locator[v].first;
+  if (--r->groups[gi].pending == 0) PRB_TRY(mark_group_ready(r, gi, calc));
+  if (r->next_group == r->groups.size()) PRB_TRY(finalize(r, calc));
+  return PRB_SUCCESS;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t prb_assign_group_by_size(const int64_t* numels, const int32_t* dtypes, const uint8_t* is_sparse, int64_t num,
+                                 const uint64_t* limits, int64_t num_limits, const int64_t* tensor_indices,
+                                 int64_t num_indices, int64_t* out_flat, int64_t* out_group_sizes,
+                                 int64_t* out_num_groups) {
+  PRB_ENFORCE(num >= 0 && num_limits >= 1 && limits != nullptr, PRB_INVALID_ARGUMENT,
+              "assign_group_by_size: need at least one group size limit");
+  if (num_indices > 0) {  // check_perm (ref reducer.cc:57-75)
+    std::vector<uint8_t> cnt((size_t)num_indices, 0);
+    for (int64_t i = 0; i < num_indices; ++i) {
+      const int64_t x = tensor_indices[i];
+      PRB_ENFORCE(x >= 0 && x < num_indices && !cnt[(size_t)x], PRB_PRECONDITION_NOT_MET,
+                  "tensor_indices must be a permutation from 0 to %lld", (long long)num_indices);
+      cnt[(size_t)x] = 1;
+    }
+  }
+  std::vector<std::vector<int64_t>> res;
+  std::map<int32_t, size_t> limit_index;                               // dtype -> index into limits
+  std::map<int32_t, std::pair<std::vector<int64_t>, uint64_t>> next;   // dtype -> (open group, bytes)
+  for (int64_t i = 0; i < num; ++i) {
+    const int64_t real = num_indices > 0 ? tensor_indices[i] : i;
+    if (is_sparse[real]) {  // a sparse var is a group of its own
+      res.push_back({real});
+      continue;
+    }
+    const int32_t dt = dtypes[i];
+    const int es = dtype_size(dt);
+    PRB_ENFORCE(es > 0, PRB_INVALID_ARGUMENT, "assign_group_by_size: unknown dtype code %d", dt);
+    auto& grp = next[dt];
+    grp.first.push_back(real);
+    grp.second += (uint64_t)es * (uint64_t)numels[i];
+    if (!limit_index.count(dt)) limit_index[dt] = 0;
+    size_t& li = limit_index[dt];
+    if (grp.second >= limits[li]) {  // ">=" after adding: a bucket may overshoot by one tensor
+      res.emplace_back(std::move(grp.first));
+      grp = std::pair<std::vector<int64_t>, uint64_t>();
+      li = std::min(li + 1, (size_t)num_limits - 1);
+    }
+  }
+  for (auto& e : next)
+    if (!e.second.first.empty()) res.emplace_back(std::move(e.second.first));
+  if (num_indices == 0)
+    std::sort(res.begin(), res.end(),
+              [](const std::vector<int64_t>& x, const std::vector<int64_t>& y) { return x.front() < y.front(); });
+  int64_t k = 0;
+  for (size_t g = 0; g < res.size(); ++g) {
+    out_group_sizes[g] = (int64_t)res[g].size();
+    for (int64_t v : res[g]) out_flat[k++] = v;
+  }
+  *out_num_groups = (int64_t)res.size();
+  return PRB_SUCCESS;
+}
+
+// ---------------------------------------------------------------- communicator
+int32_t prb_comm_get_unique_id(uint8_t id[PRB_UNIQUE_ID_BYTES]) {
+  PRB_TRY(load_nccl());
+  static_assert(sizeof(ncclUniqueId) == PRB_UNIQUE_ID_BYTES, "ncclUniqueId size");
+  ncclUniqueId uid;
+  PRB_NCCL(g_nccl.GetUniqueId(&uid));
+  memcpy(id, &uid, sizeof(uid));
+  return PRB_SUCCESS;
+}
+
+int32_t prb_comm_init_rank(const uint8_t id[PRB_UNIQUE_ID_BYTES], int32_t nranks, int32_t rank, int32_t device,
+                           PRB_Comm** out) {
+  PRB_TRY(require_device());
+  PRB_ENFORCE(nranks >= 1 && rank >= 0 && rank < nranks, PRB_INVALID_ARGUMENT, "comm_init_rank: bad rank %d of %d", rank,
+              nranks);
+  PRB_TRY(load_nccl());
+  PRB_CUDA(cudaSetDevice(device));
+  PRB_Comm* c = new PRB_Comm();
+  c->nranks = nranks;
+  c->rank = rank;
+  c->device = device;
+  ncclUniqueId uid;
+  memcpy(&uid, id, sizeof(uid));
+  ncclResult_t rc = g_nccl.CommInitRank(&c->comm, nranks, uid, rank);
+  if (rc != ncclSuccess) {
+    delete c;
+    PRB_FAIL(PRB_EXTERNAL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString(rc));
+  }
+  int lo = 0, hi = 0;
+  PRB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  PRB_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, hi));
+  *out = c;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_comm_init_single(int32_t device, PRB_Comm** out) {
+  PRB_TRY(require_device());
+  PRB_CUDA(cudaSetDevice(device));
+  PRB_Comm* c = new PRB_Comm();
+  c->device = device;
+  int lo = 0, hi = 0;
+  PRB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  PRB_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, hi));
+  *out = c;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_comm_destroy(PRB_Comm* c) {
+  if (!c) return PRB_SUCCESS;
+  if (c->comm) g_nccl.CommDestroy(c->comm);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_comm_nranks(const PRB_Comm* c) { return c ? c->nranks : 0; }
+int32_t prb_comm_rank(const PRB_Comm* c) { return c ? c->rank : -1; }
+void* prb_comm_stream(const PRB_Comm* c) { return c ? (void*)c->stream : nullptr; }
+
+int32_t prb_comm_all_reduce(PRB_Comm* c, const PRB_Tensor* in, PRB_Tensor* out, int32_t op, void* stream) {
+  PRB_ENFORCE(c && in && out && in->numel == out->numel && in->dtype == out->dtype, PRB_INVALID_ARGUMENT,
+              "all_reduce: bad arguments");
+  PRB_ENFORCE(op == 0 || op == 1, PRB_INVALID_ARGUMENT, "all_reduce: op must be 0 (sum) or 1 (max)");
+  if (c->nranks == 1) {
+    if (out->data != in->data)
+      PRB_CUDA(cudaMemcpyAsync(out->data, in->data, (size_t)in->numel * dtype_size(in->dtype), cudaMemcpyDeviceToDevice,
+                               (cudaStream_t)stream));
+    return PRB_SUCCESS;
+  }
+  ncclDataType_t nt;
+  PRB_TRY(nccl_dtype(in->dtype, &nt));
+  PRB_NCCL(g_nccl.AllReduce(in->data, out->data, (size_t)in->numel, nt, op == 0 ? ncclSum : ncclMax, c->comm,
+                            (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+
+int32_t prb_comm_broadcast(PRB_Comm* c, PRB_Tensor* buf, int32_t root, void* stream) {
+  PRB_ENFORCE(c && buf && root >= 0 && root < c->nranks, PRB_INVALID_ARGUMENT, "broadcast: bad arguments");
+  if (c->nranks == 1) return PRB_SUCCESS;
+  ncclDataType_t nt;
+  PRB_TRY(nccl_dtype(buf->dtype, &nt));
+  PRB_NCCL(g_nccl.Broadcast(buf->data, buf->data, (size_t)buf->numel, nt, root, c->comm, (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+
+// ---------------------------------------------------------------- reducer
+int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* group_flat, const int64_t* group_sizes,
+                           int64_t num_groups, PRB_Comm* comm, int32_t find_unused_parameters, PRB_Reducer** out) {
+  if (comm != nullptr) PRB_TRY(require_device());
+  PRB_ENFORCE(grads && group_flat && group_sizes && out && num > 0 && num_groups > 0, PRB_INVALID_ARGUMENT,
+              "reducer_create: bad arguments");
+  PRB_Reducer* r = new PRB_Reducer();
+  r->dry = comm == nullptr;
+  r->grads.assign(grads, grads + num);
+  r->comm = comm;
+  r->find_unused = find_unused_parameters != 0;
+  r->locator.assign((size_t)num, {-1, -1});
+  r->ready.assign((size_t)num, 0);
+  r->unused.assign((size_t)num, 0);
+  size_t arena = 0;
+  int64_t k = 0;
+  int32_t status = PRB_SUCCESS;
+  for (int64_t gi = 0; gi < num_groups && status == PRB_SUCCESS; ++gi) {
+    Group g;
+    if (group_sizes[gi] <= 0) {  // ref reducer.cc:536-540
+      set_error("The number of group[%lld]'s elements is 0.", (long long)gi);
+      status = PRB_PRECONDITION_NOT_MET;
+      break;
+    }
+    int64_t off = 0;
+    for (int64_t s = 0; s < group_sizes[gi]; ++s) {
+      const int64_t v = group_flat[k++];
+      if (v < 0 || v >= num || r->locator[(size_t)v].first >= 0) {
+        set_error("reducer_create: group %lld holds an invalid or repeated tensor index %lld", (long long)gi, (long long)v);
+        status = PRB_INVALID_ARGUMENT;
+        break;
+      }
+      const PRB_Tensor& t = r->grads[(size_t)v];
+      if (t.numel <= 0) {  // ref reducer.cc:589-593
+        set_error("The number of tensor %lld's elements is 0.", (long long)v);
+        status = PRB_PRECONDITION_NOT_MET;
+        break;
+      }
+      if (s == 0) g.dtype = t.dtype;
+      if (t.dtype != g.dtype) {  // ref reducer.cc:607-612
+        set_error("Tensor %lld has unexpected dtype.", (long long)v);
+        status = PRB_PRECONDITION_NOT_MET;
+        break;
+      }
+      const int es = dtype_size(t.dtype);
+      if (!(es == 2 || es == 4) || (t.device < 0 && !r->dry)) {
+        set_error("reducer_create: tensor %lld must be a float32/bfloat16/float16 device tensor", (long long)v);
+        status = PRB_UNIMPLEMENTED;
+        break;
+      }
+      r->locator[(size_t)v] = {gi, s};
+      g.vars.push_back(v);
+      g.slot_off.push_back(off);
+      off += (int64_t)(align_up((size_t)t.numel * es, 256) / es);
+    }
+    if (status != PRB_SUCCESS) break;
+    g.length = off;
+    g.arena_off = arena;
+    arena += align_up((size_t)off * dtype_size(g.dtype), 256);
+    r->groups.push_back(std::move(g));
+  }
+  if (status == PRB_SUCCESS)
+    for (int64_t v = 0; v < num; ++v)
+      if (r->locator[(size_t)v].first < 0) {
+        set_error("reducer_create: tensor %lld belongs to no group", (long long)v);
+        status = PRB_INVALID_ARGUMENT;
+        break;
+      }
+  if (status != PRB_SUCCESS) {
+    delete r;
+    return status;
+  }
+  r->arena_bytes = arena;
+  if (r->dry) {
+    r->finalized = true;
+    *out = r;
+    return PRB_SUCCESS;
+  }
+  cudaError_t e = cudaMalloc((void**)&r->arena, arena);
+  if (e == cudaSuccess) e = cudaMemset(r->arena, 0, arena);  // padding gaps stay zero forever
+  for (Group& g : r->groups) {
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.ready, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.done, cudaEventDisableTiming);
+  }
+  if (e != cudaSuccess) {
+    prb_reducer_destroy(r);
+    PRB_FAIL(PRB_EXTERNAL, "reducer_create: CUDA error %s", cudaGetErrorString(e));
+  }
+  r->finalized = true;  // nothing pending before the first prepare_for_backward
+  *out = r;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_destroy(PRB_Reducer* r) {
+  if (!r) return PRB_SUCCESS;
+  if (!r->dry) cudaDeviceSynchronize();
+  for (Group& g : r->groups) {
+    if (g.ready) cudaEventDestroy(g.ready);
+    if (g.done) cudaEventDestroy(g.done);
+  }
+  if (r->arena) cudaFree(r->arena);
+  delete r;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_prepare_for_backward(PRB_Reducer* r) {
+  PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  // ref: PrepareForBackward reducer.cc:669-728
+  PRB_ENFORCE(!r->need_finalize, PRB_PRECONDITION_NOT_MET,
+              "A serious error has occurred here. Please set find_unused_parameters=True to traverse backward graph "
+              "in each step to prepare reduce in advance. (the previous backward did not mark every parameter ready)");
+  r->grad_need_hooks = true;
+  r->next_group = 0;
+  for (Group& g : r->groups) {
+    g.pending = (int64_t)g.vars.size();
+    g.has_unused = false;
+  }
+  std::fill(r->ready.begin(), r->ready.end(), 0);
+  std::fill(r->unused.begin(), r->unused.end(), 0);
+  r->unused_list.clear();
+  r->has_marked_unused = false;
+  r->finalized = false;
+  r->launched.clear();
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_set_unused_vars(PRB_Reducer* r, const int64_t* var_indices, int64_t num) {
+  PRB_ENFORCE(r && (var_indices || num == 0), PRB_INVALID_ARGUMENT, "reducer: bad arguments");
+  PRB_ENFORCE(r->find_unused || num == 0, PRB_PRECONDITION_NOT_MET,
+              "unused parameters were reported but the reducer was built with find_unused_parameters=False");
+  for (int64_t i = 0; i < num; ++i) {
+    const int64_t v = var_indices[i];
+    PRB_ENFORCE(v >= 0 && v < (int64_t)r->grads.size(), PRB_OUT_OF_RANGE, "Out of bounds variable index %lld", (long long)v);
+    if (!r->unused[(size_t)v]) {
+      r->unused[(size_t)v] = 1;
+      r->unused_list.push_back(v);
+      r->groups[(size_t)r->locator[(size_t)v].first].has_unused = true;
+    }
+  }
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_mark_var_ready(PRB_Reducer* r, int64_t v, void* stream) {
+  PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  // ref: AddDistHook reducer.cc:730-772
+  PRB_ENFORCE(v >= 0 && v < (int64_t)r->locator.size(), PRB_OUT_OF_RANGE,
+              "Out of bounds variable index. it must be less than %zu, but it is %lld", r->locator.size(), (long long)v);
+  if (!r->grad_need_hooks) return PRB_SUCCESS;  // no_sync / already finalized: nothing to synchronise
+  if (!r->has_marked_unused) {
+    r->has_marked_unused = true;
+    for (int64_t u : r->unused_list) PRB_TRY(mark_var_ready_impl(r, u, false, (cudaStream_t)stream));
+  }
+  return mark_var_ready_impl(r, v, true, (cudaStream_t)stream);
+}
+
+int32_t prb_reducer_mark_vars_ready(PRB_Reducer* r, const int64_t* var_indices, int64_t num, void* stream) {
+  for (int64_t i = 0; i < num; ++i) PRB_TRY(prb_reducer_mark_var_ready(r, var_indices[i], stream));
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_set_unpack(PRB_Reducer* r, int32_t enabled) {
+  PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  r->unpack = enabled != 0;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_is_finalized(const PRB_Reducer* r) { return r && r->finalized ? 1 : 0; }
+
+int32_t prb_reducer_bucket_view(const PRB_Reducer* r, int64_t v, PRB_Tensor* out) {
+  PRB_ENFORCE(r && out, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
+  PRB_ENFORCE(v >= 0 && v < (int64_t)r->locator.size(), PRB_OUT_OF_RANGE, "Out of bounds variable index %lld", (long long)v);
+  const Group& g = r->groups[(size_t)r->locator[(size_t)v].first];
+  const size_t s = (size_t)r->locator[(size_t)v].second;
+  out->data = r->arena + g.arena_off + (size_t)g.slot_off[s] * dtype_size(g.dtype);
+  out->numel = r->grads[(size_t)v].numel;
+  out->dtype = g.dtype;
+  out->device = r->grads[(size_t)v].device;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_launched_groups(const PRB_Reducer* r, int64_t* out_order, int64_t capacity, int64_t* out_num) {
+  PRB_ENFORCE(r && out_num, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
+  *out_num = (int64_t)r->launched.size();
+  for (int64_t i = 0; i < capacity && i < (int64_t)r->launched.size(); ++i) out_order[i] = r->launched[(size_t)i];
+  return PRB_SUCCESS;
+}
+
+}  // extern "C"

@@ -1,0 +1,250 @@
+// Error state, workspace, and the thin CUDA-runtime wrappers the torch-free Python host uses.
+#include <mutex>
+#include <unordered_map>
+#include <vector>
+
+#include "prb_common.cuh"
+
+namespace prb {
+
+static thread_local std::string t_last_error;
+std::atomic<int64_t> g_launch_count{0};
+
+void set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  t_last_error = buf;
+}
+
+int32_t require_device() {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    PRB_FAIL(PRB_EXTERNAL,
+             "no usable CUDA device (%s); paddle_ray_b200 has no CPU fallback",
+             e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  }
+  return PRB_SUCCESS;
+}
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+namespace {
+struct Slot {
+  void* ptr = nullptr;
+  size_t bytes = 0;
+};
+std::mutex g_ws_mu;
+std::unordered_map<int, std::vector<Slot>> g_ws;    // device -> slots
+std::vector<Slot> g_host_ws;
+}  // namespace
+
+int32_t workspace(size_t bytes, void** out, int slot) {
+  int dev = 0;
+  PRB_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_ws_mu);
+  auto& slots = g_ws[dev];
+  if ((int)slots.size() <= slot) slots.resize(slot + 1);
+  Slot& s = slots[slot];
+  if (s.bytes < bytes) {
+    if (s.ptr) PRB_CUDA(cudaFree(s.ptr));  // implicit device sync: nothing in flight still uses it
+    s.ptr = nullptr;
+    s.bytes = 0;
+    size_t want = bytes < 4096 ? 4096 : bytes + bytes / 4;
+    PRB_CUDA(cudaMalloc(&s.ptr, want));
+    s.bytes = want;
+  }
+  *out = s.ptr;
+  return PRB_SUCCESS;
+}
+
+int32_t host_staging(size_t bytes, void** out, int slot) {
+  std::lock_guard<std::mutex> lk(g_ws_mu);
+  if ((int)g_host_ws.size() <= slot) g_host_ws.resize(slot + 1);
+  Slot& s = g_host_ws[slot];
+  if (s.bytes < bytes) {
+    if (s.ptr) PRB_CUDA(cudaFreeHost(s.ptr));
+    s.ptr = nullptr;
+    s.bytes = 0;
+    size_t want = bytes < 4096 ? 4096 : bytes + bytes / 4;
+    PRB_CUDA(cudaMallocHost(&s.ptr, want));
+    s.bytes = want;
+  }
+  *out = s.ptr;
+  return PRB_SUCCESS;
+}
+
+__global__ void spin_kernel(long long cycles) {
+  const long long t0 = clock64();
+  while (clock64() - t0 < cycles) {
+  }
+}
+
+__global__ void flush_kernel(float4* buf, size_t n) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    buf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+}  // namespace prb
+
+using namespace prb;
+
+extern "C" {
+
+const char* prb_last_error_message(void) { return t_last_error.c_str(); }
+const char* prb_version(void) { return "paddle_ray_b200 0.1 (sm_100a)"; }
+
+int32_t prb_device_count(int32_t* out) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  *out = n;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_set_device(int32_t device) {
+  PRB_TRY(require_device());
+  PRB_CUDA(cudaSetDevice(device));
+  return PRB_SUCCESS;
+}
+
+int32_t prb_device_info(int32_t device, int32_t* sm, int64_t* l2_bytes, int64_t* total_mem, char name[128]) {
+  PRB_TRY(require_device());
+  cudaDeviceProp p;
+  PRB_CUDA(cudaGetDeviceProperties(&p, device));
+  if (sm) *sm = p.multiProcessorCount;
+  if (l2_bytes) *l2_bytes = p.l2CacheSize;
+  if (total_mem) *total_mem = (int64_t)p.totalGlobalMem;
+  if (name) snprintf(name, 128, "%s", p.name);
+  return PRB_SUCCESS;
+}
+
+int32_t prb_malloc(int64_t bytes, void** out) {
+  PRB_TRY(require_device());
+  PRB_ENFORCE(bytes >= 0, PRB_INVALID_ARGUMENT, "prb_malloc: negative size");
+  *out = nullptr;
+  if (bytes == 0) bytes = 256;  // keep zero-length tensors addressable
+  PRB_CUDA(cudaMalloc(out, (size_t)bytes));
+  return PRB_SUCCESS;
+}
+int32_t prb_free(void* ptr) {
+  if (ptr) PRB_CUDA(cudaFree(ptr));
+  return PRB_SUCCESS;
+}
+int32_t prb_host_alloc(int64_t bytes, void** out) {
+  PRB_TRY(require_device());
+  *out = nullptr;
+  PRB_CUDA(cudaMallocHost(out, (size_t)(bytes > 0 ? bytes : 1)));
+  return PRB_SUCCESS;
+}
+int32_t prb_host_free(void* ptr) {
+  if (ptr) PRB_CUDA(cudaFreeHost(ptr));
+  return PRB_SUCCESS;
+}
+int32_t prb_memcpy_h2d(void* dst, const void* src, int64_t bytes, void* stream) {
+  if (bytes > 0) PRB_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+int32_t prb_memcpy_d2h(void* dst, const void* src, int64_t bytes, void* stream) {
+  if (bytes > 0) PRB_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+int32_t prb_memcpy_d2d(void* dst, const void* src, int64_t bytes, void* stream) {
+  if (bytes > 0) PRB_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+int32_t prb_memset(void* dst, int32_t value, int64_t bytes, void* stream) {
+  if (bytes > 0) PRB_CUDA(cudaMemsetAsync(dst, value, (size_t)bytes, (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+int32_t prb_stream_create(int32_t high_priority, void** out) {
+  PRB_TRY(require_device());
+  cudaStream_t s;
+  int lo = 0, hi = 0;
+  PRB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  PRB_CUDA(cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, high_priority ? hi : lo));
+  *out = (void*)s;
+  return PRB_SUCCESS;
+}
+int32_t prb_stream_destroy(void* stream) {
+  PRB_CUDA(cudaStreamDestroy((cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+int32_t prb_stream_synchronize(void* stream) {
+  PRB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+int32_t prb_device_synchronize(void) {
+  PRB_CUDA(cudaDeviceSynchronize());
+  return PRB_SUCCESS;
+}
+int32_t prb_event_create(void** out) {
+  PRB_TRY(require_device());
+  cudaEvent_t e;
+  PRB_CUDA(cudaEventCreate(&e));
+  *out = (void*)e;
+  return PRB_SUCCESS;
+}
+int32_t prb_event_destroy(void* event) {
+  PRB_CUDA(cudaEventDestroy((cudaEvent_t)event));
+  return PRB_SUCCESS;
+}
+int32_t prb_event_record(void* event, void* stream) {
+  PRB_CUDA(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+int32_t prb_event_synchronize(void* event) {
+  PRB_CUDA(cudaEventSynchronize((cudaEvent_t)event));
+  return PRB_SUCCESS;
+}
+int32_t prb_event_elapsed_ms(void* start, void* stop, float* out_ms) {
+  PRB_CUDA(cudaEventElapsedTime(out_ms, (cudaEvent_t)start, (cudaEvent_t)stop));
+  return PRB_SUCCESS;
+}
+int32_t prb_stream_wait_event(void* stream, void* event) {
+  PRB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0));
+  return PRB_SUCCESS;
+}
+
+int32_t prb_spin(int64_t microseconds, void* stream) {
+  PRB_TRY(require_device());
+  int dev = 0, khz = 0;
+  PRB_CUDA(cudaGetDevice(&dev));
+  PRB_CUDA(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
+  long long cycles = (long long)microseconds * (long long)khz / 1000;
+  spin_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(cycles);
+  PRB_CUDA(cudaGetLastError());  // bench scaffolding: not counted as a hot-path launch
+  return PRB_SUCCESS;
+}
+
+int32_t prb_flush_l2(void* stream) {
+  PRB_TRY(require_device());
+  const size_t bytes = (size_t)256 << 20;  // 256 MiB > 126 MB L2
+  void* buf = nullptr;
+  PRB_TRY(workspace(bytes, &buf, /*slot=*/7));
+  flush_kernel<<<sm_count() * 8, 256, 0, (cudaStream_t)stream>>>((float4*)buf, bytes / sizeof(float4));
+  PRB_CUDA(cudaGetLastError());  // bench scaffolding: not counted as a hot-path launch
+  return PRB_SUCCESS;
+}
+
+int64_t prb_launch_count(void) { return g_launch_count.load(); }
+
+}  // extern "C"
