@@ -261,13 +261,15 @@ typedef struct PRB_TailConfig {
   float clip_norm;
   int32_t auto_skip_clip;
   int32_t use_mp_type;       /* clip norm in fp32 for 16-bit grads (ref: clip.py:179-202) */
-  int32_t write_back_grads;  /* 1: store the unscaled/clipped gradient back (reference-visible grads) */
+  int32_t write_back_grads;  /* 1: store the unscaled (not clipped) gradient back: what p.grad holds in the reference */
   int32_t zero_grads;        /* 1: clear_grad(set_to_zero=True) folded in (ref: optimizer.py:1333-1381) */
 } PRB_TailConfig;
 
 /* Per-tensor attributes follow adamw_: lr_ratio[i], with_decay[i] (NULL = 1.0 / all decayed).
- * found_inf (bool, device), global_norm/clip (fp32, device) are outputs (optional except found_inf
- * when use_amp).  beta-pows live on the device and are advanced on the device unless found_inf. */
+ * found_inf (bool, device): with use_amp it is cleared, then set by the inf/nan check (output); with
+ * use_amp == 0 a non-NULL found_inf is an input-only skip flag (the caller unscaled earlier).
+ * global_norm/clip (fp32, device) are optional outputs.  beta-pows live on the device and are
+ * advanced on the device unless found_inf. */
 int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor* params, PRB_Tensor* grads,
                          const PRB_Tensor* learning_rate, const PRB_Tensor* moments1,
                          const PRB_Tensor* moments2, PRB_Tensor* beta1_pow, PRB_Tensor* beta2_pow,
@@ -302,6 +304,9 @@ int32_t prb_event_record(void* event, void* stream);
 int32_t prb_event_synchronize(void* event);
 int32_t prb_event_elapsed_ms(void* start, void* stop, float* out_ms);
 int32_t prb_stream_wait_event(void* stream, void* event);
+/* *dst = *dst || *src for two device bools (the bitwise_or the reference's AmpScaler applies to its
+ * per-dtype found_inf flags, ref: python/paddle/amp/grad_scaler.py:373-396). */
+int32_t prb_flag_or(void* dst, const void* src, void* stream);
 /* Busy kernel of roughly `microseconds` on `stream` (synthetic backward producer for overlap runs). */
 int32_t prb_spin(int64_t microseconds, void* stream);
 /* Writes `bytes` of scratch to evict L2 between timed iterations. */

@@ -181,10 +181,12 @@ def global_norm_clip(grads, dtypes, clip_norm: float, auto_skip_clip: bool = Fal
     order unspecified, so callers compare with tolerance.
     """
     s16, s32 = [], []
+    dt16 = None
     for g, dt in zip(grads, dtypes):
         v, v64 = squared_l2_norm(g, dt, mp=mp)
         if dt in (F16, BF16) and not mp:
             s16.append(v)
+            dt16 = dt
         else:
             s32.append(v64 if dt == F32 or mp else v)
     parts = []
@@ -192,6 +194,8 @@ def global_norm_clip(grads, dtypes, clip_norm: float, auto_skip_clip: bool = Fal
         acc = np.float32(0)
         for v in s16:
             acc = np.float32(acc + np.float32(v))
+        # add_n of T-typed scalars yields a T-typed scalar (accumulated in float), then astype(fp32)
+        acc = to_f32(from_f32(np.array([acc], np.float32), dt16), dt16)[0]
         parts.append(np.float32(acc))
     if s32:
         parts.append(np.float32(np.sum(np.array(s32, dtype=np.float64))))

@@ -8,4 +8,7 @@ from . import _lib  # noqa: F401  (raises ImportError if the shared library is n
 from . import _C_ops, core  # noqa: F401
 from .core import Event, PinnedBuffer, Stream, Tensor, current_stream, device_count, set_device, synchronize  # noqa: F401
 
+from . import amp, distributed, nn, optimizer  # noqa: F401,E402
+from .distributed import DataParallel  # noqa: F401,E402
+
 __version__ = "0.1"

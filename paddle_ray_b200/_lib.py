@@ -108,6 +108,7 @@ SIGNATURES = {
     "prb_event_synchronize": [_vp],
     "prb_event_elapsed_ms": [_vp, _vp, C.POINTER(_f32)],
     "prb_stream_wait_event": [_vp, _vp],
+    "prb_flag_or": [_vp, _vp, _vp],
     "prb_spin": [_i64, _vp],
     "prb_flush_l2": [_vp],
     "prb_launch_count": [],

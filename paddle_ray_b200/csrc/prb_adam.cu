@@ -25,13 +25,17 @@ struct Coef {
   bool use_decay, amp, clipon;
 };
 
+// AMP unscale, in place in the reference: out = T(MT(x) * inv)   (ref amp_kernel.cu:66-68).
+// This is the value a reference user sees in p.grad after the step.
 template <typename TG>
-__device__ __forceinline__ float xform_grad(float g, const Coef& k) {
-  // AMP unscale: out = T(MT(x) * inv)            (ref amp_kernel.cu:66-68)
-  if (k.amp) g = round_through<TG>(__fmul_rn(g, k.inv));
-  // clip: g * clip.astype(g.dtype), computed in T (ref python/paddle/nn/clip.py:715-732)
-  if (k.clipon) g = round_through<TG>(__fmul_rn(g, k.clip));
-  return g;
+__device__ __forceinline__ float unscale_grad(float g, const Coef& k) {
+  return k.amp ? round_through<TG>(__fmul_rn(g, k.inv)) : g;
+}
+// Global-norm clip: new_grad = g * clip.astype(g.dtype), computed in T, a NEW tensor in the
+// reference (ref python/paddle/nn/clip.py:715-732) -- it feeds the optimizer but never replaces p.grad.
+template <typename TG>
+__device__ __forceinline__ float clip_grad(float g, const Coef& k) {
+  return k.clipon ? round_through<TG>(__fmul_rn(g, k.clip)) : g;
 }
 
 __device__ __forceinline__ void adam_elem(float& p, float g, float& m1, float& m2, const Coef& k) {
@@ -122,11 +126,11 @@ __global__ void __launch_bounds__(kAdamThreads) adam_chunks_kernel(const AdamArg
 #pragma unroll
         for (int j = 0; j < kVec; ++j) {
           float p = kMaster ? mpv[u].v[j] : Conv<T>::to_f32(pv[u].v[j]);
-          const float g = xform_grad<TG>(Conv<TG>::to_f32(gv[u].v[j]), k);
-          adam_elem(p, g, m1v[u].v[j], m2v[u].v[j], k);
+          const float gu = unscale_grad<TG>(Conv<TG>::to_f32(gv[u].v[j]), k);
+          adam_elem(p, clip_grad<TG>(gu, k), m1v[u].v[j], m2v[u].v[j], k);
           po.v[j] = Conv<T>::from_f32(p);
           if (kMaster) mpv[u].v[j] = p;
-          go.v[j] = a.zero_grad ? Conv<TG>::from_f32(0.0f) : Conv<TG>::from_f32(g);
+          go.v[j] = a.zero_grad ? Conv<TG>::from_f32(0.0f) : Conv<TG>::from_f32(gu);
         }
         store_vec<float>(m1_ptr + e, m1v[u]);
         store_vec<float>(m2_ptr + e, m2v[u]);
@@ -140,9 +144,9 @@ __global__ void __launch_bounds__(kAdamThreads) adam_chunks_kernel(const AdamArg
     const int e = nvec * kVec + threadIdx.x;
     if (e < n) {
       float p = kMaster ? mp_ptr[e] : Conv<T>::to_f32(p_ptr[e]);
-      const float g = xform_grad<TG>(Conv<TG>::to_f32(g_ptr[e]), k);
+      const float g = unscale_grad<TG>(Conv<TG>::to_f32(g_ptr[e]), k);
       float m1 = m1_ptr[e], m2 = m2_ptr[e];
-      adam_elem(p, g, m1, m2, k);
+      adam_elem(p, clip_grad<TG>(g, k), m1, m2, k);
       m1_ptr[e] = m1;
       m2_ptr[e] = m2;
       p_ptr[e] = Conv<T>::from_f32(p);
@@ -156,9 +160,9 @@ __global__ void __launch_bounds__(kAdamThreads) adam_chunks_kernel(const AdamArg
     const Coef k = make_coef<TG>(d, a);
     for (int e = threadIdx.x; e < n; e += kAdamThreads) {
       float p = kMaster ? mp_ptr[e] : Conv<T>::to_f32(p_ptr[e]);
-      const float g = xform_grad<TG>(Conv<TG>::to_f32(g_ptr[e]), k);
+      const float g = unscale_grad<TG>(Conv<TG>::to_f32(g_ptr[e]), k);
       float m1 = m1_ptr[e], m2 = m2_ptr[e];
-      adam_elem(p, g, m1, m2, k);
+      adam_elem(p, clip_grad<TG>(g, k), m1, m2, k);
       m1_ptr[e] = m1;
       m2_ptr[e] = m2;
       p_ptr[e] = Conv<T>::from_f32(p);

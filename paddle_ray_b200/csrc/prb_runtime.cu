@@ -94,6 +94,10 @@ __global__ void spin_kernel(long long cycles) {
   }
 }
 
+__global__ void flag_or_kernel(bool* dst, const bool* src) {
+  if (*src) *dst = true;
+}
+
 __global__ void flush_kernel(float4* buf, size_t n) {
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
@@ -221,6 +225,14 @@ int32_t prb_event_elapsed_ms(void* start, void* stop, float* out_ms) {
 }
 int32_t prb_stream_wait_event(void* stream, void* event) {
   PRB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)event, 0));
+  return PRB_SUCCESS;
+}
+
+int32_t prb_flag_or(void* dst, const void* src, void* stream) {
+  PRB_TRY(require_device());
+  PRB_ENFORCE(dst && src, PRB_INVALID_ARGUMENT, "flag_or: NULL flag");
+  flag_or_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((bool*)dst, (const bool*)src);
+  PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 

@@ -84,7 +84,11 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   }
 
   const float* ls = cfg->use_amp ? reinterpret_cast<const float*>(loss_scale->data) : nullptr;
-  bool* found = cfg->use_amp ? reinterpret_cast<bool*>(found_inf->data) : nullptr;
+  // use_amp: cleared here, set by the check.  Otherwise a non-NULL flag is an input-only skip flag.
+  bool* found = found_inf ? reinterpret_cast<bool*>(found_inf->data) : nullptr;
+  if (found_inf)
+    PRB_ENFORCE(found_inf->numel == 1 && found_inf->dtype == PRB_BOOL && found_inf->device >= 0, PRB_INVALID_ARGUMENT,
+                "dp_step_tail: found_inf must be one bool on the device");
   const float* clip_dev = nullptr;
 
   if (cfg->use_amp) PRB_CUDA(cudaMemsetAsync(found, 0, 1, stream));
@@ -100,7 +104,8 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
       scratch_clip = partials + gt.nchunks + num;
     }
     const bool mp = cfg->use_mp_type != 0;
-    PRB_TRY(launch_grad_pass(dt_g, gt, /*write=*/false, /*norm=*/cfg->use_clip != 0, mp, ls, found, partials, stream));
+    PRB_TRY(launch_grad_pass(dt_g, gt, /*write=*/false, /*norm=*/cfg->use_clip != 0, mp, ls, cfg->use_amp ? found : nullptr,
+                             partials, stream));
     if (cfg->use_clip) {
       NormFinalizeArgs a{};
       a.ngroups = 1;

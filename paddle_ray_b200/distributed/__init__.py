@@ -1,0 +1,3 @@
+from .parallel import (DataParallel, EagerReducer, Group, ParallelEnv, assign_group_by_size, get_group, get_rank,  # noqa: F401
+                       get_world_size, init_parallel_env, sync_params_buffers)
+from .store import FileStore, TCPStore  # noqa: F401

@@ -1,0 +1,331 @@
+"""``init_parallel_env`` / ``DataParallel`` -- the host side of the gradient-bucket path.
+
+ref: python/paddle/distributed/parallel.py:202-561 (DataParallel), :921-1211 (init_parallel_env),
+     paddle/fluid/pybind/distributed_py.cc:64-77,1285-1315 (eager_assign_group_by_size, EagerReducer).
+
+The reference wraps a ``Layer`` and hangs reduce hooks on the autograd engine.  Model code and
+autograd are out of scope here, so ``DataParallel`` wraps the *parameter list*; the producer of
+gradients calls ``mark_var_ready(i)`` (the hook equivalent) as each gradient lands.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import tempfile
+import warnings
+
+import numpy as np
+
+from .. import _lib, core
+from .._lib import call, lib, tensor_array
+from ..core import Tensor
+from .store import FileStore, TCPStore
+
+
+class ParallelEnv:
+    """Rank / world size / endpoints from the environment.
+
+    Honours the reference's names (PADDLE_TRAINER_ID, PADDLE_TRAINERS_NUM, PADDLE_MASTER,
+    FLAGS_selected_gpus; parallel.py:1030-1083) and, when those are absent, the torchrun names
+    (RANK, WORLD_SIZE, LOCAL_RANK, MASTER_ADDR, MASTER_PORT).
+    """
+
+    def __init__(self):
+        env = os.environ
+        self.rank = int(env.get("PADDLE_TRAINER_ID", env.get("RANK", "0")))
+        self.world_size = int(env.get("PADDLE_TRAINERS_NUM", env.get("WORLD_SIZE", "1")))
+        sel = env.get("FLAGS_selected_gpus")
+        self.device_id = int(sel.split(",")[0]) if sel else int(env.get("LOCAL_RANK", str(self.rank)))
+        master = env.get("PADDLE_MASTER")
+        if master:
+            host, port = master.rsplit(":", 1)
+        else:
+            host, port = env.get("MASTER_ADDR", "127.0.0.1"), env.get("MASTER_PORT", "6170")
+        self.master_addr, self.master_port = host, int(port)
+        self.under_torchrun = "TORCHELASTIC_RUN_ID" in env or ("LOCAL_RANK" in env and "PADDLE_TRAINER_ID" not in env)
+
+    @property
+    def nranks(self):
+        return self.world_size
+
+    @property
+    def local_rank(self):
+        return self.rank
+
+
+class Group:
+    """A communicator handle (``paddle.distributed.collective.Group`` + its ProcessGroupNCCL)."""
+
+    def __init__(self, handle, rank, nranks, device):
+        self.handle = handle
+        self.rank = rank
+        self.nranks = nranks
+        self.device = device
+        self.comm_stream = core.Stream(handle=lib.prb_comm_stream(handle))
+
+    @property
+    def world_size(self):
+        return self.nranks
+
+    def all_reduce(self, tensor: Tensor, op: str = "sum", stream=None) -> Tensor:
+        p = tensor.prb
+        call("prb_comm_all_reduce", self.handle, C.byref(p), C.byref(p), {"sum": 0, "max": 1}[op],
+             core._stream_handle(stream))
+        return tensor
+
+    def broadcast(self, tensor: Tensor, src: int = 0, stream=None) -> Tensor:
+        p = tensor.prb
+        call("prb_comm_broadcast", self.handle, C.byref(p), int(src), core._stream_handle(stream))
+        return tensor
+
+    def barrier(self):
+        t = Tensor.zeros(1, "float32", self.device)
+        self.all_reduce(t)
+        core.current_stream().synchronize()
+
+    def __del__(self):
+        try:
+            lib.prb_comm_destroy(self.handle)
+        except Exception:
+            pass
+
+
+_default_group: Group | None = None
+
+
+def init_parallel_env(store=None) -> Group:
+    """Create the default communicator.  ref: parallel.py:921-1211, process_group_nccl.cc:559-571.
+
+    Rank 0 creates the NCCL unique id and publishes it under the reference's key; peers fetch it.
+    ``store`` may be any object with ``set(key, bytes)`` / ``get(key) -> bytes``.
+    """
+    global _default_group
+    env = ParallelEnv()
+    core.set_device(env.device_id)
+    h = C.c_void_p()
+    if env.world_size == 1:
+        call("prb_comm_init_single", env.device_id, C.byref(h))
+    else:
+        if store is None:
+            if env.under_torchrun:
+                # the launcher owns MASTER_PORT; all workers share the agent as parent process
+                path = os.path.join(tempfile.gettempdir(), "prb_store_%d_%d" % (os.getppid(), env.master_port))
+                store = FileStore(path)
+            else:
+                store = TCPStore(env.master_addr, env.master_port, env.rank == 0, env.world_size)
+        key = "ProcessGroupNCCL/nccl_ids/0/0"
+        uid = (C.c_uint8 * _lib.UNIQUE_ID_BYTES)()
+        if env.rank == 0:
+            call("prb_comm_get_unique_id", uid)
+            store.set(key, bytes(uid))
+        else:
+            raw = store.get(key)
+            C.memmove(uid, raw, _lib.UNIQUE_ID_BYTES)
+        call("prb_comm_init_rank", uid, env.world_size, env.rank, env.device_id, C.byref(h))
+    _default_group = Group(h.value, env.rank, env.world_size, env.device_id)
+    return _default_group
+
+
+def get_group() -> Group | None:
+    return _default_group
+
+
+def get_rank() -> int:
+    return _default_group.rank if _default_group else ParallelEnv().rank
+
+
+def get_world_size() -> int:
+    return _default_group.nranks if _default_group else ParallelEnv().world_size
+
+
+def assign_group_by_size(tensors, is_sparse_gradient, group_size_limits=(25 * 1024 * 1024,), tensor_indices=()):
+    """``core.eager_assign_group_by_size`` (ref distributed_py.cc:64-77, reducer.cc:45-156).
+
+    ``tensors``: objects with ``numel`` and ``dtype`` (PRB dtype code).  Pure host logic: runs
+    without a GPU.
+    """
+    n = len(tensors)
+    if len(is_sparse_gradient) != n:  # ref reducer.cc:50-57
+        raise _lib.PRBError(2, "tensors len must be equal to is_sparse_gradient len, but [%d] != [%d]"
+                            % (n, len(is_sparse_gradient)))
+    numels = (C.c_int64 * max(n, 1))(*[int(t.numel) for t in tensors])
+    dtypes = (C.c_int32 * max(n, 1))(*[int(core.dtype_code(t.dtype)) for t in tensors])
+    sparse = (C.c_uint8 * max(n, 1))(*[1 if s else 0 for s in is_sparse_gradient])
+    limits = (C.c_uint64 * len(group_size_limits))(*[int(x) for x in group_size_limits])
+    ti = (C.c_int64 * max(len(tensor_indices), 1))(*[int(x) for x in tensor_indices])
+    flat = (C.c_int64 * max(n, 1))()
+    sizes = (C.c_int64 * max(n, 1))()
+    ng = C.c_int64()
+    call("prb_assign_group_by_size", numels, dtypes, sparse, n, limits, len(group_size_limits), ti,
+         len(tensor_indices), flat, sizes, C.byref(ng))
+    out, k = [], 0
+    for g in range(ng.value):
+        out.append([int(flat[k + j]) for j in range(sizes[g])])
+        k += sizes[g]
+    return out
+
+
+class EagerReducer:
+    """``core.EagerReducer(tensors, group_indices, is_sparse, process_group, limits, find_unused)``.
+
+    ref: reducer.h:88-142, distributed_py.cc:1285-1315.  ``process_group=None`` builds the
+    host-only state machine (no device work), which is what CPU tests drive.
+    """
+
+    def __init__(self, grads, group_indices, is_sparse_gradient, process_group, group_size_limits=None,
+                 find_unused_parameters=False):
+        if any(is_sparse_gradient):
+            raise _lib.PRBError(4, "sparse (SelectedRows) gradients are out of scope (SURVEY.md 8f-4)")
+        self._grads = list(grads)
+        flat = [v for g in group_indices for v in g]
+        sizes = [len(g) for g in group_indices]
+        self._flat = (C.c_int64 * max(len(flat), 1))(*flat)
+        self._sizes = (C.c_int64 * max(len(sizes), 1))(*sizes)
+        h = C.c_void_p()
+        call("prb_reducer_create", tensor_array(self._grads), len(self._grads), self._flat, self._sizes, len(sizes),
+             process_group.handle if process_group is not None else None, int(bool(find_unused_parameters)), C.byref(h))
+        self.handle = h.value
+        self.group_indices = [list(g) for g in group_indices]
+        self._group = process_group
+
+    def prepare_for_backward(self, unused_vars=()):
+        call("prb_reducer_prepare_for_backward", self.handle)
+        if len(unused_vars):
+            arr = (C.c_int64 * len(unused_vars))(*[int(v) for v in unused_vars])
+            call("prb_reducer_set_unused_vars", self.handle, arr, len(unused_vars))
+
+    def mark_var_ready(self, var_index: int, stream=None):
+        call("prb_reducer_mark_var_ready", self.handle, int(var_index),
+             core._stream_handle(stream) if self._group is not None else None)
+
+    def mark_vars_ready(self, var_indices, stream=None):
+        arr = var_indices if isinstance(var_indices, C.Array) else (C.c_int64 * len(var_indices))(*var_indices)
+        call("prb_reducer_mark_vars_ready", self.handle, arr, len(arr),
+             core._stream_handle(stream) if self._group is not None else None)
+
+    def set_unpack(self, enabled: bool):
+        call("prb_reducer_set_unpack", self.handle, int(bool(enabled)))
+
+    @property
+    def finalized(self) -> bool:
+        return bool(lib.prb_reducer_is_finalized(self.handle))
+
+    def launched_groups(self):
+        cap = len(self.group_indices)
+        out = (C.c_int64 * max(cap, 1))()
+        n = C.c_int64()
+        call("prb_reducer_launched_groups", self.handle, out, cap, C.byref(n))
+        return [int(out[i]) for i in range(n.value)]
+
+    def bucket_view(self, var_index: int) -> Tensor:
+        p = _lib.PRBTensor()
+        call("prb_reducer_bucket_view", self.handle, int(var_index), C.byref(p))
+        return Tensor(p.numel, p.dtype, p.device, data_ptr=p.data, owner=self)
+
+    def __del__(self):
+        try:
+            lib.prb_reducer_destroy(self.handle)
+        except Exception:
+            pass
+
+
+def sync_params_buffers(parameters, group: Group, src_rank: int = 0):
+    """Broadcast every parameter from ``src_rank`` at start-up (ref parallel.py:156-199)."""
+    if group is None or group.nranks == 1:
+        return
+    for p in parameters:
+        group.broadcast(p, src_rank)
+    core.current_stream().synchronize()
+
+
+class DataParallel:
+    """``paddle.DataParallel`` over a parameter list.
+
+    Same constructor knobs and defaults as the reference (parallel.py:363-371): 25 MB buckets, a
+    1 MB bucket for the parameters whose gradients arrive last, group order reversed so that the
+    first gradients produced by backward fill group 0 (:478-491).
+
+    Per step::
+
+        dp.prepare_for_backward()          # what DataParallel.forward does (:548-561)
+        ... for each gradient as it is produced:  dp.mark_var_ready(i)
+        # when the last group has been launched the reducer finalises on its own
+
+    ``consume_from_buckets=True`` keeps the reduced gradients in the bucket arena (no split back);
+    ``dp.bucket_grads()`` then yields the views the optimizer reads directly.
+    """
+
+    def __init__(self, parameters, strategy=None, comm_buffer_size=25, last_comm_buffer_size=1,
+                 find_unused_parameters=False, group=None, consume_from_buckets=False):
+        self._parameters = [p for p in parameters if not getattr(p, "stop_gradient", False)]
+        assert len(self._parameters) > 0, (
+            "This model does not have any parameters to train, and does not need to use DataParallel")
+        self.find_unused_parameters = find_unused_parameters
+        self.grad_need_sync = True
+        self.group = group if group is not None else _default_group
+        if self.group is None:
+            warnings.warn("init_parallel_env() was not called: falling back to a single-rank communicator.")
+            self.group = init_parallel_env()
+        for p in self._parameters:
+            if p.grad is None:
+                p.grad = Tensor.zeros(p.numel, p.dtype, p.device)
+        sync_params_buffers(self._parameters, self.group)
+        self.comm_buffer_size = int(comm_buffer_size * 1024 * 1024)
+        self.last_comm_buffer_size = int(last_comm_buffer_size * 1024 * 1024)
+        self.init_reducer()
+        self._consume = False
+        if consume_from_buckets:
+            self.consume_from_buckets(True)
+
+    def init_reducer(self):
+        is_sparse = [bool(getattr(p, "is_sparse_grad", False)) for p in self._parameters]
+        self.group_indices = assign_group_by_size(self._parameters, is_sparse,
+                                                  [self.last_comm_buffer_size, self.comm_buffer_size])
+        self._reducer = EagerReducer([p.grad for p in self._parameters], list(reversed(self.group_indices)), is_sparse,
+                                     self.group, [self.last_comm_buffer_size, self.comm_buffer_size],
+                                     self.find_unused_parameters)
+        # backward produces gradients in reverse parameter order
+        self._reverse_order = (C.c_int64 * len(self._parameters))(*reversed(range(len(self._parameters))))
+
+    def consume_from_buckets(self, enabled: bool = True):
+        self._consume = bool(enabled)
+        self._reducer.set_unpack(not self._consume)
+        self._bucket_grads = [self._reducer.bucket_view(i) for i in range(len(self._parameters))] if enabled else None
+
+    def bucket_grads(self):
+        return self._bucket_grads
+
+    def parameters(self):
+        return self._parameters
+
+    def prepare_for_backward(self, unused_vars=()):
+        if self.grad_need_sync:
+            self._reducer.prepare_for_backward(unused_vars)
+
+    def mark_var_ready(self, index: int, stream=None):
+        if self.grad_need_sync:
+            self._reducer.mark_var_ready(index, stream)
+
+    def mark_all_ready(self, stream=None):
+        """Every gradient is ready (a finished backward): hooks fire in reverse parameter order."""
+        if self.grad_need_sync:
+            self._reducer.mark_vars_ready(self._reverse_order, stream)
+
+    class _NoSync:
+        def __init__(self, dp):
+            self.dp = dp
+
+        def __enter__(self):
+            self.prev = self.dp.grad_need_sync
+            self.dp.grad_need_sync = False
+
+        def __exit__(self, *exc):
+            self.dp.grad_need_sync = self.prev
+
+    def no_sync(self):
+        """Gradient accumulation without communication (ref parallel.py:496-546)."""
+        return DataParallel._NoSync(self)
+
+    @property
+    def finalized(self) -> bool:
+        return self._reducer.finalized

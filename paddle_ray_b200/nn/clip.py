@@ -1,0 +1,57 @@
+"""``paddle.nn.ClipGradByGlobalNorm``.  ref: python/paddle/nn/clip.py:577-736."""
+from __future__ import annotations
+
+from .. import _C_ops
+from ..core import Tensor
+
+_clip_by_global_norm_using_mp_type_flag = False
+
+
+def _clip_by_global_norm_using_mp_type(*args):
+    """ref clip.py:179-192: get / set the flag that casts 16-bit gradients to fp32 for the norm."""
+    global _clip_by_global_norm_using_mp_type_flag
+    assert len(args) <= 1
+    if len(args) == 1:
+        assert isinstance(args[0], bool)
+        old = _clip_by_global_norm_using_mp_type_flag
+        _clip_by_global_norm_using_mp_type_flag = args[0]
+        return old
+    return _clip_by_global_norm_using_mp_type_flag
+
+
+class ClipGradBase:
+    def __call__(self, params_grads):
+        return self._dygraph_clip(params_grads)
+
+
+class ClipGradByGlobalNorm(ClipGradBase):
+    """t_list[i] = t_list[i] * clip_norm / max(global_norm, clip_norm)   (ref clip.py:577-642).
+
+    When handed to an optimizer of this package the clip runs fused inside the optimizer's two-pass
+    step (``prb_dp_step_tail``).  Calling it directly reproduces ``_dygraph_clip``: new gradient
+    tensors are returned, the originals are left untouched (ref :715-732).
+    """
+
+    def __init__(self, clip_norm, group_name="default_group", auto_skip_clip=False):
+        self.clip_norm = float(clip_norm)
+        self.group_name = group_name
+        assert isinstance(auto_skip_clip, bool)
+        self.auto_skip_clip = auto_skip_clip
+        self.last_global_norm: Tensor | None = None
+        self.last_clip: Tensor | None = None
+
+    def __str__(self):
+        return "Gradient Clip By GlobalNorm, global_norm=%f" % (self.clip_norm)
+
+    def _dygraph_clip(self, params_grads):
+        todo = [(p, g) for p, g in params_grads if g is not None and getattr(p, "need_clip", True) is not False]
+        if not todo:
+            return params_grads  # "all parameters have been filtered out" (ref :676-682)
+        new_grads = {}
+        for p, g in todo:
+            ng = Tensor(g.numel, g.dtype, g.device)
+            ng.copy_(g)
+            new_grads[id(p)] = ng
+        self.last_global_norm, self.last_clip = _C_ops.clip_grad_by_global_norm_(
+            list(new_grads.values()), self.clip_norm, self.auto_skip_clip, _clip_by_global_norm_using_mp_type())
+        return [(p, new_grads.get(id(p), g)) for p, g in params_grads]

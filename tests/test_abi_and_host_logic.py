@@ -1,0 +1,231 @@
+"""CPU-side checks: the C ABI exports what the header declares, host logic (bucket assignment, reducer
+state machine, stores) matches the oracle / the reference's literal vectors, and compute entry points
+fail loudly without a GPU instead of falling back."""
+import ctypes as C
+import json
+import os
+import re
+import threading
+
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def prb():
+    import paddle_ray_b200 as prb
+    return prb
+
+
+def test_library_exports_every_declared_symbol(prb):
+    header = open(os.path.join(ROOT, "include", "paddle_ray_b200.h")).read()
+    declared = set(re.findall(r"\b(prb_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) > 50
+    from paddle_ray_b200 import _lib
+    lib = C.CDLL(_lib.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(lib, name), "%s is declared in the header but not exported" % name
+    # and the ctypes binding covers all of them
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+
+
+def test_header_cites_the_reference_for_every_operator():
+    header = open(os.path.join(ROOT, "include", "paddle_ray_b200.h")).read()
+    for op in ("prb_adamw", "prb_adam", "prb_merged_adam", "prb_fused_adam", "prb_check_finite_and_unscale",
+               "prb_squared_l2_norm", "prb_scale", "prb_concat", "prb_assign_group_by_size", "prb_reducer_create",
+               "prb_comm_all_reduce", "prb_update_loss_scaling"):
+        idx = header.index("int32_t %s(" % op)
+        assert "ref:" in header[max(0, idx - 1500):idx], op
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidia0"), reason="GPU present")
+def test_no_cpu_fallback(prb):
+    from paddle_ray_b200._lib import PRBError
+    assert prb.device_count() == 0
+    host = prb.Tensor(16, "float32", device=-1)
+    one = prb.Tensor(1, "float32", device=-1)
+    with pytest.raises(PRBError, match="no CPU fallback"):
+        prb._C_ops.adamw_(host, host, one, host, host, one, one, None, None, 0.9, 0.999, 1e-8, 1.0, 0.01, True)
+    with pytest.raises(PRBError, match="no CPU fallback"):
+        prb._C_ops.scale_(host, 0.5)
+    with pytest.raises(PRBError, match="no CPU fallback"):
+        prb.Tensor(16, "float32", device=0)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "paddle_ray_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in text.replace("oracle/dp_tail_oracle.c", "").replace("the CPU oracle", "") \
+                    .replace("(oracle/", "("), f
+
+
+class _T:
+    def __init__(self, numel, dtype):
+        self.numel, self.dtype = numel, dtype
+
+
+def test_assign_group_by_size_golden(prb, golden_dir):
+    names = {"float32": orc.F32, "float64": orc.F64, "float16": orc.F16, "bfloat16": orc.BF16}
+    cases = json.load(open(os.path.join(golden_dir, "bucket_cases.json")))
+    for c in cases:
+        ts = [_T(int(np.prod(s)), names[d]) for s, d in zip(c["shapes"], c["dtypes"])]
+        got = prb.distributed.assign_group_by_size(ts, c["is_sparse"], c["limits"], c["tensor_indices"])
+        assert got == c["expected"], c["name"]
+
+
+def test_assign_group_by_size_random_vs_oracle(prb):
+    rng = np.random.default_rng(0)
+    for trial in range(200):
+        n = int(rng.integers(1, 40))
+        numels = [int(x) for x in rng.integers(1, 5000, n)]
+        dts = [int(rng.choice([orc.F32, orc.BF16, orc.F16, orc.F64])) for _ in range(n)]
+        sparse = [bool(rng.random() < 0.1) for _ in range(n)]
+        limits = [int(x) for x in rng.integers(0, 20000, int(rng.integers(1, 4)))]
+        ti = [int(x) for x in rng.permutation(n)] if trial % 3 == 0 else []
+        want = orc.assign_group_by_size(numels, dts, sparse, limits, ti)
+        got = prb.distributed.assign_group_by_size([_T(a, b) for a, b in zip(numels, dts)], sparse, limits, ti)
+        assert got == want
+
+
+def test_assign_group_by_size_model_configs(prb):
+    """ResNet-50 fp32 -> 1 MiB first bucket then 25 MiB buckets; a bucket may overshoot by one tensor."""
+    from bench_configs import param_shapes
+    shapes = param_shapes("resnet50")
+    ts = [_T(int(np.prod(s)), orc.F32) for s in shapes]
+    groups = prb.distributed.assign_group_by_size(ts, [False] * len(ts), [1 << 20, 25 << 20])
+    assert sorted(v for g in groups for v in g) == list(range(len(ts)))
+    sizes = [sum(ts[v].numel * 4 for v in g) for g in groups]
+    assert sizes[0] >= (1 << 20) and all(s >= (25 << 20) for s in sizes[1:-1])
+    assert groups == orc.assign_group_by_size([t.numel for t in ts], [orc.F32] * len(ts), [False] * len(ts),
+                                              [1 << 20, 25 << 20])
+
+
+def test_assign_group_by_size_errors(prb):
+    from paddle_ray_b200._lib import PRBError
+    with pytest.raises(PRBError, match="permutation"):
+        prb.distributed.assign_group_by_size([_T(1, orc.F32), _T(1, orc.F32)], [False, False], [400], [0, 0])
+    with pytest.raises(PRBError, match="is_sparse_gradient"):
+        prb.distributed.assign_group_by_size([_T(1, orc.F32)], [False, False], [400])
+
+
+def _host_grads(prb, sizes, dtype="float32"):
+    return [prb.Tensor(n, dtype, device=-1) for n in sizes]
+
+
+def test_reducer_state_machine_matches_model_on_random_orders(prb):
+    rng = np.random.default_rng(1)
+    for trial in range(50):
+        n = int(rng.integers(2, 30))
+        sizes = [int(x) for x in rng.integers(1, 3000, n)]
+        ts = [_T(s, orc.F32) for s in sizes]
+        groups = prb.distributed.assign_group_by_size(ts, [False] * n, [2000, 6000])
+        groups = list(reversed(groups))
+        red = prb.distributed.EagerReducer(_host_grads(prb, sizes), groups, [False] * n, None)
+        model = orc.ReducerModel(groups, n)
+        for step in range(2):
+            red.prepare_for_backward()
+            model.prepare_for_backward()
+            order = list(rng.permutation(n)) if trial % 2 else list(reversed(range(n)))
+            for v in order:
+                red.mark_var_ready(int(v))
+                model.mark_var_ready(int(v))
+                assert red.launched_groups() == model.launched
+                assert red.finalized == model.finalized
+            assert red.launched_groups() == list(range(len(groups))) and red.finalized
+
+
+def test_reducer_error_behaviour(prb):
+    from paddle_ray_b200._lib import PRBError
+    sizes = [10, 20, 30, 40]
+    groups = [[3, 2], [1, 0]]
+    red = prb.distributed.EagerReducer(_host_grads(prb, sizes), groups, [False] * 4, None)
+    red.prepare_for_backward()
+    red.mark_var_ready(3)
+    with pytest.raises(PRBError, match="has been ready before"):   # reducer.cc:779-811
+        red.mark_var_ready(3)
+    with pytest.raises(PRBError, match="Out of bounds variable index"):  # reducer.cc:731-737
+        red.mark_var_ready(99)
+    with pytest.raises(PRBError, match="A serious error has occurred here"):  # reducer.cc:683-698
+        red.prepare_for_backward()
+    for v in (2, 1, 0):
+        red.mark_var_ready(v)
+    assert red.finalized
+    red.mark_var_ready(0)  # after finalize hooks only re-alias: a no-op (reducer.cc:740-758)
+    red.prepare_for_backward()
+    # dtype uniformity inside a group (reducer.cc:607-612), empty groups (:536-540), zero-size tensors (:589-593)
+    mixed = [prb.Tensor(4, "float32", device=-1), prb.Tensor(4, "bfloat16", device=-1)]
+    with pytest.raises(PRBError, match="unexpected dtype"):
+        prb.distributed.EagerReducer(mixed, [[0, 1]], [False, False], None)
+    with pytest.raises(PRBError, match="elements is 0"):
+        prb.distributed.EagerReducer(_host_grads(prb, [0, 4]), [[0, 1]], [False, False], None)
+    with pytest.raises(PRBError, match="find_unused_parameters=False"):
+        red.prepare_for_backward([1])
+
+
+def test_reducer_unused_vars_are_marked_with_the_first_hook(prb):
+    sizes = [10, 20, 30, 40]
+    groups = [[3, 2], [1, 0]]
+    red = prb.distributed.EagerReducer(_host_grads(prb, sizes), groups, [False] * 4, None, None, True)
+    red.prepare_for_backward(unused_vars=[2, 0])
+    red.mark_var_ready(3)          # marks 2 and 0 ready too -> group 0 complete
+    assert red.launched_groups() == [0]
+    red.mark_var_ready(1)
+    assert red.launched_groups() == [0, 1] and red.finalized
+
+
+def test_stores_roundtrip(tmp_path):
+    from paddle_ray_b200.distributed import FileStore, TCPStore
+    fs = FileStore(str(tmp_path / "fs"), timeout=5)
+    fs.set("ProcessGroupNCCL/nccl_ids/0/0", b"\x01" * 128)
+    assert fs.get("ProcessGroupNCCL/nccl_ids/0/0") == b"\x01" * 128
+    assert fs.add("ctr", 2) == 2 and fs.add("ctr", 3) == 5
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    master = TCPStore("127.0.0.1", port, True, 2, timeout=10)
+    got = {}
+
+    def peer():
+        c = TCPStore("127.0.0.1", port, False, 2, timeout=10)
+        got["v"] = c.get("k")       # blocks until the master publishes
+        got["n"] = c.add("n", 1)
+        c.close()
+
+    t = threading.Thread(target=peer)
+    t.start()
+    master.set("k", b"unique-id-bytes")
+    t.join(10)
+    assert got["v"] == b"unique-id-bytes" and got["n"] == 1
+    assert master.add("n", 1) == 2
+    master.close()
+
+
+def test_parallel_env_reads_reference_and_torchrun_names(monkeypatch):
+    from paddle_ray_b200.distributed import ParallelEnv
+    for k in ("PADDLE_TRAINER_ID", "PADDLE_TRAINERS_NUM", "PADDLE_MASTER", "FLAGS_selected_gpus", "RANK", "WORLD_SIZE",
+              "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "TORCHELASTIC_RUN_ID"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("PADDLE_TRAINER_ID", "3")
+    monkeypatch.setenv("PADDLE_TRAINERS_NUM", "8")
+    monkeypatch.setenv("PADDLE_MASTER", "10.0.0.1:6170")
+    monkeypatch.setenv("FLAGS_selected_gpus", "5")
+    e = ParallelEnv()
+    assert (e.rank, e.world_size, e.device_id, e.master_addr, e.master_port) == (3, 8, 5, "10.0.0.1", 6170)
+    for k in ("PADDLE_TRAINER_ID", "PADDLE_TRAINERS_NUM", "PADDLE_MASTER", "FLAGS_selected_gpus"):
+        monkeypatch.delenv(k)
+    monkeypatch.setenv("RANK", "1")
+    monkeypatch.setenv("WORLD_SIZE", "2")
+    monkeypatch.setenv("LOCAL_RANK", "1")
+    monkeypatch.setenv("MASTER_ADDR", "127.0.0.1")
+    monkeypatch.setenv("MASTER_PORT", "29501")
+    e = ParallelEnv()
+    assert (e.rank, e.world_size, e.device_id, e.master_port, e.under_torchrun) == (1, 2, 1, 29501, True)
