@@ -1,0 +1,413 @@
+#!/usr/bin/env python
+"""Benchmark of the data-parallel step tail (BASELINE.json metric: AdamW+grad-sync step GB/s & ms/step).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload resnet50]
+
+One "step" = one pass of the hot path over one batch of synthetic gradients:
+    prepare_for_backward -> every gradient marked ready (reverse parameter order) ->
+    per bucket: pack + 1/nranks scale -> NCCL allreduce on the comm stream (N > 1) ->
+    one fused multi-tensor AdamW launch that reads the reduced gradients straight from the bucket arena.
+Default workload = BASELINE.json configs[1]: ResNet-50 parameter shapes (161 tensors, 25,557,032 fp32
+elements), paddle.DataParallel + paddle.optimizer.AdamW, fp32, no AMP, no clip.
+
+`value` = whole-job algorithmic GB/s with inputs resident in HBM; `e2e` = the same metric through the
+public Python API with the gradients coming from pinned HOST memory every step (H2D inside the timed
+region) and a result read back (D2H).  Algorithmic bytes per element: pack r4+w4, AdamW
+r16+w12 -> 36 B/elem for fp32; bf16+master AMP+clip: pack r2+w2, norm pass r2, update r14+w14 -> 34 B/elem.
+
+The oracle (oracle/) is imported only by the cpu_baseline / --impl reference legs.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import bench_configs  # noqa: E402
+
+METRIC = "adamw_grad_sync_step_throughput"
+UNIT = "GB/s"
+
+WORKLOADS = {
+    # name: (shape list, param dtype, grad dtype, amp, clip, multi_precision, bytes/elem, human description)
+    "resnet50": ("resnet50", "float32", "float32", False, False, False, 36,
+                 "ResNet-50 param shapes (161 tensors, 25,557,032 elems), DataParallel + AdamW fp32"),
+    "resnet18": ("resnet18", "float32", "float32", False, False, False, 36,
+                 "ResNet-18 param shapes (62 tensors, 11,689,512 elems), DataParallel + AdamW fp32"),
+    "bert_base": ("bert_base", "bfloat16", "bfloat16", True, True, True, 34,
+                  "BERT-base shapes (206 tensors, 110,106,428 elems), AMP bf16 + fp32 master, global-norm clip"),
+    "gpt2_medium": ("gpt2_medium", "bfloat16", "bfloat16", True, True, True, 34,
+                    "GPT-2 medium shapes (292 tensors, 354,823,168 elems), multi_precision bf16, 25 MB buckets"),
+}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+# --------------------------------------------------------------------------------------------
+# clocks: sampled DURING the timed region
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    BAD = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20}
+    NOTE = {"sw_power_cap": 0x4}
+
+    def __init__(self, device_index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        self.h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[device_index]) if vis and vis.split(",")[device_index].isdigit() else device_index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.h = None
+
+    def _sample(self):
+        if self.h is None:
+            return
+        try:
+            self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+            mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            for name, bit in {**self.BAD, **self.NOTE}.items():
+                if mask & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def start(self):
+        def run():
+            while not self._stop.is_set():
+                self._sample()
+                time.sleep(0.002)
+        self._thread = threading.Thread(target=run, daemon=True)
+        self._thread.start()
+
+    def stop(self):
+        self._sample()
+        self._stop.set()
+        if self._thread:
+            self._thread.join(1.0)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unsampled"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------------------------
+# workload construction (product API only)
+# --------------------------------------------------------------------------------------------
+def build_workload(prb, name, rank):
+    shapes_name, pdt, gdt, amp, clip, mp, bpe, desc = WORKLOADS[name] if name in WORKLOADS else \
+        (name, "float32", "float32", False, False, False, 36, "flat sweep " + name)
+    numels = bench_configs.param_numels(shapes_name)
+    rng = np.random.default_rng(1234 + rank)
+    params, host_grads = [], []
+    for i, n in enumerate(numels):
+        p32 = rng.normal(0, 0.02, n).astype(np.float32)
+        g32 = rng.normal(0, 1e-2, n).astype(np.float32)
+        if amp:
+            g32 *= np.float32(2.0 ** 15)
+        if pdt == "float32":
+            p = prb.Tensor.from_numpy(p32, name="w_%d" % i)
+        else:
+            p = prb.Tensor.from_numpy(p32).astype(pdt)
+            p.name = "w_%d" % i
+        if gdt == "float32":
+            g = prb.Tensor.from_numpy(g32)
+            host_grads.append(g32)
+        else:
+            g = prb.Tensor.from_numpy(g32).astype(gdt)
+            host_grads.append(g.numpy())
+        p.grad = g
+        params.append(p)
+    grad_clip = prb.nn.ClipGradByGlobalNorm(1.0) if clip else None
+    opt = prb.optimizer.AdamW(learning_rate=1e-3, beta1=0.9, beta2=0.999, epsilon=1e-8, parameters=params,
+                              weight_decay=0.01, grad_clip=grad_clip, multi_precision=mp)
+    # the reduced gradients are consumed from the bucket arena; nothing reads an unscaled copy back
+    opt._write_back_unscaled_grads = False
+    opt._create_accumulators()
+    # moments start away from zero (m1 N(0,1e-3), m2 U(0,1e-3), step 10)
+    for p in params:
+        acc = opt._accumulators[p.name]
+        acc["moment1"].copy_from_numpy(rng.normal(0, 1e-3, p.numel).astype(np.float32))
+        acc["moment2"].copy_from_numpy(rng.uniform(0, 1e-3, p.numel).astype(np.float32))
+    opt._beta1_pow.copy_from_numpy(np.array([0.9 ** 10], np.float32))
+    opt._beta2_pow.copy_from_numpy(np.array([0.999 ** 10], np.float32))
+    scaler = prb.amp.GradScaler(init_loss_scaling=2.0 ** 15) if amp else None
+    dp = prb.DataParallel(params, comm_buffer_size=25, last_comm_buffer_size=1, consume_from_buckets=True)
+    for p, v in zip(params, dp.bucket_grads()):
+        p._reduced_grad = v
+    return {"params": params, "opt": opt, "scaler": scaler, "dp": dp, "numels": numels, "bpe": bpe, "desc": desc,
+            "host_grads": host_grads, "amp": amp, "clip": clip, "pdt": pdt, "gdt": gdt,
+            "elems": int(sum(numels)), "buckets": len(dp.group_indices)}
+
+
+def make_step(w):
+    dp, opt, scaler = w["dp"], w["opt"], w["scaler"]
+
+    def tail():
+        if scaler is not None:
+            scaler.step(opt)
+            scaler.update()
+        else:
+            opt.step()
+
+    def step():
+        dp.prepare_for_backward()
+        dp.mark_all_ready()
+        tail()
+
+    return step, tail
+
+
+# --------------------------------------------------------------------------------------------
+# CPU baseline: the reference's CPU path restated in oracle/ (kind "port"), all host threads
+# --------------------------------------------------------------------------------------------
+def cpu_reference_run(workload, nranks, budget_s, min_steps=2, max_steps=10 ** 9):
+    """concat -> scale(1/nranks) -> [allreduce: one process, nothing to exchange] -> split -> AdamW per tensor.
+    ref: reducer.cc:1037-1070 on CPUPlace, cpu/adamw_kernel.cc:96-189.  fp32 only (the CPU kernel
+    registers float/double only), so bf16 workloads are timed with fp32 storage of the same shapes."""
+    from oracle import oracle as orc
+    shapes_name = WORKLOADS[workload][0] if workload in WORKLOADS else workload
+    bpe = WORKLOADS[workload][6] if workload in WORKLOADS else 36
+    numels = bench_configs.param_numels(shapes_name)
+    rng = np.random.default_rng(1234)
+    threads = orc.max_threads()
+    P = [rng.normal(0, 0.02, n).astype(np.float32) for n in numels]
+    G = [rng.normal(0, 1e-2, n).astype(np.float32) for n in numels]
+    M1 = [rng.normal(0, 1e-3, n).astype(np.float32) for n in numels]
+    M2 = [rng.uniform(0, 1e-3, n).astype(np.float32) for n in numels]
+    b1p, b2p = np.float32(0.9 ** 10), np.float32(0.999 ** 10)
+    elems = int(sum(numels))
+
+    bucket = np.empty(elems, np.float32)  # a caching allocator would hand the same pages back every step
+    grads = [np.empty(n, np.float32) for n in numels]
+
+    def one_step():
+        orc.concat(G, out=bucket)                                # memcpy-loop concat
+        orc.cpu_scale_f32(bucket, np.float32(1.0 / nranks), threads)
+        orc.split(bucket, numels, outs=grads)                    # memcpy-loop split
+        for p, g, m1, m2 in zip(P, grads, M1, M2):
+            orc.cpu_adamw(p, g, m1, m2, lr=1e-3, lr_ratio=1.0, beta1=0.9, beta2=0.999, epsilon=1e-8, coeff=0.01,
+                          beta1_pow=b1p, beta2_pow=b2p, nthreads=threads)
+
+    one_step()  # warm-up (page faults, thread pool)
+    t0 = time.perf_counter()
+    steps = 0
+    while steps < max_steps and (steps < min_steps or time.perf_counter() - t0 < budget_s):
+        one_step()
+        steps += 1
+    dt = time.perf_counter() - t0
+    return {"gbs": elems * bpe * steps / dt / 1e9, "ms_per_step": dt / steps * 1e3, "steps": steps, "threads": threads,
+            "elems": elems, "seconds": dt}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0  # only rank 0 runs the CPU arm
+    # each "step" of this arm = one full CPU pass over the workload; bounded so the run ends within minutes
+    budget = 60.0
+    r = cpu_reference_run(args.workload, args.gpus, budget_s=budget, min_steps=1, max_steps=args.steps + args.warmup)
+    desc = WORKLOADS[args.workload][7] if args.workload in WORKLOADS else args.workload
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["gbs"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
+        "warmup": 1, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "path": "CPU: concat -> scale(1/nranks) -> split -> AdamW (oracle port of the "
+                   "reference's CPU kernels; Paddle itself cannot be built here)", "allreduce": "none (one process)"},
+        "cpu_baseline": {"value": r["gbs"], "unit": UNIT, "cores": r["threads"], "kind": "port",
+                         "sample": "%d full steps of the workload in %.1f s" % (r["steps"], r["seconds"])},
+        "e2e": {"value": r["gbs"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------------
+# the GPU arm
+# --------------------------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import paddle_ray_b200 as prb  # fails loudly if the CUDA library is missing
+    from paddle_ray_b200._lib import lib
+
+    if prb.device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    group = prb.distributed.init_parallel_env()
+    rank, nranks = group.rank, group.nranks
+    if nranks != args.gpus:
+        raise SystemExit("bench.py: --gpus %d but WORLD_SIZE=%d (launch N>1 through torch.distributed.run)" % (args.gpus, nranks))
+    w = build_workload(prb, args.workload, rank)
+    step, tail = make_step(w)
+    stream = prb.current_stream()
+    peak, peak_kind = measured_peak()
+    bytes_per_step = w["elems"] * w["bpe"]
+
+    def rank_max(x: float) -> float:
+        t = prb.Tensor.from_numpy(np.array([x], np.float32))
+        group.all_reduce(t, "max")
+        return float(t.numpy()[0])
+
+    # ---- warm-up (also builds every cached plan)
+    for _ in range(max(args.warmup, 3)):
+        step()
+    stream.synchronize()
+
+    # ---- timed region: exactly K steps, barrier + sync on both sides, CUDA events on the launching stream
+    group.barrier()
+    prb.synchronize()
+    sampler = ClockSampler(group.device)
+    ev0, ev1 = prb.Event(), prb.Event()
+    ka = [prb.Event() for _ in range(args.steps)]
+    kb = [prb.Event() for _ in range(args.steps)]
+    launches0 = lib.prb_launch_count()
+    sampler.start()
+    ev0.record()
+    for i in range(args.steps):
+        w["dp"].prepare_for_backward()
+        w["dp"].mark_all_ready()
+        ka[i].record()
+        tail()            # the dominant kernel: one fused multi-tensor AdamW launch (+ its 1-thread beta-pow kernel)
+        kb[i].record()
+    ev1.record()
+    ev1.synchronize()
+    clocks = sampler.stop()
+    launches = lib.prb_launch_count() - launches0
+    group.barrier()
+    prb.synchronize()
+    ms_total = rank_max(ev0.elapsed_ms(ev1))
+    ms_per_step = ms_total / args.steps
+    value = bytes_per_step * nranks / (ms_per_step * 1e-3) / 1e9
+    tail_ms = float(np.mean([a.elapsed_ms(b) for a, b in zip(ka, kb)]))
+
+    # ---- roofline of the dominant kernel (AdamW update pass): algorithmic bytes / live launch duration
+    upd_bpe = 28 if w["gdt"] == w["pdt"] else 30
+    tail_bytes = w["elems"] * (upd_bpe + (2 if w["clip"] or w["amp"] else 0))  # + the norm pass read for AMP/clip runs
+    achieved = tail_bytes / (tail_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "adam_chunks_kernel (+grad_pass_kernel when AMP/clip)",
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peak_kind == "measured" else "profiling-recipe fallback",
+                "algorithmic_bytes_per_launch": tail_bytes, "avg_launch_ms": tail_ms,
+                "frac_of_nominal_8TBps": achieved / 8000.0}
+    try:  # dram bytes per launch from the committed ncu capture, when one exists for this workload
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            roofline["traffic"] = json.load(f).get(args.workload)
+    except Exception:
+        pass
+
+    # ---- e2e: gradients arrive from pinned host memory every step, a result is read back every step
+    gsz = 4 if w["gdt"] == "float32" else 2
+    pinned = [prb.PinnedBuffer(n, np.float32 if gsz == 4 else np.uint16) for n in w["numels"]]
+    for pb, hg in zip(pinned, w["host_grads"]):
+        pb.array[:] = hg
+    res_host = prb.PinnedBuffer(w["numels"][0] + 2, np.float32 if w["pdt"] == "float32" else np.uint16)
+    h2d = sum(pb.nbytes for pb in pinned)
+    p0 = w["params"][0]
+    d2h = p0.nbytes + 8
+
+    def e2e_step():
+        for p, pb in zip(w["params"], pinned):
+            prb._lib.call("prb_memcpy_h2d", p.grad.data_ptr, pb.ptr, pb.nbytes, stream.handle)
+        step()
+        prb._lib.call("prb_memcpy_d2h", res_host.ptr, p0.data_ptr, p0.nbytes, stream.handle)
+        prb._lib.call("prb_memcpy_d2h", res_host.ptr + p0.nbytes, w["opt"]._beta1_pow.data_ptr, 4, stream.handle)
+        prb._lib.call("prb_memcpy_d2h", res_host.ptr + p0.nbytes + 4, w["opt"]._beta2_pow.data_ptr, 4, stream.handle)
+        stream.synchronize()  # the caller consumes the result on the host
+
+    for _ in range(3):
+        e2e_step()
+    group.barrier()
+    prb.synchronize()
+    e2e_steps = max(3, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    prb.synchronize()
+    e2e_ms = rank_max((time.perf_counter() - t0) * 1e3) / e2e_steps
+    e2e = {"value": bytes_per_step * nranks / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps}
+
+    # ---- CPU baseline (rank 0, N = 1 only): bounded sample of the same workload on the host cores
+    cpu_baseline = None
+    if rank == 0 and nranks == 1 and not args.no_cpu_baseline:
+        r = cpu_reference_run(args.workload, 1, budget_s=12.0)
+        cpu_baseline = {"value": r["gbs"], "unit": UNIT, "cores": r["threads"], "kind": "port",
+                        "ms_per_step": r["ms_per_step"],
+                        "sample": "%d full steps of the same workload (%d elems, fp32) in %.1f s" % (r["steps"], r["elems"], r["seconds"])}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": nranks, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": w["desc"], "elements_per_gpu": w["elems"], "tensors": len(w["numels"]),
+                       "buckets": w["buckets"], "bucket_mb": [25, 1], "param_dtype": w["pdt"], "grad_dtype": w["gdt"],
+                       "amp": w["amp"], "clip": w["clip"], "algorithmic_bytes_per_elem": w["bpe"],
+                       "l2": "working set %.0f MB per step > 126 MB L2 (inputs larger than L2, no flush)" %
+                             (w["elems"] * (w["bpe"] + 8) / 1e6),
+                       "parallelism": "dp%d" % nranks, "pct_of_measured_hbm_peak_per_gpu": 100.0 * value / nranks / peak,
+                       "pct_of_nominal_8TBps_per_gpu": 100.0 * value / nranks / 8000.0},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+        }
+        if cpu_baseline is not None:
+            line["cpu_baseline"] = cpu_baseline
+        print(json.dumps(line), flush=True)
+    group.barrier()
+    return 0
+
+
+def self_launch(args):
+    """`python bench.py --gpus N` without a launcher: start N ranks of this script on 127.0.0.1."""
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    procs = []
+    for r in range(args.gpus):
+        env = {**os.environ, "RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(args.gpus),
+               "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "PRB_SELF_LAUNCHED": "1"}
+        procs.append(subprocess.Popen([sys.executable, os.path.abspath(__file__)] + sys.argv[1:], env=env))
+    rc = 0
+    for p in procs:
+        rc = rc or p.wait()
+    return rc
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="resnet50")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        return self_launch(args)
+    return run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -131,19 +131,21 @@ def scale(x: np.ndarray, dtype: int, scale_d: float, bias: float = 0.0, bias_aft
     return out
 
 
-def concat(arrays) -> np.ndarray:
+def concat(arrays, out=None) -> np.ndarray:
     """Dense byte concat of same-dtype 1-D arrays (concat_and_split_functor.cc:52-66)."""
     arrays = [np.ascontiguousarray(a) for a in arrays]
     total = sum(a.size for a in arrays)
-    out = np.empty(total, dtype=arrays[0].dtype)
+    if out is None:
+        out = np.empty(total, dtype=arrays[0].dtype)
     ptrs = (C.c_void_p * len(arrays))(*[a.ctypes.data for a in arrays])
     nb = np.array([a.nbytes for a in arrays], dtype=np.int64)
     lib().orc_concat(len(arrays), ptrs, _p(nb), _p(out))
     return out
 
 
-def split(bucket: np.ndarray, numels) -> list:
-    outs = [np.empty(int(n), dtype=bucket.dtype) for n in numels]
+def split(bucket: np.ndarray, numels, outs=None) -> list:
+    if outs is None:
+        outs = [np.empty(int(n), dtype=bucket.dtype) for n in numels]
     ptrs = (C.c_void_p * len(outs))(*[o.ctypes.data for o in outs])
     nb = np.array([o.nbytes for o in outs], dtype=np.int64)
     lib().orc_split(len(outs), _p(bucket), _p(nb), ptrs)

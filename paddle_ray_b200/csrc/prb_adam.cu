@@ -68,8 +68,8 @@ __device__ __forceinline__ Coef make_coef(const AdamDesc* __restrict__ d, const 
   return k;
 }
 
-template <typename T, typename TG, bool kMaster>
-__global__ void __launch_bounds__(kAdamThreads) adam_chunks_kernel(const AdamArgs a) {
+template <typename T, typename TG, bool kMaster, int kAdamThreads, int kAdamUnroll, int kMinBlocks>
+__global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(const AdamArgs a) {
   const bool skipped = a.skip != nullptr && *a.skip;
   if (skipped && !a.zero_grad) return;
 
@@ -191,16 +191,51 @@ __global__ void beta_pow_kernel(const PowPair* pairs, int n, float beta1, float 
   }
 }
 
+// Launch geometry variants {threads, lane-vectors per thread, min CTAs per SM}; PRB_ADAM_VARIANT
+// selects one at load time (tuning aid), the default is the measured best (profiles/).
+struct Variant {
+  int threads, unroll, min_blocks;
+};
+constexpr Variant kVariants[] = {{256, 2, 2}, {256, 1, 4}, {128, 2, 4}, {128, 1, 8}, {512, 1, 2}, {256, 2, 3}};
+constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
+constexpr int kDefaultVariant = 3;  // 128 threads x 1 lane-vector, >= 8 CTAs/SM: best on B200 (profiles/r1_adam_variants.md)
+
+int active_variant() {
+  static int v = [] {
+    const char* e = getenv("PRB_ADAM_VARIANT");
+    int x = e ? atoi(e) : kDefaultVariant;
+    return (x < 0 || x >= kNumVariants) ? kDefaultVariant : x;
+  }();
+  return v;
+}
+
+template <typename T, typename TG, int kThreads, int kUnroll, int kMinBlocks>
+void launch_variant(bool has_master, const AdamArgs& a, cudaStream_t stream) {
+  if (has_master) adam_chunks_kernel<T, TG, true, kThreads, kUnroll, kMinBlocks><<<a.nchunks, kThreads, 0, stream>>>(a);
+  else adam_chunks_kernel<T, TG, false, kThreads, kUnroll, kMinBlocks><<<a.nchunks, kThreads, 0, stream>>>(a);
+}
+
 template <typename T, typename TG>
 int32_t launch_typed(bool has_master, const AdamArgs& a, cudaStream_t stream) {
   if (a.nchunks == 0) return PRB_SUCCESS;
-  if (has_master) adam_chunks_kernel<T, TG, true><<<a.nchunks, kAdamThreads, 0, stream>>>(a);
-  else adam_chunks_kernel<T, TG, false><<<a.nchunks, kAdamThreads, 0, stream>>>(a);
+  switch (active_variant()) {
+    case 0: launch_variant<T, TG, 256, 2, 2>(has_master, a, stream); break;
+    case 1: launch_variant<T, TG, 256, 1, 4>(has_master, a, stream); break;
+    case 2: launch_variant<T, TG, 128, 2, 4>(has_master, a, stream); break;
+    case 3: launch_variant<T, TG, 128, 1, 8>(has_master, a, stream); break;
+    case 4: launch_variant<T, TG, 512, 1, 2>(has_master, a, stream); break;
+    default: launch_variant<T, TG, 256, 2, 3>(has_master, a, stream); break;
+  }
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 
 }  // namespace
+
+int adam_chunk_elems() {
+  const Variant v = kVariants[active_variant()];
+  return v.threads * kVec * v.unroll;
+}
 
 int32_t launch_adam(int32_t dtype_param, int32_t dtype_grad, bool has_master, const AdamArgs& a, cudaStream_t stream) {
   if (dtype_param == PRB_FLOAT32 && dtype_grad == PRB_FLOAT32) return launch_typed<float, float>(has_master, a, stream);
@@ -388,7 +423,7 @@ int32_t run_adam_list(const ListArgs& A, cudaStream_t stream) {
                              stream));  // pageable source: staged before return
 
   DeviceTable tab;
-  PRB_TRY(get_table(descs.data(), sizeof(AdamDesc), (int)n, numels.data(), kAdamChunk, stream, &tab));
+  PRB_TRY(get_table(descs.data(), sizeof(AdamDesc), (int)n, numels.data(), adam_chunk_elems(), stream, &tab));
 
   AdamArgs a;
   memset(&a, 0, sizeof(a));

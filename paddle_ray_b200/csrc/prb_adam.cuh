@@ -38,9 +38,8 @@ struct AdamArgs {
   int32_t zero_grad;         // 1: store zeros to grad after consuming it (clear_grad folded in)
 };
 
-constexpr int kAdamThreads = 256;
-constexpr int kAdamUnroll = 2;
-constexpr int kAdamChunk = kAdamThreads * kVec * kAdamUnroll;  // 4096 elements per CTA
+// Elements per CTA of the active launch geometry (threads * kVec * lane-vectors per thread).
+int adam_chunk_elems();
 
 int32_t launch_adam(int32_t dtype_param, int32_t dtype_grad, bool has_master, const AdamArgs& args,
                     cudaStream_t stream);

@@ -108,6 +108,9 @@ struct Group {
   cudaEvent_t ready = nullptr;    // recorded on the calc stream after pack
   cudaEvent_t done = nullptr;     // recorded on the comm stream after allreduce (+unpack)
   bool has_unused = false;
+  // plans cached per group (rebuilt only when the set of unused parameters changes)
+  DeviceTable pack_tab, unpack_tab;
+  bool pack_valid = false, unpack_valid = false, pack_had_unused = false;
 };
 }  // namespace
 
@@ -168,9 +171,12 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
         PRB_CUDA(cudaMemsetAsync(region + (size_t)g.slot_off[s] * es, 0, (size_t)r->grads[g.vars[s]].numel * es, calc));
   }
   // pack + scale_(bucket, 1.0/nranks, 0.0, false) in one pass, calc stream
-  DeviceTable pack;
-  PRB_TRY(group_tables(r, g, false, calc, &pack));
-  PRB_TRY(launch_scale(g.dtype, pack, 1.0 / (double)c->nranks, 0.0f, false, calc));
+  if (!g.pack_valid || g.has_unused || g.pack_had_unused) {
+    PRB_TRY(group_tables(r, g, false, calc, &g.pack_tab));
+    g.pack_valid = true;
+    g.pack_had_unused = g.has_unused;
+  }
+  PRB_TRY(launch_scale(g.dtype, g.pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
   if (c->nranks > 1) {
     // SyncDefaultStream: comm stream waits for the calc stream (ref process_group_nccl.cc:658-667)
     PRB_CUDA(cudaEventRecord(g.ready, calc));
@@ -179,15 +185,19 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
     PRB_TRY(nccl_dtype(g.dtype, &nt));
     PRB_NCCL(g_nccl.AllReduce(region, region, (size_t)g.length, nt, ncclSum, c->comm, c->stream));
     if (r->unpack) {  // the reference also splits on the comm stream (reducer.cc:1062-1069)
-      DeviceTable un;
-      PRB_TRY(group_tables(r, g, true, c->stream, &un));
-      PRB_TRY(launch_copy(es, un, c->stream));
+      if (!g.unpack_valid) {
+        PRB_TRY(group_tables(r, g, true, c->stream, &g.unpack_tab));
+        g.unpack_valid = true;
+      }
+      PRB_TRY(launch_copy(es, g.unpack_tab, c->stream));
     }
     PRB_CUDA(cudaEventRecord(g.done, c->stream));
   } else if (r->unpack) {
-    DeviceTable un;
-    PRB_TRY(group_tables(r, g, true, calc, &un));
-    PRB_TRY(launch_copy(es, un, calc));
+    if (!g.unpack_valid) {
+      PRB_TRY(group_tables(r, g, true, calc, &g.unpack_tab));
+      g.unpack_valid = true;
+    }
+    PRB_TRY(launch_copy(es, g.unpack_tab, calc));
   }
   r->launched.push_back((int64_t)gi);
   return PRB_SUCCESS;

@@ -126,7 +126,7 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   }
 
   DeviceTable tab;
-  PRB_TRY(get_table(descs.data(), sizeof(AdamDesc), (int)num, numels.data(), kAdamChunk, stream, &tab));
+  PRB_TRY(get_table(descs.data(), sizeof(AdamDesc), (int)num, numels.data(), adam_chunk_elems(), stream, &tab));
   AdamArgs a;
   memset(&a, 0, sizeof(a));
   a.descs = reinterpret_cast<const AdamDesc*>(tab.descs);

@@ -82,6 +82,8 @@ class Optimizer:
         self._fused_cache = None
         # True folds clear_grad(set_to_zero=True) into the update pass (gradients are zeroed as they are consumed)
         self._zero_grads_in_step = False
+        # True keeps p.grad reference-visible after an AMP step (the unscaled gradient is stored back)
+        self._write_back_unscaled_grads = True
         self.clear_gradients = self.clear_grad
 
     # ---- auxiliary vars (found_inf hand-off from GradScaler; ref adamw.py:283-291)
@@ -186,6 +188,7 @@ class Optimizer:
         # The ctypes argument block is built once and reused while the buffers stay the same.
         key = (tuple(g.data_ptr for _, g in pg), id(clip), loss_scale.data_ptr if loss_scale is not None else 0,
                found_inf.data_ptr if found_inf is not None else 0, self._zero_grads_in_step,
+               self._write_back_unscaled_grads,
                _clip_by_global_norm_using_mp_type())
         cached = self._fused_cache
         if cached is None or cached[0] != key:
@@ -203,7 +206,8 @@ class Optimizer:
             cfg.auto_skip_clip = int(clip.auto_skip_clip) if clip else 0
             cfg.use_mp_type = int(_clip_by_global_norm_using_mp_type())
             # p.grad holds the unscaled (never the clipped) gradient after a reference step
-            cfg.write_back_grads = int(loss_scale is not None and not self._zero_grads_in_step)
+            cfg.write_back_grads = int(loss_scale is not None and self._write_back_unscaled_grads
+                                       and not self._zero_grads_in_step)
             cfg.zero_grads = int(self._zero_grads_in_step)
             lr_ratio, with_decay = self._tensor_attrs(pg)
             acc = [self._accumulators[p.name] for p in params]

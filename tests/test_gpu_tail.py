@@ -77,10 +77,10 @@ def check(prb, opt, params, host, dtype):
 def test_reducer_single_rank_pack_unpack_is_bit_exact(prb):
     rng = np.random.default_rng(0)
     params, host = make_params(prb, rng, SIZES, orc.F32)
-    for h in host:
+    for p, h in zip(params, host):
         h["grad"][:1] = -0.0
-    params[0].grad.copy_from_numpy(host[0]["grad"])
-    dp = prb.DataParallel(params, comm_buffer_size=1, last_comm_buffer_size=0.01)
+        p.grad.copy_from_numpy(h["grad"])
+    dp = prb.DataParallel(params, comm_buffer_size=0.1, last_comm_buffer_size=0.01)
     assert len(dp.group_indices) > 2
     for _ in range(2):
         dp.prepare_for_backward()
@@ -102,7 +102,7 @@ def test_dataparallel_adamw_fp32_step(prb, consume):
     """configs[1] shape of the path: DataParallel + AdamW fp32, no AMP, no clip; 3 steps."""
     rng = np.random.default_rng(1)
     params, host = make_params(prb, rng, SIZES, orc.F32)
-    dp = prb.DataParallel(params, comm_buffer_size=1, last_comm_buffer_size=0.01, consume_from_buckets=consume)
+    dp = prb.DataParallel(params, comm_buffer_size=0.1, last_comm_buffer_size=0.01, consume_from_buckets=consume)
     opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, weight_decay=0.01,
                               apply_decay_param_fun=lambda name: name not in ("w_0", "w_1"),
                               lr_ratio=lambda p: 0.5 if p.name == "w_3" else 1.0)
@@ -137,7 +137,7 @@ def test_amp_bf16_master_clip_step(prb, main_grad, inject):
     opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, weight_decay=0.01, grad_clip=clip,
                               multi_precision=True)
     scaler = prb.amp.GradScaler(init_loss_scaling=2.0 ** 15, incr_every_n_steps=2, decr_every_n_nan_or_inf=1)
-    dp = prb.DataParallel(params, comm_buffer_size=1, last_comm_buffer_size=0.01)
+    dp = prb.DataParallel(params, comm_buffer_size=0.1, last_comm_buffer_size=0.01)
     if inject:
         bad = host[5]["grad"]
         bad[17] = orc.from_f32(np.array([np.inf if inject == "inf" else np.nan], np.float32), gdt)[0]

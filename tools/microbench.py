@@ -35,7 +35,7 @@ def main():
     lr = T.from_numpy(np.array([1e-3], np.float32))
     b1 = T.from_numpy(np.array([0.9 ** 10], np.float32))
     b2 = T.from_numpy(np.array([0.999 ** 10], np.float32))
-    for logn in (20, 22, 24, 26, 28):
+    for logn in [int(x) for x in os.environ.get('PRB_MB_SIZES', '20,22,24,26,28').split(',')]:
         n = 1 << logn
         p, g, m1 = (T.from_numpy(np.random.default_rng(i).normal(0, 0.02, n).astype(np.float32)) for i in range(3))
         m2 = T.from_numpy(np.random.default_rng(3).uniform(0, 1e-3, n).astype(np.float32))
@@ -53,9 +53,12 @@ def main():
     # bf16 multi-precision
     for logn in (24, 27):
         n = 1 << logn
-        p = T.zeros(n, "bfloat16")
-        g = T.zeros(n, "bfloat16")
-        mp, m1, m2 = (T.zeros(n, "float32") for _ in range(3))
+        r = np.random.default_rng(7)
+        mp = T.from_numpy(r.normal(0, 0.02, n).astype(np.float32))
+        p = mp.astype("bfloat16")
+        g = T.from_numpy(r.normal(0, 1e-2, n).astype(np.float32)).astype("bfloat16")
+        m1 = T.from_numpy(r.normal(0, 1e-3, n).astype(np.float32))
+        m2 = T.from_numpy(r.uniform(0, 1e-3, n).astype(np.float32))
         ms = timeit(lambda: _C_ops.adamw_(p, g, lr, m1, m2, b1, b2, mp, None, 0.9, 0.999, 1e-8, 1.0, 0.01, True, False, 1000, True, True))
         gbs = n * 28 / ms / 1e6
         print(f"adamw bf16+master n=2^{logn}: {ms*1e3:9.1f} us  {gbs:8.1f} GB/s  {gbs/PEAK:.3f}")
