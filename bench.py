@@ -120,8 +120,19 @@ def build_workload(prb, name, rank):
         (name, "float32", "float32", False, False, False, 36, "flat sweep " + name)
     numels = bench_configs.param_numels(shapes_name)
     rng = np.random.default_rng(1234 + rank)
-    params, host_grads = [], []
-    for i, n in enumerate(numels):
+    # gradients live in ONE device arena (256-byte aligned views), mirrored by one pinned host arena, so the
+    # e2e leg moves them with a single H2D copy -- what a caller that controls allocation would do
+    gsz = 4 if gdt == "float32" else 2
+    align = 256 // gsz
+    offs, total = [], 0
+    for n in numels:
+        offs.append(total)
+        total += (n + align - 1) // align * align
+    grad_arena = prb.Tensor.zeros(total, gdt)
+    host_arena = prb.PinnedBuffer(total, np.float32 if gsz == 4 else np.uint16)
+    host_arena.array[:] = 0
+    params = []
+    for i, (n, off) in enumerate(zip(numels, offs)):
         p32 = rng.normal(0, 0.02, n).astype(np.float32)
         g32 = rng.normal(0, 1e-2, n).astype(np.float32)
         if amp:
@@ -131,12 +142,14 @@ def build_workload(prb, name, rank):
         else:
             p = prb.Tensor.from_numpy(p32).astype(pdt)
             p.name = "w_%d" % i
+        g = grad_arena.view(off, n)
         if gdt == "float32":
-            g = prb.Tensor.from_numpy(g32)
-            host_grads.append(g32)
+            g.copy_from_numpy(g32)
         else:
-            g = prb.Tensor.from_numpy(g32).astype(gdt)
-            host_grads.append(g.numpy())
+            tmp = prb.Tensor.from_numpy(g32).astype(gdt)
+            g.copy_(tmp)
+            prb.current_stream().synchronize()
+        host_arena.array[off:off + n] = g.numpy()
         p.grad = g
         params.append(p)
     grad_clip = prb.nn.ClipGradByGlobalNorm(1.0) if clip else None
@@ -157,7 +170,7 @@ def build_workload(prb, name, rank):
     for p, v in zip(params, dp.bucket_grads()):
         p._reduced_grad = v
     return {"params": params, "opt": opt, "scaler": scaler, "dp": dp, "numels": numels, "bpe": bpe, "desc": desc,
-            "host_grads": host_grads, "amp": amp, "clip": clip, "pdt": pdt, "gdt": gdt,
+            "grad_arena": grad_arena, "host_arena": host_arena, "amp": amp, "clip": clip, "pdt": pdt, "gdt": gdt,
             "elems": int(sum(numels)), "buckets": len(dp.group_indices)}
 
 
@@ -315,18 +328,13 @@ def run_gpu_arm(args):
         pass
 
     # ---- e2e: gradients arrive from pinned host memory every step, a result is read back every step
-    gsz = 4 if w["gdt"] == "float32" else 2
-    pinned = [prb.PinnedBuffer(n, np.float32 if gsz == 4 else np.uint16) for n in w["numels"]]
-    for pb, hg in zip(pinned, w["host_grads"]):
-        pb.array[:] = hg
     res_host = prb.PinnedBuffer(w["numels"][0] + 2, np.float32 if w["pdt"] == "float32" else np.uint16)
-    h2d = sum(pb.nbytes for pb in pinned)
+    h2d = w["host_arena"].nbytes
     p0 = w["params"][0]
     d2h = p0.nbytes + 8
 
     def e2e_step():
-        for p, pb in zip(w["params"], pinned):
-            prb._lib.call("prb_memcpy_h2d", p.grad.data_ptr, pb.ptr, pb.nbytes, stream.handle)
+        prb._lib.call("prb_memcpy_h2d", w["grad_arena"].data_ptr, w["host_arena"].ptr, h2d, stream.handle)
         step()
         prb._lib.call("prb_memcpy_d2h", res_host.ptr, p0.data_ptr, p0.nbytes, stream.handle)
         prb._lib.call("prb_memcpy_d2h", res_host.ptr + p0.nbytes, w["opt"]._beta1_pow.data_ptr, 4, stream.handle)

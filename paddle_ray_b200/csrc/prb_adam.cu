@@ -68,8 +68,33 @@ __device__ __forceinline__ Coef make_coef(const AdamDesc* __restrict__ d, const 
   return k;
 }
 
+// Shared beta-pow accumulators advanced inside the update kernel (ref UpdateAdamWBetaPow
+// adamw_kernel.cu:130-139), which removes the separate 1-thread launch.  Each CTA takes a ticket
+// AFTER the old values have arrived in the registers of the one thread that reads them (the dummy
+// register operands of the inline atom make the instruction wait for them), so the CTA that draws the last ticket knows every CTA
+// has read the old values and may overwrite them.  The atomic's latency hides under the data loads
+// already in flight.
+__device__ __forceinline__ void advance_pows_once(const AdamArgs& a, const Coef& k) {
+  if (a.pow_ticket == nullptr) return;
+  unsigned int t;
+  asm volatile(
+      "{\n\t.reg .f32 dep0, dep1;\n\tmov.f32 dep0, %2;\n\tmov.f32 dep1, %3;\n\t"
+      "atom.global.add.u32 %0, [%1], 1;\n\t}"
+      : "=r"(t)
+      : "l"(a.pow_ticket), "f"(k.bc2), "f"(k.step)
+      : "memory");
+  if (t == gridDim.x - 1) {
+    *a.pow_ticket = 0u;
+    *a.pow_b1 = __fmul_rn(a.beta1, *a.pow_b1);
+    *a.pow_b2 = __fmul_rn(a.beta2, *a.pow_b2);
+  }
+}
+
 template <typename T, typename TG, bool kMaster, int kAdamThreads, int kAdamUnroll, int kMinBlocks>
 __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(const AdamArgs a) {
+  // Per-tensor coefficients are fetched and derived by ONE thread (while the data loads of the
+  // whole CTA are in flight) and broadcast through shared memory.
+  __shared__ Coef sk;
   const bool skipped = a.skip != nullptr && *a.skip;
   if (skipped && !a.zero_grad) return;
 
@@ -113,8 +138,12 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
         load_vec<float>(m2_ptr + e, m2v[u]);
       }
     }
-    // ---- per-tensor coefficients: fetched and derived while the data loads are in flight
-    const Coef k = make_coef<TG>(d, a);
+    if (threadIdx.x == 0) {
+      sk = make_coef<TG>(d, a);
+      advance_pows_once(a, sk);
+    }
+    __syncthreads();
+    const Coef k = sk;
     // ---- compute + store
 #pragma unroll
     for (int u = 0; u < kAdamUnroll; ++u) {
@@ -157,7 +186,12 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
   } else {
     // Unaligned tensor (caller passed a pointer that is not 32-/16-byte aligned): coalesced
     // element-wise accesses, same arithmetic.
-    const Coef k = make_coef<TG>(d, a);
+    if (threadIdx.x == 0) {
+      sk = make_coef<TG>(d, a);
+      advance_pows_once(a, sk);
+    }
+    __syncthreads();
+    const Coef k = sk;
     for (int e = threadIdx.x; e < n; e += kAdamThreads) {
       float p = kMaster ? mp_ptr[e] : Conv<T>::to_f32(p_ptr[e]);
       const float g = unscale_grad<TG>(Conv<TG>::to_f32(g_ptr[e]), k);
@@ -171,6 +205,7 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
       else if (go_ptr) go_ptr[e] = Conv<TG>::from_f32(g);
     }
   }
+
 }
 
 struct PowPair {

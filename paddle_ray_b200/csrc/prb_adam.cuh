@@ -36,6 +36,11 @@ struct AdamArgs {
   const float* loss_scale;   // AMP: g = T(MT(g) * inv), inv = float(1.0 / double(*loss_scale)); nullptr = off
   const float* clip;         // global-norm clip: g = T(MT(g) * MT(T(*clip))); nullptr = off
   int32_t zero_grad;         // 1: store zeros to grad after consuming it (clear_grad folded in)
+  // Shared beta-pow accumulators advanced by the LAST CTA to finish (ticket counter), which removes
+  // the separate 1-thread launch: every CTA has read the old value before it takes its ticket.
+  float* pow_b1;             // nullptr = off
+  float* pow_b2;
+  unsigned int* pow_ticket;  // zero-initialised device counter, reset by the last CTA
 };
 
 // Elements per CTA of the active launch geometry (threads * kVec * lane-vectors per thread).

@@ -15,9 +15,23 @@
 namespace prb {
 namespace {
 
-constexpr int kMapThreads = 256;
-constexpr int kMapUnroll = 4;
-static_assert(kMapChunk == kMapThreads * kVec * kMapUnroll, "chunk size");
+// Launch geometry variants {threads, lane-vectors per thread, min CTAs per SM}; PRB_MAP_VARIANT selects
+// one at load time (tuning aid), the default is the measured best (profiles/).
+struct MapVariant {
+  int threads, unroll, min_blocks;
+};
+constexpr MapVariant kMapVariants[] = {{256, 4, 2}, {256, 2, 4}, {256, 1, 8}, {128, 1, 16}, {128, 2, 8}, {512, 1, 4}};
+constexpr int kNumMapVariants = sizeof(kMapVariants) / sizeof(kMapVariants[0]);
+constexpr int kDefaultMapVariant = 0;
+
+int active_map_variant() {
+  static int v = [] {
+    const char* e = getenv("PRB_MAP_VARIANT");
+    int x = e ? atoi(e) : kDefaultMapVariant;
+    return (x < 0 || x >= kNumMapVariants) ? kDefaultMapVariant : x;
+  }();
+  return v;
+}
 
 struct CopyOp {
   template <typename T>
@@ -38,9 +52,10 @@ struct ScaleOp {
   }
 };
 
-template <typename T, typename Op>
-__global__ void __launch_bounds__(kMapThreads) map_chunks_kernel(const MapDesc* __restrict__ descs,
-                                                                 const Chunk* __restrict__ chunks, const Op op) {
+template <typename T, typename Op, int kMapThreads, int kMapUnroll, int kMinBlocks>
+__global__ void __launch_bounds__(kMapThreads, kMinBlocks) map_chunks_kernel(const MapDesc* __restrict__ descs,
+                                                                             const Chunk* __restrict__ chunks,
+                                                                             const Op op) {
   const int4 craw = __ldg(reinterpret_cast<const int4*>(chunks) + blockIdx.x);
   const int n = craw.y;
   const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
@@ -76,13 +91,27 @@ __global__ void __launch_bounds__(kMapThreads) map_chunks_kernel(const MapDesc* 
 template <typename T, typename Op>
 int32_t launch_map_typed(const DeviceTable& tab, const Op& op, cudaStream_t stream) {
   if (tab.nchunks == 0) return PRB_SUCCESS;
-  map_chunks_kernel<T, Op><<<tab.nchunks, kMapThreads, 0, stream>>>(reinterpret_cast<const MapDesc*>(tab.descs),
-                                                                    tab.chunks, op);
+  const MapDesc* d = reinterpret_cast<const MapDesc*>(tab.descs);
+#define PRB_MAP(T_, U_, B_) map_chunks_kernel<T, Op, T_, U_, B_><<<tab.nchunks, T_, 0, stream>>>(d, tab.chunks, op)
+  switch (active_map_variant()) {
+    case 0: PRB_MAP(256, 4, 2); break;
+    case 1: PRB_MAP(256, 2, 4); break;
+    case 2: PRB_MAP(256, 1, 8); break;
+    case 3: PRB_MAP(128, 1, 16); break;
+    case 4: PRB_MAP(128, 2, 8); break;
+    default: PRB_MAP(512, 1, 4); break;
+  }
+#undef PRB_MAP
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 
 }  // namespace
+
+int map_chunk_elems() {
+  const MapVariant v = kMapVariants[active_map_variant()];
+  return v.threads * kVec * v.unroll;
+}
 
 bool map_aligned(const void* src, const void* dst, int elem_size) {
   const uintptr_t a = (uintptr_t)elem_size * kVec;
@@ -124,7 +153,7 @@ int32_t prb_scale(const PRB_Tensor* x, double scale, float bias, int32_t bias_af
   d.dst = out->data;
   d.aligned = map_aligned(d.src, d.dst, dtype_size(x->dtype)) ? 1 : 0;
   DeviceTable tab;
-  PRB_TRY(get_table(&d, sizeof(d), 1, &x->numel, kMapChunk, (cudaStream_t)stream, &tab));
+  PRB_TRY(get_table(&d, sizeof(d), 1, &x->numel, map_chunk_elems(), (cudaStream_t)stream, &tab));
   return launch_scale(x->dtype, tab, scale, bias, bias_after_scale != 0, (cudaStream_t)stream);
 }
 
@@ -161,7 +190,7 @@ static int32_t concat_split(const PRB_Tensor* flat, const PRB_Tensor* parts, int
               (long long)off, (long long)flat->numel);
   if (descs.empty()) return PRB_SUCCESS;
   DeviceTable tab;
-  PRB_TRY(get_table(descs.data(), sizeof(MapDesc), (int)descs.size(), numels.data(), kMapChunk, stream, &tab));
+  PRB_TRY(get_table(descs.data(), sizeof(MapDesc), (int)descs.size(), numels.data(), map_chunk_elems(), stream, &tab));
   return launch_copy(es, tab, stream);
 }
 

@@ -13,7 +13,8 @@ struct alignas(16) MapDesc {
 };
 static_assert(sizeof(MapDesc) == 32, "MapDesc layout");
 
-constexpr int kMapChunk = 256 * kVec * 4;  // 8192 elements per CTA
+// Elements per CTA of the active launch geometry.
+int map_chunk_elems();
 
 bool map_aligned(const void* src, const void* dst, int elem_size);
 // Pure bit copy of 2- or 4-byte elements.

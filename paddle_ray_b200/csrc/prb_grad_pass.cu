@@ -7,8 +7,26 @@
 namespace prb {
 namespace {
 
-template <typename T, bool kWrite, bool kNorm, bool kMp>
-__global__ void __launch_bounds__(kGradThreads) grad_pass_kernel(const GradDesc* __restrict__ descs,
+// Launch geometry variants {threads, lane-vectors per thread, min CTAs per SM}; PRB_GRAD_VARIANT selects
+// one at load time (tuning aid), the default is the measured best (profiles/).
+struct GradVariant {
+  int threads, unroll, min_blocks;
+};
+constexpr GradVariant kGradVariants[] = {{256, 4, 2}, {256, 2, 4}, {256, 1, 8}, {128, 1, 16}, {128, 2, 8}};
+constexpr int kNumGradVariants = sizeof(kGradVariants) / sizeof(kGradVariants[0]);
+constexpr int kDefaultGradVariant = 0;
+
+int active_grad_variant() {
+  static int v = [] {
+    const char* e = getenv("PRB_GRAD_VARIANT");
+    int x = e ? atoi(e) : kDefaultGradVariant;
+    return (x < 0 || x >= kNumGradVariants) ? kDefaultGradVariant : x;
+  }();
+  return v;
+}
+
+template <typename T, bool kWrite, bool kNorm, bool kMp, int kGradThreads, int kGradUnroll, int kMinBlocks>
+__global__ void __launch_bounds__(kGradThreads, kMinBlocks) grad_pass_kernel(const GradDesc* __restrict__ descs,
                                                                  const Chunk* __restrict__ chunks,
                                                                  const float* __restrict__ loss_scale,
                                                                  bool* __restrict__ found_inf,
@@ -164,6 +182,8 @@ __global__ void __launch_bounds__(kFinThreads) norm_finalize_kernel(const NormFi
   }
 }
 
+constexpr int kGradThreads = 256;  // geometry of the (rare) clip-multiply and zero-fill passes
+
 template <typename T>
 __global__ void __launch_bounds__(kGradThreads) clip_mul_kernel(const GradDesc* __restrict__ descs,
                                                                 const Chunk* __restrict__ chunks,
@@ -178,20 +198,12 @@ __global__ void __launch_bounds__(kGradThreads) clip_mul_kernel(const GradDesc* 
   T* __restrict__ x = reinterpret_cast<T*>(d->out) + offset;
   if (d->aligned) {
     const int nvec = n / kVec;
-    Pack<T> v[kGradUnroll];
+    for (int i = threadIdx.x; i < nvec; i += kGradThreads) {  // works for any chunk size of the shared table
+      Pack<T> v;
+      load_vec<T>(x + i * kVec, v);
 #pragma unroll
-    for (int u = 0; u < kGradUnroll; ++u) {
-      const int i = u * kGradThreads + threadIdx.x;
-      if (i < nvec) load_vec<T>(x + i * kVec, v[u]);
-    }
-#pragma unroll
-    for (int u = 0; u < kGradUnroll; ++u) {
-      const int i = u * kGradThreads + threadIdx.x;
-      if (i < nvec) {
-#pragma unroll
-        for (int j = 0; j < kVec; ++j) v[u].v[j] = Conv<T>::from_f32(__fmul_rn(Conv<T>::to_f32(v[u].v[j]), c));
-        store_vec<T>(x + i * kVec, v[u]);
-      }
+      for (int j = 0; j < kVec; ++j) v.v[j] = Conv<T>::from_f32(__fmul_rn(Conv<T>::to_f32(v.v[j]), c));
+      store_vec<T>(x + i * kVec, v);
     }
     const int e = nvec * kVec + threadIdx.x;
     if (e < n) x[e] = Conv<T>::from_f32(__fmul_rn(Conv<T>::to_f32(x[e]), c));
@@ -244,7 +256,18 @@ int32_t launch_pass_typed(const DeviceTable& tab, bool write, bool norm, bool mp
                           float* partials, cudaStream_t stream) {
   if (tab.nchunks == 0) return PRB_SUCCESS;
   const GradDesc* d = reinterpret_cast<const GradDesc*>(tab.descs);
-#define PRB_GP(W, N, M) grad_pass_kernel<T, W, N, M><<<tab.nchunks, kGradThreads, 0, stream>>>(d, tab.chunks, ls, found, partials)
+#define PRB_GPV(W, N, M, T_, U_, B_) \
+  grad_pass_kernel<T, W, N, M, T_, U_, B_><<<tab.nchunks, T_, 0, stream>>>(d, tab.chunks, ls, found, partials)
+#define PRB_GP(W, N, M)                                    \
+  do {                                                     \
+    switch (active_grad_variant()) {                       \
+      case 0: PRB_GPV(W, N, M, 256, 4, 2); break;          \
+      case 1: PRB_GPV(W, N, M, 256, 2, 4); break;          \
+      case 2: PRB_GPV(W, N, M, 256, 1, 8); break;          \
+      case 3: PRB_GPV(W, N, M, 128, 1, 16); break;         \
+      default: PRB_GPV(W, N, M, 128, 2, 8); break;         \
+    }                                                      \
+  } while (0)
   if (write && !norm) PRB_GP(true, false, false);
   else if (write && norm && !mp) PRB_GP(true, true, false);
   else if (write && norm && mp) PRB_GP(true, true, true);
@@ -252,11 +275,17 @@ int32_t launch_pass_typed(const DeviceTable& tab, bool write, bool norm, bool mp
   else if (!write && norm && mp) PRB_GP(false, true, true);
   else PRB_GP(false, false, false);
 #undef PRB_GP
+#undef PRB_GPV
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 
 }  // namespace
+
+int grad_chunk_elems() {
+  const GradVariant v = kGradVariants[active_grad_variant()];
+  return v.threads * kVec * v.unroll;
+}
 
 int32_t launch_grad_pass(int32_t dtype, const DeviceTable& tab, bool write, bool norm, bool mp, const float* loss_scale,
                          bool* found_inf, float* partials, cudaStream_t stream) {
@@ -306,7 +335,7 @@ int32_t grad_table(const PRB_Tensor* xs, const PRB_Tensor* outs, int64_t num, in
     numels.push_back(xs[i].numel);
     if (index_of) index_of->push_back(i);
   }
-  return get_table(descs.data(), sizeof(GradDesc), (int)descs.size(), numels.data(), kGradChunk, stream, tab);
+  return get_table(descs.data(), sizeof(GradDesc), (int)descs.size(), numels.data(), grad_chunk_elems(), stream, tab);
 }
 
 }  // namespace
@@ -455,7 +484,7 @@ int32_t prb_update_loss_scaling(const PRB_Tensor* xs, int64_t num, const PRB_Ten
       }
       if (descs.empty()) continue;
       DeviceTable tab;
-      PRB_TRY(get_table(descs.data(), sizeof(GradDesc), (int)descs.size(), numels.data(), kGradChunk, stream, &tab));
+      PRB_TRY(get_table(descs.data(), sizeof(GradDesc), (int)descs.size(), numels.data(), grad_chunk_elems(), stream, &tab));
       if (tab.nchunks == 0) continue;
       const GradDesc* d = reinterpret_cast<const GradDesc*>(tab.descs);
       if (es == 4) fill_zero_if_kernel<uint32_t><<<tab.nchunks, kGradThreads, 0, stream>>>(d, tab.chunks, flag);

@@ -21,9 +21,7 @@ struct alignas(16) GradDesc {
 };
 static_assert(sizeof(GradDesc) == 32, "GradDesc layout");
 
-constexpr int kGradThreads = 256;
-constexpr int kGradUnroll = 4;
-constexpr int kGradChunk = kGradThreads * kVec * kGradUnroll;  // 8192 elements per CTA
+int grad_chunk_elems();      // elements per CTA of the active grad-pass launch geometry
 
 // write: store T(MT(x) * inv) to out; norm: accumulate squares into partials[chunk];
 // mp: squares kept in fp32 (clip.py:195-202) instead of rounded to T.

@@ -91,10 +91,12 @@ int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const i
   e.device = dev;
   e.image.swap(image);
   PRB_CUDA(cudaMalloc(&e.dev_blob, blob_bytes));
-  // Blocking copy: a plan is built once and may then be used from any stream (calc or comm), so it
-  // must be complete before this call returns.  Plan creation is a warm-up event, never per step.
-  (void)stream;
-  PRB_CUDA(cudaMemcpy(e.dev_blob, blob.data(), blob_bytes, cudaMemcpyHostToDevice));
+  // A plan is built once and may then be used from any stream (calc or comm), so the upload must be
+  // COMPLETE before this call returns: enqueue on the caller's stream, then wait for that stream.
+  // (A plain cudaMemcpy from pageable memory may return while its DMA is still in flight on the legacy
+  // stream, which non-blocking streams do not wait for.)  Plan creation is a warm-up event, never per step.
+  PRB_CUDA(cudaMemcpyAsync(e.dev_blob, blob.data(), blob_bytes, cudaMemcpyHostToDevice, stream));
+  PRB_CUDA(cudaStreamSynchronize(stream));
   e.table.descs = (const uint8_t*)e.dev_blob + descs_off;
   e.table.chunks = (const Chunk*)((const uint8_t*)e.dev_blob + chunks_off);
   e.table.first_chunk = (const int32_t*)((const uint8_t*)e.dev_blob + first_off);

@@ -132,6 +132,14 @@ struct PRB_Reducer {
   bool unpack = true;
   bool find_unused = false;
   bool dry = false;  // host-only: state machine without device work (comm == NULL)
+  // Batch mode (prb_reducer_mark_vars_ready with one rank): groups that complete inside one call are
+  // packed by ONE launch instead of one launch per group -- with nothing to communicate there is no
+  // pipelining to preserve.
+  bool batching = false;
+  std::vector<size_t> batch;
+  std::vector<size_t> batch_key;
+  DeviceTable batch_pack_tab, batch_unpack_tab;
+  bool batch_valid = false;
   std::vector<int64_t> launched;
 };
 
@@ -152,7 +160,7 @@ int32_t group_tables(PRB_Reducer* r, Group& g, bool for_unpack, cudaStream_t str
     descs.push_back(d);
     numels.push_back(r->grads[v].numel);
   }
-  return get_table(descs.data(), sizeof(MapDesc), (int)descs.size(), numels.data(), kMapChunk, stream, tab);
+  return get_table(descs.data(), sizeof(MapDesc), (int)descs.size(), numels.data(), map_chunk_elems(), stream, tab);
 }
 
 // ref: FusedAllReduceSchedule reducer.cc:1037-1070 ("concat > div_nranks > allreduce > split")
@@ -164,6 +172,12 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   }
   PRB_Comm* c = r->comm;
   const int es = dtype_size(g.dtype);
+  if (r->batching && c->nranks == 1 && !g.has_unused && !g.pack_had_unused &&
+      (r->batch.empty() || r->groups[r->batch.front()].dtype == g.dtype)) {
+    r->batch.push_back(gi);
+    r->launched.push_back((int64_t)gi);
+    return PRB_SUCCESS;
+  }
   char* region = r->arena + g.arena_off;
   if (g.has_unused) {
     for (size_t s = 0; s < g.vars.size(); ++s)
@@ -200,6 +214,44 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
     PRB_TRY(launch_copy(es, g.unpack_tab, calc));
   }
   r->launched.push_back((int64_t)gi);
+  return PRB_SUCCESS;
+}
+
+int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
+  if (r->batch.empty()) return PRB_SUCCESS;
+  if (!r->batch_valid || r->batch_key != r->batch) {
+    std::vector<MapDesc> pack, unpack;
+    std::vector<int64_t> numels;
+    for (size_t gi : r->batch) {
+      Group& g = r->groups[gi];
+      const int es = dtype_size(g.dtype);
+      for (size_t s = 0; s < g.vars.size(); ++s) {
+        const int64_t v = g.vars[s];
+        char* slot = r->arena + g.arena_off + (size_t)g.slot_off[s] * es;
+        MapDesc d{};
+        d.src = r->grads[v].data;
+        d.dst = slot;
+        d.aligned = map_aligned(d.src, d.dst, es) ? 1 : 0;
+        pack.push_back(d);
+        MapDesc u{};
+        u.src = slot;
+        u.dst = r->grads[v].data;
+        u.aligned = d.aligned;
+        unpack.push_back(u);
+        numels.push_back(r->grads[v].numel);
+      }
+    }
+    PRB_TRY(get_table(pack.data(), sizeof(MapDesc), (int)pack.size(), numels.data(), map_chunk_elems(), calc,
+                      &r->batch_pack_tab));
+    PRB_TRY(get_table(unpack.data(), sizeof(MapDesc), (int)unpack.size(), numels.data(), map_chunk_elems(), calc,
+                      &r->batch_unpack_tab));
+    r->batch_key = r->batch;
+    r->batch_valid = true;
+  }
+  const int32_t dt = r->groups[r->batch.front()].dtype;
+  r->batch.clear();
+  PRB_TRY(launch_scale(dt, r->batch_pack_tab, 1.0, 0.0f, false, calc));  // 1.0 / nranks with one rank
+  if (r->unpack) PRB_TRY(launch_copy(dtype_size(dt), r->batch_unpack_tab, calc));
   return PRB_SUCCESS;
 }
 
@@ -537,8 +589,14 @@ int32_t prb_reducer_mark_var_ready(PRB_Reducer* r, int64_t v, void* stream) {
 }
 
 int32_t prb_reducer_mark_vars_ready(PRB_Reducer* r, const int64_t* var_indices, int64_t num, void* stream) {
-  for (int64_t i = 0; i < num; ++i) PRB_TRY(prb_reducer_mark_var_ready(r, var_indices[i], stream));
-  return PRB_SUCCESS;
+  PRB_ENFORCE(r && (var_indices || num == 0), PRB_INVALID_ARGUMENT, "reducer: bad arguments");
+  r->batching = !r->dry;
+  int32_t st = PRB_SUCCESS;
+  for (int64_t i = 0; i < num && st == PRB_SUCCESS; ++i) st = prb_reducer_mark_var_ready(r, var_indices[i], stream);
+  r->batching = false;
+  if (st == PRB_SUCCESS && !r->dry) st = flush_batch(r, (cudaStream_t)stream);
+  r->batch.clear();
+  return st;
 }
 
 int32_t prb_reducer_set_unpack(PRB_Reducer* r, int32_t enabled) {

@@ -72,6 +72,23 @@ int32_t workspace(size_t bytes, void** out, int slot) {
   return PRB_SUCCESS;
 }
 
+int32_t ticket_counter(void** out) {
+  int dev = 0;
+  PRB_CUDA(cudaGetDevice(&dev));
+  static std::mutex mu;
+  static std::unordered_map<int, void*> counters;
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = counters.find(dev);
+  if (it == counters.end()) {
+    void* p = nullptr;
+    PRB_CUDA(cudaMalloc(&p, 256));
+    PRB_CUDA(cudaMemset(p, 0, 256));
+    it = counters.emplace(dev, p).first;
+  }
+  *out = it->second;
+  return PRB_SUCCESS;
+}
+
 int32_t host_staging(size_t bytes, void** out, int slot) {
   std::lock_guard<std::mutex> lk(g_ws_mu);
   if ((int)g_host_ws.size() <= slot) g_host_ws.resize(slot + 1);

@@ -94,7 +94,7 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   if (cfg->use_amp) PRB_CUDA(cudaMemsetAsync(found, 0, 1, stream));
   if (cfg->use_amp || cfg->use_clip) {
     DeviceTable gt;
-    PRB_TRY(get_table(gdescs.data(), sizeof(GradDesc), (int)num, numels.data(), kGradChunk, stream, &gt));
+    PRB_TRY(get_table(gdescs.data(), sizeof(GradDesc), (int)num, numels.data(), grad_chunk_elems(), stream, &gt));
     float* partials = nullptr;
     float* scratch_clip = nullptr;
     if (cfg->use_clip) {
@@ -139,7 +139,11 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   a.loss_scale = ls;
   a.clip = clip_dev;
   a.zero_grad = cfg->zero_grads;
-  PRB_TRY(launch_adam(dt_p, dt_g, master, a, stream));
-  return beta_pow_update_device(beta1_pow, beta2_pow, nullptr, nullptr, 1, (float)cfg->beta1, (float)cfg->beta2, found,
-                                stream);
+  // beta-pow accumulators advance inside the update kernel (last-CTA ticket) unless found_inf
+  void* tk = nullptr;
+  PRB_TRY(ticket_counter(&tk));
+  a.pow_b1 = reinterpret_cast<float*>(beta1_pow->data);
+  a.pow_b2 = reinterpret_cast<float*>(beta2_pow->data);
+  a.pow_ticket = reinterpret_cast<unsigned int*>(tk);
+  return launch_adam(dt_p, dt_g, master, a, stream);
 }
