@@ -1,0 +1,68 @@
+"""One rank of the multi-GPU parity check (launched by tests/test_gpu_multi.py or by hand under torchrun).
+
+Mirrors the reference's parallel_dygraph_gradient_check_in_eager_mode.py:139-150: gradients must be EQUAL
+across ranks after the sync; here additionally equal to the oracle's scale-then-sum for 2 ranks (order cannot
+matter with two addends) and within tolerance for more.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import paddle_ray_b200 as prb  # noqa: E402
+from oracle import oracle as orc  # noqa: E402
+
+
+def main(out_dir):
+    group = prb.distributed.init_parallel_env()
+    rank, n = group.rank, group.nranks
+    sizes = [64, 64, 3 * 3 * 64 * 16, 1000, 7, 4096, 4097, 250000, 1, 300000]
+    for dtype in (orc.F32, orc.BF16):
+        params, grads_all = [], []
+        for i, sz in enumerate(sizes):
+            p = prb.Tensor.from_numpy(orc.from_f32(np.random.default_rng(100 + i).normal(0, 0.02, sz).astype(np.float32), dtype),
+                                      dtype, name="w_%d" % i)
+            per_rank = [orc.from_f32(np.random.default_rng(1000 * r + i).normal(0, 1e-2, sz).astype(np.float32), dtype)
+                        for r in range(n)]
+            p.grad = prb.Tensor.from_numpy(per_rank[rank], dtype)
+            params.append(p)
+            grads_all.append(per_rank)
+        dp = prb.DataParallel(params, comm_buffer_size=0.4, last_comm_buffer_size=0.01)
+        assert len(dp.group_indices) >= 3, dp.group_indices
+        opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, multi_precision=dtype != orc.F32)
+        for step in range(2):
+            dp.prepare_for_backward()
+            # hooks fire one by one, in reverse order, like a backward pass (not the batch call)
+            for i in reversed(range(len(params))):
+                dp.mark_var_ready(i)
+            assert dp.finalized
+            prb.current_stream().synchronize()
+            for i, p in enumerate(params):
+                got = p.grad.numpy()
+                scaled = [orc.to_f32(orc.scale(g, dtype, 1.0 / n), dtype).astype(np.float64) for g in grads_all[i]]
+                want = np.sum(scaled, axis=0)
+                if dtype == orc.F32 and n == 2:
+                    np.testing.assert_array_equal(got, want.astype(np.float32))
+                else:
+                    tol = 1e-6 if dtype == orc.F32 else 1e-2
+                    np.testing.assert_allclose(orc.to_f32(got, dtype), want, rtol=tol, atol=tol * 1e-2)
+                np.save(os.path.join(out_dir, "grad_%d_%d_%d_r%d.npy" % (dtype, step, i, rank)), got)
+                # next step: every rank feeds its own fresh gradient again
+                p.grad.copy_from_numpy(grads_all[i][rank])
+            opt.step()
+        prb.current_stream().synchronize()
+        for i, p in enumerate(params):
+            np.save(os.path.join(out_dir, "param_%d_%d_r%d.npy" % (dtype, i, rank)), p.numpy())
+    # timing helper used by bench.py: max over ranks through the communicator
+    t = prb.Tensor.from_numpy(np.array([float(rank + 1)], np.float32))
+    group.all_reduce(t, "max")
+    assert t.numpy()[0] == float(n)
+    group.barrier()
+    print("rank %d ok" % rank, flush=True)
+
+
+if __name__ == "__main__":
+    main(sys.argv[1])

@@ -1,0 +1,44 @@
+"""Multi-GPU parity (needs >= 2 GPUs on the box; skipped otherwise): NCCL bucket allreduce through DataParallel."""
+import glob
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpus():
+    import paddle_ray_b200 as prb
+    return prb.device_count()
+
+
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+def test_dataparallel_grads_equal_across_ranks(tmp_path, nranks):
+    if _ngpus() < nranks:
+        pytest.skip("needs %d GPUs" % nranks)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    procs = []
+    for r in range(nranks):
+        env = {**os.environ, "RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(nranks), "MASTER_ADDR": "127.0.0.1",
+               "MASTER_PORT": str(port)}
+        procs.append(subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "dist_worker.py"), str(tmp_path)],
+                                      env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+    outs = [p.communicate(timeout=600)[0].decode() for p in procs]
+    for r, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, "rank %d failed:\n%s" % (r, o[-3000:])
+    # grads and updated params are bit-equal across ranks (ref parallel_dygraph_gradient_check_in_eager_mode.py:139-150)
+    files = sorted(glob.glob(os.path.join(str(tmp_path), "*_r0.npy")))
+    assert files
+    for f0 in files:
+        a = np.load(f0)
+        for r in range(1, nranks):
+            b = np.load(f0.replace("_r0.npy", "_r%d.npy" % r))
+            assert a.tobytes() == b.tobytes(), os.path.basename(f0)
