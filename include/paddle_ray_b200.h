@@ -143,6 +143,21 @@ int32_t prb_update_loss_scaling(const PRB_Tensor* xs, int64_t num, const PRB_Ten
  * workspace (grown with cudaMalloc when needed). */
 int32_t prb_squared_l2_norm(const PRB_Tensor* x, PRB_Tensor* out, void* stream);
 
+/* Same result as prb_squared_l2_norm for callers that cannot allocate device memory when they need a
+ * norm: code running inside a process whose memory pool already owns the whole GPU, sections that must
+ * not block on cudaMalloc/cudaFree, out-of-memory handlers.  This entry point has NO counterpart in the
+ * reference (its reduce kernels always allocate a temporary); it exists for those callers only.
+ *  - It never calls cudaMalloc/cudaFree: the partial sums live in a fixed array inside the library image
+ *    (~128 KiB of device memory on every GPU that loads the library, held until the process exits).
+ *  - x may have at most PRB_NOALLOC_MAX_NUMEL elements; more is rejected with PRB_INVALID_ARGUMENT.
+ *  - x and out must live on the CURRENT device.  The first call on each device resolves the array's
+ *    address (cudaGetSymbolAddress); make that call at start-up, before any stream capture.
+ *  - Every call on a device shares the array.  A call overwrites what it later reads, so nothing needs
+ *    clearing between calls, but two calls that overlap on the GPU (different streams) corrupt each
+ *    other: keep them on one stream or order them with events. */
+#define PRB_NOALLOC_MAX_NUMEL 268435456LL /* 32768 chunks x 8192 elements */
+int32_t prb_squared_l2_norm_noalloc(const PRB_Tensor* x, PRB_Tensor* out, void* stream);
+
 /* Multi-tensor form of the per-gradient loop in ClipGradByGlobalNorm._dygraph_clip
  * (ref: python/paddle/nn/clip.py:643-736): per-tensor squared norms (typed like the op),
  * their grouped sum, sqrt, clip = max_norm / max(norm, max_norm) (or the auto_skip_clip rule),

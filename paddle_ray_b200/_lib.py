@@ -61,6 +61,7 @@ SIGNATURES = {
     "prb_check_finite_and_unscale": [_T, _i64, _T, _T, _T, _vp],
     "prb_update_loss_scaling": [_T, _i64, _T, _T, _T, _T, _i32, _i32, _f32, _f32, _i32, _T, _T, _T, _T, _vp],
     "prb_squared_l2_norm": [_T, _T, _vp],
+    "prb_squared_l2_norm_noalloc": [_T, _T, _vp],
     "prb_clip_grad_by_global_norm": [_T, _i64, _f32, _i32, _i32, _T, _T, _vp],
     "prb_scale": [_T, _f64, _f32, _i32, _T, _vp],
     "prb_concat": [_T, _i64, _T, _vp],
