@@ -251,6 +251,15 @@ int32_t prb_reducer_mark_vars_ready(PRB_Reducer* r, const int64_t* var_indices, 
 /* 1 -> split reduced buckets back into the grads at finalize (reference behaviour, default);
  * 0 -> leave them in the arena for prb_dp_step_tail to consume directly. */
 int32_t prb_reducer_set_unpack(PRB_Reducer* r, int32_t enabled);
+/* Pipelined consumption.  With deferred waiting enabled, finalising no longer makes the calc stream wait
+ * for every bucket (ref: FinalizeBackward reducer.cc:1013-1035 waits for all tasks); instead the consumer
+ * calls prb_reducer_wait_group(r, k, stream) right before it touches the k-th LAUNCHED group's slots, so the
+ * optimizer update of early buckets overlaps the allreduce of later ones. */
+int32_t prb_reducer_set_deferred_wait(PRB_Reducer* r, int32_t enabled);
+int32_t prb_reducer_wait_group(PRB_Reducer* r, int64_t group_index, void* stream);
+int32_t prb_reducer_num_groups(const PRB_Reducer* r);
+/* Index (in launch order, i.e. as passed to prb_reducer_create) of the group that holds parameter i. */
+int32_t prb_reducer_group_of(const PRB_Reducer* r, int64_t var_index, int64_t* out_group);
 /* 1 when every group of the current backward has been launched and finalised. */
 int32_t prb_reducer_is_finalized(const PRB_Reducer* r);
 /* Device address / element offset of parameter i's slot inside the bucket arena. */
@@ -278,6 +287,8 @@ typedef struct PRB_TailConfig {
   int32_t use_mp_type;       /* clip norm in fp32 for 16-bit grads (ref: clip.py:179-202) */
   int32_t write_back_grads;  /* 1: store the unscaled (not clipped) gradient back: what p.grad holds in the reference */
   int32_t zero_grads;        /* 1: clear_grad(set_to_zero=True) folded in (ref: optimizer.py:1333-1381) */
+  int32_t keep_beta_pow;     /* 1: do not advance the beta-pow accumulators in this call (a step split into
+                                several calls, one per bucket, advances them in its last call only) */
 } PRB_TailConfig;
 
 /* Per-tensor attributes follow adamw_: lr_ratio[i], with_decay[i] (NULL = 1.0 / all decayed).

@@ -27,7 +27,7 @@ class TailConfig(C.Structure):
         ("beta1", C.c_double), ("beta2", C.c_double), ("epsilon", C.c_double),
         ("coeff", C.c_float), ("use_adamw", C.c_int32), ("multi_precision", C.c_int32), ("use_amp", C.c_int32),
         ("use_clip", C.c_int32), ("clip_norm", C.c_float), ("auto_skip_clip", C.c_int32), ("use_mp_type", C.c_int32),
-        ("write_back_grads", C.c_int32), ("zero_grads", C.c_int32),
+        ("write_back_grads", C.c_int32), ("zero_grads", C.c_int32), ("keep_beta_pow", C.c_int32),
     ]
 
 
@@ -84,6 +84,10 @@ SIGNATURES = {
     "prb_reducer_mark_var_ready": [_vp, _i64, _vp],
     "prb_reducer_mark_vars_ready": [_vp, _vp, _i64, _vp],
     "prb_reducer_set_unpack": [_vp, _i32],
+    "prb_reducer_set_deferred_wait": [_vp, _i32],
+    "prb_reducer_wait_group": [_vp, _i64, _vp],
+    "prb_reducer_num_groups": [_vp],
+    "prb_reducer_group_of": [_vp, _i64, C.POINTER(_i64)],
     "prb_reducer_is_finalized": [_vp],
     "prb_reducer_bucket_view": [_vp, _i64, _T],
     "prb_reducer_launched_groups": [_vp, _vp, _i64, _vp],
@@ -119,7 +123,7 @@ SIGNATURES = {
 _RESTYPES = {"prb_comm_stream": _vp, "prb_launch_count": _i64, "prb_last_error_message": C.c_char_p,
              "prb_version": C.c_char_p}
 # entry points whose int32 return value is a value, not a status
-_VALUE_RETURN = {"prb_comm_nranks", "prb_comm_rank", "prb_reducer_is_finalized"}
+_VALUE_RETURN = {"prb_comm_nranks", "prb_comm_rank", "prb_reducer_is_finalized", "prb_reducer_num_groups"}
 
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)  # AttributeError here == the .so does not export what the header declares

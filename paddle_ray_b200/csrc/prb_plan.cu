@@ -15,6 +15,7 @@ struct Entry {
   std::vector<uint8_t> image;  // host image, compared on hit to rule out hash collisions
   void* dev_blob = nullptr;
   DeviceTable table;
+  bool pinned = false;
 };
 
 std::mutex g_mu;
@@ -34,7 +35,7 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 }  // namespace
 
 int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const int64_t* numels, int chunk_elems,
-                  cudaStream_t stream, DeviceTable* out) {
+                  cudaStream_t stream, DeviceTable* out, bool pin) {
   int dev = 0;
   PRB_CUDA(cudaGetDevice(&dev));
   // host image = [chunk_elems][desc_bytes][descs...][numels...]
@@ -49,6 +50,7 @@ int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const i
   for (auto it = g_lru.begin(); it != g_lru.end(); ++it) {
     if (it->key == key && it->device == dev && it->image == image) {
       g_lru.splice(g_lru.begin(), g_lru, it);
+      g_lru.front().pinned |= pin;
       *out = g_lru.front().table;
       return PRB_SUCCESS;
     }
@@ -83,12 +85,18 @@ int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const i
   memcpy(blob.data() + first_off, first.data(), first.size() * 4);
 
   if (g_lru.size() >= kMaxPlans) {
-    cudaFree(g_lru.back().dev_blob);  // synchronises the device: no kernel still reads the evicted plan
-    g_lru.pop_back();
+    for (auto it = g_lru.end(); it != g_lru.begin();) {  // least recently used entry that nobody holds on to
+      --it;
+      if (it->pinned) continue;
+      cudaFree(it->dev_blob);  // synchronises the device: no kernel still reads the evicted plan
+      g_lru.erase(it);
+      break;
+    }
   }
   Entry e;
   e.key = key;
   e.device = dev;
+  e.pinned = pin;
   e.image.swap(image);
   PRB_CUDA(cudaMalloc(&e.dev_blob, blob_bytes));
   // A plan is built once and may then be used from any stream (calc or comm), so the upload must be

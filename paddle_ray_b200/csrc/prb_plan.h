@@ -21,7 +21,9 @@ struct DeviceTable {
 };
 
 // host_descs: ndescs * desc_bytes bytes.  numels[i]: elements of tensor i (0 allowed -> no chunks).
+// pin: the caller keeps the returned DeviceTable beyond this call (the reducer caches its pack/unpack plans),
+// so the entry is exempt from LRU eviction for the life of the process.
 int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const int64_t* numels, int chunk_elems,
-                  cudaStream_t stream, DeviceTable* out);
+                  cudaStream_t stream, DeviceTable* out, bool pin = false);
 
 }  // namespace prb

@@ -34,6 +34,9 @@ struct NcclApi {
   ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
   ncclResult_t (*GetVersion)(int*) = nullptr;
+  // optional (NCCL >= 2.19): user-buffer registration lets NVLink/NVLS collectives skip staging copies
+  ncclResult_t (*CommRegister)(const ncclComm_t, void*, size_t, void**) = nullptr;
+  ncclResult_t (*CommDeregister)(const ncclComm_t, void*) = nullptr;
 };
 NcclApi g_nccl;
 std::mutex g_nccl_mu;
@@ -61,6 +64,8 @@ int32_t load_nccl() {
   PRB_SYM(GetErrorString, "ncclGetErrorString");
   PRB_SYM(GetVersion, "ncclGetVersion");
 #undef PRB_SYM
+  g_nccl.CommRegister = reinterpret_cast<decltype(g_nccl.CommRegister)>(dlsym(h, "ncclCommRegister"));
+  g_nccl.CommDeregister = reinterpret_cast<decltype(g_nccl.CommDeregister)>(dlsym(h, "ncclCommDeregister"));
   g_nccl.handle = h;
   return PRB_SUCCESS;
 }
@@ -121,6 +126,7 @@ struct PRB_Reducer {
   PRB_Comm* comm = nullptr;
   char* arena = nullptr;
   size_t arena_bytes = 0;
+  void* arena_reg = nullptr;  // ncclCommRegister handle of the arena (NULL when unavailable)
   size_t next_group = 0;
   std::vector<uint8_t> ready;
   std::vector<uint8_t> unused;
@@ -130,6 +136,7 @@ struct PRB_Reducer {
   bool grad_need_hooks = false;
   bool finalized = false;
   bool unpack = true;
+  bool deferred_wait = false;  // the consumer waits per group (prb_reducer_wait_group)
   bool find_unused = false;
   bool dry = false;  // host-only: state machine without device work (comm == NULL)
   // Batch mode (prb_reducer_mark_vars_ready with one rank): groups that complete inside one call are
@@ -160,7 +167,8 @@ int32_t group_tables(PRB_Reducer* r, Group& g, bool for_unpack, cudaStream_t str
     descs.push_back(d);
     numels.push_back(r->grads[v].numel);
   }
-  return get_table(descs.data(), sizeof(MapDesc), (int)descs.size(), numels.data(), map_chunk_elems(), stream, tab);
+  return get_table(descs.data(), sizeof(MapDesc), (int)descs.size(), numels.data(), map_chunk_elems(), stream, tab,
+                   /*pin=*/true);
 }
 
 // ref: FusedAllReduceSchedule reducer.cc:1037-1070 ("concat > div_nranks > allreduce > split")
@@ -242,9 +250,9 @@ int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
       }
     }
     PRB_TRY(get_table(pack.data(), sizeof(MapDesc), (int)pack.size(), numels.data(), map_chunk_elems(), calc,
-                      &r->batch_pack_tab));
+                      &r->batch_pack_tab, /*pin=*/true));
     PRB_TRY(get_table(unpack.data(), sizeof(MapDesc), (int)unpack.size(), numels.data(), map_chunk_elems(), calc,
-                      &r->batch_unpack_tab));
+                      &r->batch_unpack_tab, /*pin=*/true));
     r->batch_key = r->batch;
     r->batch_valid = true;
   }
@@ -259,7 +267,7 @@ int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
 int32_t finalize(PRB_Reducer* r, cudaStream_t calc) {
   r->need_finalize = false;
   r->grad_need_hooks = false;
-  if (!r->dry && r->comm->nranks > 1)
+  if (!r->dry && r->comm->nranks > 1 && !r->deferred_wait)
     for (Group& g : r->groups) PRB_CUDA(cudaStreamWaitEvent(calc, g.done, 0));
   r->finalized = true;
   return PRB_SUCCESS;
@@ -521,6 +529,11 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
     prb_reducer_destroy(r);
     PRB_FAIL(PRB_EXTERNAL, "reducer_create: CUDA error %s", cudaGetErrorString(e));
   }
+  // The persistent arena is registered with the communicator once (the reference's per-step buckets never
+  // can be): NCCL then reduces straight out of it over NVLink / NVLS without staging copies.
+  if (comm->nranks > 1 && g_nccl.CommRegister != nullptr && getenv("PRB_NO_NCCL_REGISTER") == nullptr) {
+    if (g_nccl.CommRegister(comm->comm, r->arena, arena, &r->arena_reg) != ncclSuccess) r->arena_reg = nullptr;
+  }
   r->finalized = true;  // nothing pending before the first prepare_for_backward
   *out = r;
   return PRB_SUCCESS;
@@ -529,6 +542,7 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
 int32_t prb_reducer_destroy(PRB_Reducer* r) {
   if (!r) return PRB_SUCCESS;
   if (!r->dry) cudaDeviceSynchronize();
+  if (r->arena_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(r->comm->comm, r->arena_reg);
   for (Group& g : r->groups) {
     if (g.ready) cudaEventDestroy(g.ready);
     if (g.done) cudaEventDestroy(g.done);
@@ -606,6 +620,30 @@ int32_t prb_reducer_set_unpack(PRB_Reducer* r, int32_t enabled) {
 }
 
 int32_t prb_reducer_is_finalized(const PRB_Reducer* r) { return r && r->finalized ? 1 : 0; }
+
+int32_t prb_reducer_set_deferred_wait(PRB_Reducer* r, int32_t enabled) {
+  PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  r->deferred_wait = enabled != 0;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_wait_group(PRB_Reducer* r, int64_t gi, void* stream) {
+  PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  PRB_ENFORCE(gi >= 0 && gi < (int64_t)r->groups.size(), PRB_OUT_OF_RANGE, "Out of bounds group index %lld", (long long)gi);
+  PRB_ENFORCE((size_t)gi < r->next_group, PRB_PRECONDITION_NOT_MET,
+              "group %lld has not been launched in this backward yet", (long long)gi);
+  if (!r->dry && r->comm->nranks > 1) PRB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, r->groups[(size_t)gi].done, 0));
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_num_groups(const PRB_Reducer* r) { return r ? (int32_t)r->groups.size() : 0; }
+
+int32_t prb_reducer_group_of(const PRB_Reducer* r, int64_t v, int64_t* out_group) {
+  PRB_ENFORCE(r && out_group, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
+  PRB_ENFORCE(v >= 0 && v < (int64_t)r->locator.size(), PRB_OUT_OF_RANGE, "Out of bounds variable index %lld", (long long)v);
+  *out_group = r->locator[(size_t)v].first;
+  return PRB_SUCCESS;
+}
 
 int32_t prb_reducer_bucket_view(const PRB_Reducer* r, int64_t v, PRB_Tensor* out) {
   PRB_ENFORCE(r && out, PRB_INVALID_ARGUMENT, "reducer: bad arguments");

@@ -105,9 +105,15 @@ int32_t host_staging(size_t bytes, void** out, int slot) {
   return PRB_SUCCESS;
 }
 
-__global__ void spin_kernel(long long cycles) {
-  const long long t0 = clock64();
-  while (clock64() - t0 < cycles) {
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__global__ void spin_kernel(unsigned long long ns) {
+  const unsigned long long t0 = global_ns();
+  while (global_ns() - t0 < ns) {
   }
 }
 
@@ -255,11 +261,7 @@ int32_t prb_flag_or(void* dst, const void* src, void* stream) {
 
 int32_t prb_spin(int64_t microseconds, void* stream) {
   PRB_TRY(require_device());
-  int dev = 0, khz = 0;
-  PRB_CUDA(cudaGetDevice(&dev));
-  PRB_CUDA(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
-  long long cycles = (long long)microseconds * (long long)khz / 1000;
-  spin_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(cycles);
+  spin_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((unsigned long long)(microseconds > 0 ? microseconds : 0) * 1000ull);
   PRB_CUDA(cudaGetLastError());  // bench scaffolding: not counted as a hot-path launch
   return PRB_SUCCESS;
 }

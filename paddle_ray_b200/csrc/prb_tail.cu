@@ -142,8 +142,10 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   // beta-pow accumulators advance inside the update kernel (last-CTA ticket) unless found_inf
   void* tk = nullptr;
   PRB_TRY(ticket_counter(&tk));
-  a.pow_b1 = reinterpret_cast<float*>(beta1_pow->data);
-  a.pow_b2 = reinterpret_cast<float*>(beta2_pow->data);
-  a.pow_ticket = reinterpret_cast<unsigned int*>(tk);
+  if (!cfg->keep_beta_pow) {
+    a.pow_b1 = reinterpret_cast<float*>(beta1_pow->data);
+    a.pow_b2 = reinterpret_cast<float*>(beta2_pow->data);
+    a.pow_ticket = reinterpret_cast<unsigned int*>(tk);
+  }
   return launch_adam(dt_p, dt_g, master, a, stream);
 }

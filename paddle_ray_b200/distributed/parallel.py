@@ -206,6 +206,17 @@ class EagerReducer:
     def set_unpack(self, enabled: bool):
         call("prb_reducer_set_unpack", self.handle, int(bool(enabled)))
 
+    def set_deferred_wait(self, enabled: bool):
+        call("prb_reducer_set_deferred_wait", self.handle, int(bool(enabled)))
+
+    def wait_group(self, group_index: int, stream=None):
+        call("prb_reducer_wait_group", self.handle, int(group_index), core._stream_handle(stream))
+
+    def group_of(self, var_index: int) -> int:
+        g = C.c_int64()
+        call("prb_reducer_group_of", self.handle, int(var_index), C.byref(g))
+        return int(g.value)
+
     @property
     def finalized(self) -> bool:
         return bool(lib.prb_reducer_is_finalized(self.handle))
@@ -274,6 +285,7 @@ class DataParallel:
         self.last_comm_buffer_size = int(last_comm_buffer_size * 1024 * 1024)
         self.init_reducer()
         self._consume = False
+        self.pipelined = False
         if consume_from_buckets:
             self.consume_from_buckets(True)
 
@@ -288,9 +300,30 @@ class DataParallel:
         self._reverse_order = (C.c_int64 * len(self._parameters))(*reversed(range(len(self._parameters))))
 
     def consume_from_buckets(self, enabled: bool = True):
+        """Leave the reduced gradients in the bucket arena and let the optimizer read them there.
+
+        Each parameter gets ``_reduced_grad`` (the view of its slot) and ``_bucket`` (this wrapper and the
+        launch-order index of its group).  With more than one rank the calc stream no longer waits for every
+        bucket at the end of backward; the optimizer waits per bucket instead (``wait_group``)."""
         self._consume = bool(enabled)
         self._reducer.set_unpack(not self._consume)
+        self.pipelined = self._consume and self.group.nranks > 1
+        self._reducer.set_deferred_wait(self.pipelined)
         self._bucket_grads = [self._reducer.bucket_view(i) for i in range(len(self._parameters))] if enabled else None
+        for i, p in enumerate(self._parameters):
+            if enabled:
+                p._reduced_grad = self._bucket_grads[i]
+                p._bucket = (self, self._reducer.group_of(i))
+            else:
+                p._reduced_grad = None
+                p._bucket = (None, 0)
+
+    def wait_group(self, group_index: int, stream=None):
+        self._reducer.wait_group(group_index, stream)
+
+    def wait_all_groups(self, stream=None):
+        for gi in range(len(self.group_indices)):
+            self._reducer.wait_group(gi, stream)
 
     def bucket_grads(self):
         return self._bucket_grads

@@ -79,7 +79,7 @@ class Optimizer:
         self._lr_tensor = None
         self._lr_value = None
         self._lr_feeder = None
-        self._fused_cache = None
+        self._fused_cache = {}
         # True folds clear_grad(set_to_zero=True) into the update pass (gradients are zeroed as they are consumed)
         self._zero_grads_in_step = False
         # True keeps p.grad reference-visible after an AMP step (the unscaled gradient is stored back)
@@ -185,13 +185,32 @@ class Optimizer:
         clip = self._grad_clip
         if clip is not None and not all(getattr(p, "need_clip", True) is not False for p, _ in pg):
             return self._per_tensor_step(pg, found_inf, loss_scale)
+        # Gradients that sit in a DataParallel bucket arena of a multi-rank job: without a global dependency
+        # (no clip, no AMP) each bucket's parameters are updated as soon as THAT bucket's allreduce is done,
+        # overlapping the allreduce of the buckets behind it.
+        dp = getattr(pg[0][0], "_bucket", (None, 0))[0]
+        if dp is not None and dp.pipelined:
+            if clip is None and loss_scale is None and found_inf is None:
+                by_group = {}
+                for p, g in pg:
+                    by_group.setdefault(p._bucket[1], []).append((p, g))
+                order = sorted(by_group)
+                for k, gi in enumerate(order):
+                    dp.wait_group(gi)
+                    self._tail_call(by_group[gi], None, None, keep_beta_pow=k != len(order) - 1)
+                return
+            dp.wait_all_groups()
+        self._tail_call(pg, found_inf, loss_scale, keep_beta_pow=False)
+
+    def _tail_call(self, pg, found_inf, loss_scale, keep_beta_pow):
+        clip = self._grad_clip
         # The ctypes argument block is built once and reused while the buffers stay the same.
         key = (tuple(g.data_ptr for _, g in pg), id(clip), loss_scale.data_ptr if loss_scale is not None else 0,
                found_inf.data_ptr if found_inf is not None else 0, self._zero_grads_in_step,
                self._write_back_unscaled_grads,
-               _clip_by_global_norm_using_mp_type())
-        cached = self._fused_cache
-        if cached is None or cached[0] != key:
+               _clip_by_global_norm_using_mp_type(), keep_beta_pow)
+        cached = self._fused_cache.get(key)
+        if cached is None:
             params = [p for p, _ in pg]
             grads = [g for _, g in pg]
             mp = self._find_master(params[0])
@@ -209,6 +228,7 @@ class Optimizer:
             cfg.write_back_grads = int(loss_scale is not None and self._write_back_unscaled_grads
                                        and not self._zero_grads_in_step)
             cfg.zero_grads = int(self._zero_grads_in_step)
+            cfg.keep_beta_pow = int(keep_beta_pow)
             lr_ratio, with_decay = self._tensor_attrs(pg)
             acc = [self._accumulators[p.name] for p in params]
             keep = {
@@ -231,8 +251,10 @@ class Optimizer:
             keep["args"] = (C.byref(cfg), keep["params"], keep["grads"], None, keep["m1"], keep["m2"], C.byref(keep["b1"]),
                             C.byref(keep["b2"]), keep["masters"], keep["n"], lr_ratio.ctypes.data, with_decay.ctypes.data,
                             ref("ls"), ref("fi"), ref("gn"), ref("cl"))
-            cached = self._fused_cache = (key, keep)
-        keep = cached[1]
+            if len(self._fused_cache) > 64:
+                self._fused_cache.clear()
+            cached = self._fused_cache[key] = keep
+        keep = cached
         lr = self._global_lr().prb
         args = keep["args"]
         call("prb_dp_step_tail", *args[:3], C.byref(lr), *args[4:], core._stream_handle(None))

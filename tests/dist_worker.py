@@ -50,12 +50,41 @@ def main(out_dir):
                     tol = 1e-6 if dtype == orc.F32 else 1e-2
                     np.testing.assert_allclose(orc.to_f32(got, dtype), want, rtol=tol, atol=tol * 1e-2)
                 np.save(os.path.join(out_dir, "grad_%d_%d_%d_r%d.npy" % (dtype, step, i, rank)), got)
-                # next step: every rank feeds its own fresh gradient again
+            opt.step()  # consumes the synchronised gradients
+            prb.current_stream().synchronize()
+            for i, p in enumerate(params):  # next step: every rank feeds its own fresh gradient again
                 p.grad.copy_from_numpy(grads_all[i][rank])
-            opt.step()
         prb.current_stream().synchronize()
         for i, p in enumerate(params):
             np.save(os.path.join(out_dir, "param_%d_%d_r%d.npy" % (dtype, i, rank)), p.numpy())
+    # pipelined consumption: the optimizer reads the bucket arena and waits per bucket (no clip, no AMP)
+    params, grads_all, host = [], [], []
+    for i, sz in enumerate(sizes):
+        p0 = np.random.default_rng(100 + i).normal(0, 0.02, sz).astype(np.float32)
+        p = prb.Tensor.from_numpy(p0, name="w_%d" % i)
+        per_rank = [np.random.default_rng(1000 * r + i).normal(0, 1e-2, sz).astype(np.float32) for r in range(n)]
+        p.grad = prb.Tensor.from_numpy(per_rank[rank])
+        params.append(p)
+        grads_all.append(per_rank)
+        host.append({"p": p0.copy(), "m1": np.zeros(sz, np.float32), "m2": np.zeros(sz, np.float32)})
+    dp = prb.DataParallel(params, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True)
+    assert dp.pipelined
+    opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, weight_decay=0.01)
+    b1p, b2p = np.float32(0.9), np.float32(0.999)
+    for step in range(3):
+        dp.prepare_for_backward()
+        dp.mark_all_ready()
+        opt.step()
+        prb.current_stream().synchronize()
+        for i, (p, h) in enumerate(zip(params, host)):
+            avg = np.sum([orc.scale(g, orc.F32, 1.0 / n).astype(np.float64) for g in grads_all[i]], axis=0).astype(np.float32)
+            if n == 2:  # two addends: the allreduce result is exactly this
+                orc.adam(h["p"], avg, h["m1"], h["m2"], None, dtype_param=orc.F32, dtype_grad=orc.F32, lr=1e-3, beta1=0.9,
+                         beta2=0.999, epsilon=1e-8, coeff=0.01, use_decay=True, beta1_pow=b1p, beta2_pow=b2p)
+                np.testing.assert_array_equal(p.numpy(), h["p"])
+            np.save(os.path.join(out_dir, "pipe_param_%d_%d_r%d.npy" % (step, i, rank)), p.numpy())
+        b1p, b2p = np.float32(0.9) * b1p, np.float32(0.999) * b2p
+    assert opt._beta1_pow.numpy()[0] == b1p
     # timing helper used by bench.py: max over ranks through the communicator
     t = prb.Tensor.from_numpy(np.array([float(rank + 1)], np.float32))
     group.all_reduce(t, "max")

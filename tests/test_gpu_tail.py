@@ -106,9 +106,6 @@ def test_dataparallel_adamw_fp32_step(prb, consume):
     opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, weight_decay=0.01,
                               apply_decay_param_fun=lambda name: name not in ("w_0", "w_1"),
                               lr_ratio=lambda p: 0.5 if p.name == "w_3" else 1.0)
-    if consume:
-        for p, v in zip(params, dp.bucket_grads()):
-            p._reduced_grad = v
     wd = [p.name not in ("w_0", "w_1") for p in params]
     ratio = [0.5 if p.name == "w_3" else 1.0 for p in params]
     b1p, b2p = np.float32(0.9), np.float32(0.999)
