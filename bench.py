@@ -377,7 +377,7 @@ def run_gpu_arm(args):
                        "amp": w["amp"], "clip": w["clip"], "algorithmic_bytes_per_elem": w["bpe"],
                        "l2": "working set %.0f MB per step > 126 MB L2 (inputs larger than L2, no flush)" %
                              (w["elems"] * (w["bpe"] + 8) / 1e6),
-                       "parallelism": "dp%d" % nranks, "pct_of_measured_hbm_peak_per_gpu": 100.0 * value / nranks / peak,
+                       "parallelism": "dp%d" % nranks, "allreduce": w["dp"]._reducer.allreduce_backend, "pct_of_measured_hbm_peak_per_gpu": 100.0 * value / nranks / peak,
                        "pct_of_nominal_8TBps_per_gpu": 100.0 * value / nranks / 8000.0},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
         }

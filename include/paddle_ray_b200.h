@@ -260,6 +260,15 @@ int32_t prb_reducer_wait_group(PRB_Reducer* r, int64_t group_index, void* stream
 int32_t prb_reducer_num_groups(const PRB_Reducer* r);
 /* Index (in launch order, i.e. as passed to prb_reducer_create) of the group that holds parameter i. */
 int32_t prb_reducer_group_of(const PRB_Reducer* r, int64_t var_index, int64_t* out_group);
+/* Which allreduce runs the buckets: 0 = none (one rank / host-only), 1 = NCCL, 2 = the library's own two-shot
+ * kernel over NVLink peer memory (PRB_ALLREDUCE=nvlink; single node, needs CUDA IPC between the ranks; falls
+ * back to NCCL collectively when it cannot be set up).  prb_reducer_comm_error reports (synchronously) whether
+ * a wait inside that kernel ever ran into its time limit, i.e. a peer never arrived. */
+int32_t prb_reducer_allreduce_backend(const PRB_Reducer* r);
+/* Only the allreduce of one group's bucket region, in place, on `stream` (measurement aid: lets a benchmark time
+ * the exchange step of ref reducer.cc:1058 by itself with either backend). */
+int32_t prb_reducer_allreduce_group(PRB_Reducer* r, int64_t group_index, void* stream);
+int32_t prb_reducer_comm_error(PRB_Reducer* r, int32_t* out);
 /* 1 when every group of the current backward has been launched and finalised. */
 int32_t prb_reducer_is_finalized(const PRB_Reducer* r);
 /* Device address / element offset of parameter i's slot inside the bucket arena. */

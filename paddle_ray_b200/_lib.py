@@ -88,6 +88,9 @@ SIGNATURES = {
     "prb_reducer_wait_group": [_vp, _i64, _vp],
     "prb_reducer_num_groups": [_vp],
     "prb_reducer_group_of": [_vp, _i64, C.POINTER(_i64)],
+    "prb_reducer_allreduce_backend": [_vp],
+    "prb_reducer_allreduce_group": [_vp, _i64, _vp],
+    "prb_reducer_comm_error": [_vp, C.POINTER(_i32)],
     "prb_reducer_is_finalized": [_vp],
     "prb_reducer_bucket_view": [_vp, _i64, _T],
     "prb_reducer_launched_groups": [_vp, _vp, _i64, _vp],
@@ -123,7 +126,7 @@ SIGNATURES = {
 _RESTYPES = {"prb_comm_stream": _vp, "prb_launch_count": _i64, "prb_last_error_message": C.c_char_p,
              "prb_version": C.c_char_p}
 # entry points whose int32 return value is a value, not a status
-_VALUE_RETURN = {"prb_comm_nranks", "prb_comm_rank", "prb_reducer_is_finalized", "prb_reducer_num_groups"}
+_VALUE_RETURN = {"prb_comm_nranks", "prb_comm_rank", "prb_reducer_is_finalized", "prb_reducer_num_groups", "prb_reducer_allreduce_backend"}
 
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)  # AttributeError here == the .so does not export what the header declares

@@ -150,6 +150,8 @@ class Tensor:
         self.stop_gradient = False
         self.optimize_attr = {"learning_rate": 1.0}
         self.is_sparse_grad = False
+        self._reduced_grad = None      # view of this parameter's slot in a DataParallel bucket arena
+        self._bucket = (None, 0)       # (DataParallel, launch-order group index) when gradients are consumed there
         self._owner = owner  # keeps the backing allocation alive for views
         self._host = None
         self._owned = False

@@ -12,7 +12,8 @@ namespace {
 struct GradVariant {
   int threads, unroll, min_blocks;
 };
-constexpr GradVariant kGradVariants[] = {{256, 4, 2}, {256, 2, 4}, {256, 1, 8}, {128, 1, 16}, {128, 2, 8}};
+constexpr GradVariant kGradVariants[] = {{256, 4, 2}, {256, 2, 4}, {256, 1, 8}, {128, 1, 16}, {128, 2, 8},
+                                         {256, 8, 2}, {512, 4, 1}, {512, 8, 1}};
 constexpr int kNumGradVariants = sizeof(kGradVariants) / sizeof(kGradVariants[0]);
 constexpr int kDefaultGradVariant = 0;
 
@@ -127,51 +128,66 @@ __device__ __forceinline__ void store_tensor_sum(const NormGroup& g, int t, floa
   }
 }
 
+constexpr int kFinMaxTensors = 4096;  // tensors per dtype group staged in shared memory
+
 __global__ void __launch_bounds__(kFinThreads) norm_finalize_kernel(const NormFinalizeArgs a) {
   __shared__ float red[kFinThreads / 32];
+  __shared__ int s_first[kFinMaxTensors + 1];   // chunk ranges of the group's tensors
+  __shared__ float s_sum[kFinMaxTensors];       // per-tensor sums of the group
+  __shared__ float s_group[3];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = kFinThreads >> 5;
   for (int gi = 0; gi < a.ngroups; ++gi) {
     const NormGroup& g = a.g[gi];
-    // big tensors: all threads (uniform control flow: every thread sees the same chunk counts)
-    for (int t = 0; t < g.ntensors; ++t) {
-      const int c0 = g.first_chunk[t], c1 = g.first_chunk[t + 1];
-      if (c1 - c0 <= kFinBigTensor) continue;
-      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-      int c = c0 + threadIdx.x;
-      for (; c + 3 * kFinThreads < c1; c += 4 * kFinThreads) {
-        const float v0 = g.partials[c], v1 = g.partials[c + kFinThreads], v2 = g.partials[c + 2 * kFinThreads],
-                    v3 = g.partials[c + 3 * kFinThreads];
-        s0 = __fadd_rn(s0, v0);
-        s1 = __fadd_rn(s1, v1);
-        s2 = __fadd_rn(s2, v2);
-        s3 = __fadd_rn(s3, v3);
+    float group_sum = 0.0f;  // meaningful in thread 0 only
+    for (int base = 0; base < g.ntensors; base += kFinMaxTensors) {
+      const int nt = min(kFinMaxTensors, g.ntensors - base);
+      // stage the chunk ranges with one coalesced pass (a serial walk over global memory costs ~0.3 us per tensor)
+      for (int i = threadIdx.x; i <= nt; i += kFinThreads) s_first[i] = g.first_chunk[base + i];
+      __syncthreads();
+      // big tensors: all threads (uniform control flow: every thread sees the same chunk counts)
+      for (int t = 0; t < nt; ++t) {
+        const int c0 = s_first[t], c1 = s_first[t + 1];
+        if (c1 - c0 <= kFinBigTensor) continue;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int c = c0 + threadIdx.x;
+        for (; c + 3 * kFinThreads < c1; c += 4 * kFinThreads) {
+          const float v0 = g.partials[c], v1 = g.partials[c + kFinThreads], v2 = g.partials[c + 2 * kFinThreads],
+                      v3 = g.partials[c + 3 * kFinThreads];
+          s0 = __fadd_rn(s0, v0);
+          s1 = __fadd_rn(s1, v1);
+          s2 = __fadd_rn(s2, v2);
+          s3 = __fadd_rn(s3, v3);
+        }
+        for (; c < c1; c += kFinThreads) s0 = __fadd_rn(s0, g.partials[c]);
+        float s = __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
+        s = block_sum<kFinThreads>(s, red);
+        if (threadIdx.x == 0) s_sum[t] = round_mode(s, g.round_mode);  // the op's output is T-typed
       }
-      for (; c < c1; c += kFinThreads) s0 = __fadd_rn(s0, g.partials[c]);
-      float s = __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
-      s = block_sum<kFinThreads>(s, red);
-      if (threadIdx.x == 0) store_tensor_sum(g, t, round_mode(s, g.round_mode));  // the op's output is T-typed
+      // small tensors: one warp each
+      for (int t = warp; t < nt; t += nwarps) {
+        const int c0 = s_first[t], c1 = s_first[t + 1];
+        if (c1 - c0 > kFinBigTensor) continue;
+        float s = 0.0f;
+        for (int c = c0 + lane; c < c1; c += 32) s = __fadd_rn(s, g.partials[c]);
+        s = warp_sum(s);
+        if (lane == 0) s_sum[t] = round_mode(s, g.round_mode);
+      }
+      __syncthreads();
+      for (int t = threadIdx.x; t < nt; t += kFinThreads) store_tensor_sum(g, base + t, s_sum[t]);
+      if (threadIdx.x == 0)
+        for (int t = 0; t < nt; ++t) group_sum = __fadd_rn(group_sum, s_sum[t]);  // add_n, list order
+      __syncthreads();
     }
-    // small tensors: one warp each
-    for (int t = warp; t < g.ntensors; t += nwarps) {
-      const int c0 = g.first_chunk[t], c1 = g.first_chunk[t + 1];
-      if (c1 - c0 > kFinBigTensor) continue;
-      float s = 0.0f;
-      for (int c = c0 + lane; c < c1; c += 32) s = __fadd_rn(s, g.partials[c]);
-      s = warp_sum(s);
-      if (lane == 0) store_tensor_sum(g, t, round_mode(s, g.round_mode));
-    }
+    if (threadIdx.x == 0) s_group[gi] = group_sum;
   }
   if (!a.compute_clip) return;
-  __syncthreads();
   if (threadIdx.x == 0) {
     float total = 0.0f;
     for (int gi = 0; gi < a.ngroups; ++gi) {
       const NormGroup& g = a.g[gi];
       if (g.ntensors == 0) continue;
-      float s = 0.0f;
-      for (int t = 0; t < g.ntensors; ++t) s = __fadd_rn(s, g.tensor_sums[t]);  // add_n, list order
-      s = round_mode(s, g.round_mode);                                           // add_n output is T-typed
-      total = __fadd_rn(total, s);                                               // astype(fp32) then add_n
+      const float s = round_mode(s_group[gi], g.round_mode);  // add_n output is T-typed
+      total = __fadd_rn(total, s);                            // astype(fp32) then add_n
     }
     const float norm = __fsqrt_rn(total);
     float clip = 1.0f;
@@ -265,7 +281,10 @@ int32_t launch_pass_typed(const DeviceTable& tab, bool write, bool norm, bool mp
       case 1: PRB_GPV(W, N, M, 256, 2, 4); break;          \
       case 2: PRB_GPV(W, N, M, 256, 1, 8); break;          \
       case 3: PRB_GPV(W, N, M, 128, 1, 16); break;         \
-      default: PRB_GPV(W, N, M, 128, 2, 8); break;         \
+      case 4: PRB_GPV(W, N, M, 128, 2, 8); break;          \
+      case 5: PRB_GPV(W, N, M, 256, 8, 2); break;          \
+      case 6: PRB_GPV(W, N, M, 512, 4, 1); break;          \
+      default: PRB_GPV(W, N, M, 512, 8, 1); break;         \
     }                                                      \
   } while (0)
   if (write && !norm) PRB_GP(true, false, false);

@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "prb_bucket.cuh"
+#include "prb_nvlink.h"
 
 namespace prb {
 namespace {
@@ -32,6 +33,7 @@ struct NcclApi {
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
   ncclResult_t (*GetVersion)(int*) = nullptr;
   // optional (NCCL >= 2.19): user-buffer registration lets NVLink/NVLS collectives skip staging copies
@@ -61,6 +63,7 @@ int32_t load_nccl() {
   PRB_SYM(CommDestroy, "ncclCommDestroy");
   PRB_SYM(AllReduce, "ncclAllReduce");
   PRB_SYM(Broadcast, "ncclBroadcast");
+  PRB_SYM(AllGather, "ncclAllGather");
   PRB_SYM(GetErrorString, "ncclGetErrorString");
   PRB_SYM(GetVersion, "ncclGetVersion");
 #undef PRB_SYM
@@ -91,6 +94,25 @@ int32_t nccl_dtype(int32_t dt, ncclDataType_t* out) {
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// the two small collectives prb_nvlink.cu needs during set-up
+int32_t nvl_all_gather_bytes(void* comm, const void* send, void* recv, size_t bytes, cudaStream_t s) {
+  PRB_NCCL(g_nccl.AllGather(send, recv, bytes, ncclChar, (ncclComm_t)comm, s));
+  return PRB_SUCCESS;
+}
+int32_t nvl_all_min_int(void* comm, int value, int* out, cudaStream_t s) {
+  int* d = nullptr;
+  PRB_CUDA(cudaMalloc((void**)&d, sizeof(int)));
+  PRB_CUDA(cudaMemcpyAsync(d, &value, sizeof(int), cudaMemcpyHostToDevice, s));
+  ncclResult_t rc = g_nccl.AllReduce(d, d, 1, ncclInt32, ncclMin, (ncclComm_t)comm, s);
+  if (rc == ncclSuccess) {
+    cudaMemcpyAsync(out, d, sizeof(int), cudaMemcpyDeviceToHost, s);
+    cudaStreamSynchronize(s);
+  }
+  cudaFree(d);
+  PRB_ENFORCE(rc == ncclSuccess, PRB_EXTERNAL, "NCCL error: %s", g_nccl.GetErrorString(rc));
+  return PRB_SUCCESS;
+}
+
 }  // namespace
 }  // namespace prb
 
@@ -100,6 +122,7 @@ struct PRB_Comm {
   int nranks = 1, rank = 0, device = 0;
   ncclComm_t comm = nullptr;
   cudaStream_t stream = nullptr;  // dedicated high-priority comm stream (ref process_group_nccl.cc:688-737)
+  cudaStream_t stream2 = nullptr; // second comm stream: the NVLink allreduce alternates between the two
 };
 
 namespace {
@@ -127,6 +150,7 @@ struct PRB_Reducer {
   char* arena = nullptr;
   size_t arena_bytes = 0;
   void* arena_reg = nullptr;  // ncclCommRegister handle of the arena (NULL when unavailable)
+  NvlContext* nvl = nullptr;  // NVLink peer-memory allreduce (PRB_ALLREDUCE=nvlink), else NCCL
   size_t next_group = 0;
   std::vector<uint8_t> ready;
   std::vector<uint8_t> unused;
@@ -201,19 +225,25 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   PRB_TRY(launch_scale(g.dtype, g.pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
   if (c->nranks > 1) {
     // SyncDefaultStream: comm stream waits for the calc stream (ref process_group_nccl.cc:658-667)
+    cudaStream_t cs = c->stream;
+    if (r->nvl != nullptr && nvl_next_slot(r->nvl) == 1) cs = c->stream2;  // alternate: barriers hide under transfers
     PRB_CUDA(cudaEventRecord(g.ready, calc));
-    PRB_CUDA(cudaStreamWaitEvent(c->stream, g.ready, 0));
-    ncclDataType_t nt;
-    PRB_TRY(nccl_dtype(g.dtype, &nt));
-    PRB_NCCL(g_nccl.AllReduce(region, region, (size_t)g.length, nt, ncclSum, c->comm, c->stream));
+    PRB_CUDA(cudaStreamWaitEvent(cs, g.ready, 0));
+    if (r->nvl != nullptr) {
+      PRB_TRY(nvl_allreduce(r->nvl, g.arena_off, g.length, g.dtype, cs));
+    } else {
+      ncclDataType_t nt;
+      PRB_TRY(nccl_dtype(g.dtype, &nt));
+      PRB_NCCL(g_nccl.AllReduce(region, region, (size_t)g.length, nt, ncclSum, c->comm, cs));
+    }
     if (r->unpack) {  // the reference also splits on the comm stream (reducer.cc:1062-1069)
       if (!g.unpack_valid) {
-        PRB_TRY(group_tables(r, g, true, c->stream, &g.unpack_tab));
+        PRB_TRY(group_tables(r, g, true, cs, &g.unpack_tab));
         g.unpack_valid = true;
       }
-      PRB_TRY(launch_copy(es, g.unpack_tab, c->stream));
+      PRB_TRY(launch_copy(es, g.unpack_tab, cs));
     }
-    PRB_CUDA(cudaEventRecord(g.done, c->stream));
+    PRB_CUDA(cudaEventRecord(g.done, cs));
   } else if (r->unpack) {
     if (!g.unpack_valid) {
       PRB_TRY(group_tables(r, g, true, calc, &g.unpack_tab));
@@ -387,6 +417,7 @@ int32_t prb_comm_init_rank(const uint8_t id[PRB_UNIQUE_ID_BYTES], int32_t nranks
   int lo = 0, hi = 0;
   PRB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
   PRB_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, hi));
+  PRB_CUDA(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, hi));
   *out = c;
   return PRB_SUCCESS;
 }
@@ -407,6 +438,7 @@ int32_t prb_comm_destroy(PRB_Comm* c) {
   if (!c) return PRB_SUCCESS;
   if (c->comm) g_nccl.CommDestroy(c->comm);
   if (c->stream) cudaStreamDestroy(c->stream);
+  if (c->stream2) cudaStreamDestroy(c->stream2);
   delete c;
   return PRB_SUCCESS;
 }
@@ -534,6 +566,16 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
   if (comm->nranks > 1 && g_nccl.CommRegister != nullptr && getenv("PRB_NO_NCCL_REGISTER") == nullptr) {
     if (g_nccl.CommRegister(comm->comm, r->arena, arena, &r->arena_reg) != ncclSuccess) r->arena_reg = nullptr;
   }
+  // Optional: allreduce written as our own kernel over NVLink peer memory instead of NCCL.
+  const char* ar = getenv("PRB_ALLREDUCE");
+  if (comm->nranks > 1 && ar != nullptr && strcmp(ar, "nvlink") == 0) {
+    NvlCollectives nc{(void*)comm->comm, nvl_all_gather_bytes, nvl_all_min_int};
+    int32_t st = nvl_setup(nc, comm->nranks, comm->rank, r->arena, arena, comm->stream, &r->nvl);
+    if (st != PRB_SUCCESS) {
+      prb_reducer_destroy(r);
+      return st;
+    }
+  }
   r->finalized = true;  // nothing pending before the first prepare_for_backward
   *out = r;
   return PRB_SUCCESS;
@@ -543,6 +585,7 @@ int32_t prb_reducer_destroy(PRB_Reducer* r) {
   if (!r) return PRB_SUCCESS;
   if (!r->dry) cudaDeviceSynchronize();
   if (r->arena_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(r->comm->comm, r->arena_reg);
+  if (r->nvl) nvl_destroy(r->nvl);
   for (Group& g : r->groups) {
     if (g.ready) cudaEventDestroy(g.ready);
     if (g.done) cudaEventDestroy(g.done);
@@ -620,6 +663,39 @@ int32_t prb_reducer_set_unpack(PRB_Reducer* r, int32_t enabled) {
 }
 
 int32_t prb_reducer_is_finalized(const PRB_Reducer* r) { return r && r->finalized ? 1 : 0; }
+
+int32_t prb_reducer_allreduce_backend(const PRB_Reducer* r) {
+  if (r == nullptr || r->dry || r->comm->nranks == 1) return 0;
+  return r->nvl != nullptr ? 2 : 1;
+}
+
+int32_t prb_reducer_allreduce_group(PRB_Reducer* r, int64_t gi, void* stream) {
+  PRB_ENFORCE(r && !r->dry, PRB_INVALID_ARGUMENT, "reducer: bad handle");
+  PRB_ENFORCE(gi >= 0 && gi < (int64_t)r->groups.size(), PRB_OUT_OF_RANGE, "Out of bounds group index %lld", (long long)gi);
+  Group& g = r->groups[(size_t)gi];
+  PRB_Comm* c = r->comm;
+  if (c->nranks == 1) return PRB_SUCCESS;
+  if (r->nvl != nullptr) {
+    // stand-alone calls all go to the caller's one stream, which orders them whatever slot they use
+    return nvl_allreduce(r->nvl, g.arena_off, g.length, g.dtype, (cudaStream_t)stream);
+  }
+  ncclDataType_t nt;
+  PRB_TRY(nccl_dtype(g.dtype, &nt));
+  char* region = r->arena + g.arena_off;
+  PRB_NCCL(g_nccl.AllReduce(region, region, (size_t)g.length, nt, ncclSum, c->comm, (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_comm_error(PRB_Reducer* r, int32_t* out) {
+  PRB_ENFORCE(r && out, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
+  *out = 0;
+  if (r->nvl != nullptr) {
+    int e = 0;
+    PRB_TRY(nvl_error_flag(r->nvl, &e));
+    *out = e;
+  }
+  return PRB_SUCCESS;
+}
 
 int32_t prb_reducer_set_deferred_wait(PRB_Reducer* r, int32_t enabled) {
   PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");

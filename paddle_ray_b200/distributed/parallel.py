@@ -206,6 +206,18 @@ class EagerReducer:
     def set_unpack(self, enabled: bool):
         call("prb_reducer_set_unpack", self.handle, int(bool(enabled)))
 
+    @property
+    def allreduce_backend(self) -> str:
+        return {0: "none", 1: "nccl", 2: "nvlink"}[lib.prb_reducer_allreduce_backend(self.handle)]
+
+    def allreduce_group(self, group_index: int, stream=None):
+        call("prb_reducer_allreduce_group", self.handle, int(group_index), core._stream_handle(stream))
+
+    def comm_error(self) -> bool:
+        e = C.c_int32()
+        call("prb_reducer_comm_error", self.handle, C.byref(e))
+        return bool(e.value)
+
     def set_deferred_wait(self, enabled: bool):
         call("prb_reducer_set_deferred_wait", self.handle, int(bool(enabled)))
 

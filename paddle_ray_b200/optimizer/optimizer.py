@@ -79,7 +79,7 @@ class Optimizer:
         self._lr_tensor = None
         self._lr_value = None
         self._lr_feeder = None
-        self._fused_cache = {}
+        self._step_plans = {}
         # True folds clear_grad(set_to_zero=True) into the update pass (gradients are zeroed as they are consumed)
         self._zero_grads_in_step = False
         # True keeps p.grad reference-visible after an AMP step (the unscaled gradient is stored back)
@@ -152,112 +152,113 @@ class Optimizer:
 
     # ---- step
     def _params_grads(self):
-        out = []
-        for p in self._parameter_list:
-            if getattr(p, "stop_gradient", False):
-                continue
-            g = getattr(p, "_reduced_grad", None) or p.grad
-            if g is not None:
-                out.append((p, g))
-        return out
+        return [(p, p._reduced_grad or p.grad) for p in self._parameter_list
+                if not p.stop_gradient and (p._reduced_grad is not None or p.grad is not None)]
 
     def step(self):
-        """ref optimizer.py:1447-1504 -> _apply_optimize :1178-1221."""
+        """ref optimizer.py:1447-1504 -> _apply_optimize :1178-1221.
+
+        The per-step host work is a cache lookup plus one C call per launch: the argument blocks of the
+        fused tail are built once per distinct set of buffers and options (``_step_plans``)."""
         self._create_accumulators()
         pg = self._params_grads()
         if not pg:
             return
         found_inf = self._get_auxiliary_var("found_inf")
         loss_scale = self._get_auxiliary_var("loss_scale")  # set by GradScaler when the unscale is deferred to us
-        uniform = len({p.dtype for p, _ in pg}) == 1 and len({g.dtype for _, g in pg}) == 1 and \
-            len({self._find_master(p) for p, _ in pg}) == 1
-        if uniform:
-            self._fused_step(pg, found_inf, loss_scale)
-        else:
-            self._per_tensor_step(pg, found_inf, loss_scale)
+        clip = self._grad_clip
+        key = (tuple(g.data_ptr for _, g in pg), id(clip), loss_scale.data_ptr if loss_scale is not None else 0,
+               found_inf.data_ptr if found_inf is not None else 0, self._zero_grads_in_step,
+               self._write_back_unscaled_grads, _clip_by_global_norm_using_mp_type())
+        plan = self._step_plans.get(key)
+        if plan is None:
+            if len(self._step_plans) > 16:
+                self._step_plans.clear()
+            plan = self._step_plans[key] = self._build_plan(pg, found_inf, loss_scale)
+        if plan is None:  # mixed dtypes or per-parameter clip exclusions: the reference-shaped loop
+            return self._per_tensor_step(pg, found_inf, loss_scale)
+        lr = self._global_lr().prb
+        lr_ref = C.byref(lr)
+        stream = core._stream_handle(None)
+        for dp, gi, args in plan:
+            if dp is not None:
+                if gi is None:
+                    dp.wait_all_groups()
+                else:
+                    dp.wait_group(gi)
+            call("prb_dp_step_tail", args[0], args[1], args[2], lr_ref, *args[4:16], stream)
 
     def _tensor_attrs(self, pg):
         lr_ratio = np.ones(len(pg), np.float32)
         with_decay = np.ones(len(pg), np.uint8)
         return lr_ratio, with_decay
 
-    def _fused_step(self, pg, found_inf, loss_scale):
+    def _build_plan(self, pg, found_inf, loss_scale):
+        """-> list of (DataParallel or None, group index or None, argument block), or None for the slow path."""
+        uniform = len({p.dtype for p, _ in pg}) == 1 and len({g.dtype for _, g in pg}) == 1 and \
+            len({self._find_master(p) for p, _ in pg}) == 1
         clip = self._grad_clip
-        if clip is not None and not all(getattr(p, "need_clip", True) is not False for p, _ in pg):
-            return self._per_tensor_step(pg, found_inf, loss_scale)
+        if not uniform or (clip is not None and not all(p.need_clip is not False for p, _ in pg)):
+            return None
         # Gradients that sit in a DataParallel bucket arena of a multi-rank job: without a global dependency
         # (no clip, no AMP) each bucket's parameters are updated as soon as THAT bucket's allreduce is done,
         # overlapping the allreduce of the buckets behind it.
-        dp = getattr(pg[0][0], "_bucket", (None, 0))[0]
+        dp = pg[0][0]._bucket[0]
         if dp is not None and dp.pipelined:
             if clip is None and loss_scale is None and found_inf is None:
                 by_group = {}
                 for p, g in pg:
                     by_group.setdefault(p._bucket[1], []).append((p, g))
                 order = sorted(by_group)
-                for k, gi in enumerate(order):
-                    dp.wait_group(gi)
-                    self._tail_call(by_group[gi], None, None, keep_beta_pow=k != len(order) - 1)
-                return
-            dp.wait_all_groups()
-        self._tail_call(pg, found_inf, loss_scale, keep_beta_pow=False)
+                return [(dp, gi, self._tail_args(by_group[gi], None, None, keep_beta_pow=k != len(order) - 1))
+                        for k, gi in enumerate(order)]
+            return [(dp, None, self._tail_args(pg, found_inf, loss_scale, keep_beta_pow=False))]
+        return [(None, None, self._tail_args(pg, found_inf, loss_scale, keep_beta_pow=False))]
 
-    def _tail_call(self, pg, found_inf, loss_scale, keep_beta_pow):
+    def _tail_args(self, pg, found_inf, loss_scale, keep_beta_pow):
+        """ctypes argument block of one prb_dp_step_tail call (kept alive by the plan that holds it)."""
         clip = self._grad_clip
-        # The ctypes argument block is built once and reused while the buffers stay the same.
-        key = (tuple(g.data_ptr for _, g in pg), id(clip), loss_scale.data_ptr if loss_scale is not None else 0,
-               found_inf.data_ptr if found_inf is not None else 0, self._zero_grads_in_step,
-               self._write_back_unscaled_grads,
-               _clip_by_global_norm_using_mp_type(), keep_beta_pow)
-        cached = self._fused_cache.get(key)
-        if cached is None:
-            params = [p for p, _ in pg]
-            grads = [g for _, g in pg]
-            mp = self._find_master(params[0])
-            cfg = TailConfig()
-            cfg.beta1, cfg.beta2, cfg.epsilon = float(self._beta1), float(self._beta2), float(self._epsilon)
-            cfg.coeff = float(self._coeff())
-            cfg.use_adamw = int(self._use_adamw)
-            cfg.multi_precision = int(mp)
-            cfg.use_amp = int(loss_scale is not None)
-            cfg.use_clip = int(clip is not None)
-            cfg.clip_norm = float(clip.clip_norm) if clip else 0.0
-            cfg.auto_skip_clip = int(clip.auto_skip_clip) if clip else 0
-            cfg.use_mp_type = int(_clip_by_global_norm_using_mp_type())
-            # p.grad holds the unscaled (never the clipped) gradient after a reference step
-            cfg.write_back_grads = int(loss_scale is not None and self._write_back_unscaled_grads
-                                       and not self._zero_grads_in_step)
-            cfg.zero_grads = int(self._zero_grads_in_step)
-            cfg.keep_beta_pow = int(keep_beta_pow)
-            lr_ratio, with_decay = self._tensor_attrs(pg)
-            acc = [self._accumulators[p.name] for p in params]
-            keep = {
-                "cfg": cfg, "params": tensor_array(params), "grads": tensor_array(grads),
-                "m1": tensor_array([a[self._moment1_acc_str] for a in acc]),
-                "m2": tensor_array([a[self._moment2_acc_str] for a in acc]),
-                "masters": tensor_array([self._master_weights[p.name] for p in params]) if mp else None,
-                "lr_ratio": lr_ratio, "with_decay": with_decay, "b1": self._beta1_pow.prb, "b2": self._beta2_pow.prb,
-                "n": len(params), "ls": None, "fi": None, "gn": None, "cl": None,
-            }
-            if clip is not None:
-                if clip.last_global_norm is None:
-                    clip.last_global_norm, clip.last_clip = Tensor.zeros(1, FLOAT32), Tensor.zeros(1, FLOAT32)
-                keep["gn"], keep["cl"] = clip.last_global_norm.prb, clip.last_clip.prb
-            if loss_scale is not None:
-                keep["ls"] = loss_scale.prb
-            if found_inf is not None:  # with use_amp=0 it is an input-only skip flag (unscale_ ran earlier)
-                keep["fi"] = found_inf.prb
-            ref = lambda k: C.byref(keep[k]) if keep[k] is not None else None  # noqa: E731
-            keep["args"] = (C.byref(cfg), keep["params"], keep["grads"], None, keep["m1"], keep["m2"], C.byref(keep["b1"]),
-                            C.byref(keep["b2"]), keep["masters"], keep["n"], lr_ratio.ctypes.data, with_decay.ctypes.data,
-                            ref("ls"), ref("fi"), ref("gn"), ref("cl"))
-            if len(self._fused_cache) > 64:
-                self._fused_cache.clear()
-            cached = self._fused_cache[key] = keep
-        keep = cached
-        lr = self._global_lr().prb
-        args = keep["args"]
-        call("prb_dp_step_tail", *args[:3], C.byref(lr), *args[4:], core._stream_handle(None))
+        params = [p for p, _ in pg]
+        grads = [g for _, g in pg]
+        mp = self._find_master(params[0])
+        cfg = TailConfig()
+        cfg.beta1, cfg.beta2, cfg.epsilon = float(self._beta1), float(self._beta2), float(self._epsilon)
+        cfg.coeff = float(self._coeff())
+        cfg.use_adamw = int(self._use_adamw)
+        cfg.multi_precision = int(mp)
+        cfg.use_amp = int(loss_scale is not None)
+        cfg.use_clip = int(clip is not None)
+        cfg.clip_norm = float(clip.clip_norm) if clip else 0.0
+        cfg.auto_skip_clip = int(clip.auto_skip_clip) if clip else 0
+        cfg.use_mp_type = int(_clip_by_global_norm_using_mp_type())
+        # p.grad holds the unscaled (never the clipped) gradient after a reference step
+        cfg.write_back_grads = int(loss_scale is not None and self._write_back_unscaled_grads
+                                   and not self._zero_grads_in_step)
+        cfg.zero_grads = int(self._zero_grads_in_step)
+        cfg.keep_beta_pow = int(keep_beta_pow)
+        lr_ratio, with_decay = self._tensor_attrs(pg)
+        acc = [self._accumulators[p.name] for p in params]
+        keep = {
+            "cfg": cfg, "params": tensor_array(params), "grads": tensor_array(grads),
+            "m1": tensor_array([a[self._moment1_acc_str] for a in acc]),
+            "m2": tensor_array([a[self._moment2_acc_str] for a in acc]),
+            "masters": tensor_array([self._master_weights[p.name] for p in params]) if mp else None,
+            "lr_ratio": lr_ratio, "with_decay": with_decay, "b1": self._beta1_pow.prb, "b2": self._beta2_pow.prb,
+            "ls": None, "fi": None, "gn": None, "cl": None,
+        }
+        if clip is not None:
+            if clip.last_global_norm is None:
+                clip.last_global_norm, clip.last_clip = Tensor.zeros(1, FLOAT32), Tensor.zeros(1, FLOAT32)
+            keep["gn"], keep["cl"] = clip.last_global_norm.prb, clip.last_clip.prb
+        if loss_scale is not None:
+            keep["ls"] = loss_scale.prb
+        if found_inf is not None:  # with use_amp=0 it is an input-only skip flag (unscale_ ran earlier)
+            keep["fi"] = found_inf.prb
+        ref = lambda k: C.byref(keep[k]) if keep[k] is not None else None  # noqa: E731
+        args = (C.byref(cfg), keep["params"], keep["grads"], None, keep["m1"], keep["m2"], C.byref(keep["b1"]),
+                C.byref(keep["b2"]), keep["masters"], len(params), lr_ratio.ctypes.data, with_decay.ctypes.data,
+                ref("ls"), ref("fi"), ref("gn"), ref("cl"))
+        return args + (keep,)  # the trailing dict only keeps the ctypes objects alive
 
     def _per_tensor_step(self, pg, found_inf, loss_scale):
         """Reference-shaped loop: one adam(w)_ call per parameter (ref adamw.py:445-465)."""

@@ -32,6 +32,7 @@ def main(out_dir):
             grads_all.append(per_rank)
         dp = prb.DataParallel(params, comm_buffer_size=0.4, last_comm_buffer_size=0.01)
         assert len(dp.group_indices) >= 3, dp.group_indices
+        assert dp._reducer.allreduce_backend == os.environ.get("PRB_ALLREDUCE", "nccl"), dp._reducer.allreduce_backend
         opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, multi_precision=dtype != orc.F32)
         for step in range(2):
             dp.prepare_for_backward()
@@ -85,6 +86,7 @@ def main(out_dir):
             np.save(os.path.join(out_dir, "pipe_param_%d_%d_r%d.npy" % (step, i, rank)), p.numpy())
         b1p, b2p = np.float32(0.9) * b1p, np.float32(0.999) * b2p
     assert opt._beta1_pow.numpy()[0] == b1p
+    assert not dp._reducer.comm_error()
     # timing helper used by bench.py: max over ranks through the communicator
     t = prb.Tensor.from_numpy(np.array([float(rank + 1)], np.float32))
     group.all_reduce(t, "max")

@@ -17,8 +17,9 @@ def _ngpus():
     return prb.device_count()
 
 
+@pytest.mark.parametrize("backend", ["nccl", "nvlink"])
 @pytest.mark.parametrize("nranks", [2, 4, 8])
-def test_dataparallel_grads_equal_across_ranks(tmp_path, nranks):
+def test_dataparallel_grads_equal_across_ranks(tmp_path, nranks, backend):
     if _ngpus() < nranks:
         pytest.skip("needs %d GPUs" % nranks)
     s = socket.socket()
@@ -28,7 +29,7 @@ def test_dataparallel_grads_equal_across_ranks(tmp_path, nranks):
     procs = []
     for r in range(nranks):
         env = {**os.environ, "RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(nranks), "MASTER_ADDR": "127.0.0.1",
-               "MASTER_PORT": str(port)}
+               "MASTER_PORT": str(port), "PRB_ALLREDUCE": backend}
         procs.append(subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "dist_worker.py"), str(tmp_path)],
                                       env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
     outs = [p.communicate(timeout=600)[0].decode() for p in procs]
