@@ -288,17 +288,17 @@ def run_gpu_arm(args):
     prb.synchronize()
     sampler = ClockSampler(group.device)
     ev0, ev1 = prb.Event(), prb.Event()
-    ka = [prb.Event() for _ in range(args.steps)]
-    kb = [prb.Event() for _ in range(args.steps)]
+    # CUDA events right around every optimizer launch (after its per-bucket stream wait), from a pre-built pool
+    ncalls = max(1, w["buckets"]) if w["dp"].pipelined else 1
+    w["opt"]._launch_events = [(prb.Event(), prb.Event()) for _ in range(args.steps * ncalls + 8)]
+    w["opt"]._launch_events_used = []
     launches0 = lib.prb_launch_count()
     sampler.start()
     ev0.record()
     for i in range(args.steps):
         w["dp"].prepare_for_backward()
         w["dp"].mark_all_ready()
-        ka[i].record()
-        tail()            # the dominant kernel: one fused multi-tensor AdamW launch (+ its 1-thread beta-pow kernel)
-        kb[i].record()
+        tail()            # the dominant kernel: the fused multi-tensor AdamW launch (one per bucket when pipelined)
     ev1.record()
     ev1.synchronize()
     clocks = sampler.stop()
@@ -308,7 +308,9 @@ def run_gpu_arm(args):
     ms_total = rank_max(ev0.elapsed_ms(ev1))
     ms_per_step = ms_total / args.steps
     value = bytes_per_step * nranks / (ms_per_step * 1e-3) / 1e9
-    tail_ms = float(np.mean([a.elapsed_ms(b) for a, b in zip(ka, kb)]))
+    used = w["opt"]._launch_events_used
+    w["opt"]._launch_events = None
+    tail_ms = float(sum(a.elapsed_ms(b) for a, b in used)) / args.steps   # optimizer launch time per step
 
     # ---- roofline of the dominant kernel (AdamW update pass): algorithmic bytes / live launch duration
     upd_bpe = 28 if w["gdt"] == w["pdt"] else 30
@@ -397,25 +399,21 @@ def measure_overlap(prb, w, group, tail, rank_max, steps=20):
     groups = list(reversed(dp.group_indices))  # launch order
     idx = [(C.c_int64 * len(g))(*g) for g in groups]
 
-    # total comm: the buckets' allreduces alone, back to back on the comm stream
-    views = [[dp._reducer.bucket_view(v) for v in g] for g in groups]
-    spans = []
-    for g, vs in zip(groups, views):
-        first = min(vs, key=lambda t: t.data_ptr)
-        last = max(vs, key=lambda t: t.data_ptr)
-        n = (last.data_ptr + last.nbytes - first.data_ptr) // (4 if w["gdt"] == "float32" else 2)
-        spans.append(prb.Tensor(n, w["gdt"], first.device, data_ptr=first.data_ptr, owner=dp))
+    # total comm: the buckets' allreduces alone (same backend as the step), back to back on the comm stream
+    red = dp._reducer
+    ng = len(groups)
     cs = group.comm_stream
+    prb.synchronize()
     for _ in range(3):
-        for t in spans:
-            group.all_reduce(t, stream=cs)
+        for k in range(ng):
+            red.allreduce_group(k, cs)
     cs.synchronize()
     group.barrier()
     e0, e1 = prb.Event(), prb.Event()
     e0.record(cs)
     for _ in range(steps):
-        for t in spans:
-            group.all_reduce(t, stream=cs)
+        for k in range(ng):
+            red.allreduce_group(k, cs)
     e1.record(cs)
     e1.synchronize()
     total_comm = rank_max(e0.elapsed_ms(e1)) / steps

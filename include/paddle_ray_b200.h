@@ -261,8 +261,8 @@ int32_t prb_reducer_num_groups(const PRB_Reducer* r);
 /* Index (in launch order, i.e. as passed to prb_reducer_create) of the group that holds parameter i. */
 int32_t prb_reducer_group_of(const PRB_Reducer* r, int64_t var_index, int64_t* out_group);
 /* Which allreduce runs the buckets: 0 = none (one rank / host-only), 1 = NCCL, 2 = the library's own two-shot
- * kernel over NVLink peer memory (PRB_ALLREDUCE=nvlink; single node, needs CUDA IPC between the ranks; falls
- * back to NCCL collectively when it cannot be set up).  prb_reducer_comm_error reports (synchronously) whether
+ * kernel over NVLink peer memory (the default on a single node; needs CUDA IPC between the ranks and falls back to
+ * NCCL collectively when it cannot be set up; PRB_ALLREDUCE=nccl forces NCCL).  prb_reducer_comm_error reports (synchronously) whether
  * a wait inside that kernel ever ran into its time limit, i.e. a peer never arrived. */
 int32_t prb_reducer_allreduce_backend(const PRB_Reducer* r);
 /* Only the allreduce of one group's bucket region, in place, on `stream` (measurement aid: lets a benchmark time

@@ -22,8 +22,8 @@
 // to NCCL's for two ranks (one addition); for more ranks the fp32 accumulation with one final rounding
 // is at least as accurate as pairwise sums in T.
 //
-// Selected with PRB_ALLREDUCE=nvlink (needs CUDA IPC between the ranks; falls back to NCCL if any rank
-// cannot set it up -- the decision is taken collectively).
+// The default for multi-rank reducers (PRB_ALLREDUCE=nccl forces NCCL).  Needs CUDA IPC between the ranks;
+// falls back to NCCL if any rank cannot set it up -- the decision is taken collectively.
 #include "prb_nvlink.h"
 
 namespace prb {

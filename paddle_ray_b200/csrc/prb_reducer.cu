@@ -561,14 +561,17 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
     prb_reducer_destroy(r);
     PRB_FAIL(PRB_EXTERNAL, "reducer_create: CUDA error %s", cudaGetErrorString(e));
   }
-  // The persistent arena is registered with the communicator once (the reference's per-step buckets never
-  // can be): NCCL then reduces straight out of it over NVLink / NVLS without staging copies.
-  if (comm->nranks > 1 && g_nccl.CommRegister != nullptr && getenv("PRB_NO_NCCL_REGISTER") == nullptr) {
+  // Opt-in (PRB_NCCL_REGISTER=1): register the persistent arena with the communicator so NCCL can reduce
+  // straight out of it.  Measured on 8 x B200 with NCCL 2.27.3 it is a large LOSS (8 MiB allreduce 2.7 ms
+  // registered vs 72 us unregistered, profiles/r1_multi_gpu.md), so it stays off by default.
+  if (comm->nranks > 1 && g_nccl.CommRegister != nullptr && getenv("PRB_NCCL_REGISTER") != nullptr) {
     if (g_nccl.CommRegister(comm->comm, r->arena, arena, &r->arena_reg) != ncclSuccess) r->arena_reg = nullptr;
   }
   // Optional: allreduce written as our own kernel over NVLink peer memory instead of NCCL.
+  // Default on a single NVSwitch node; PRB_ALLREDUCE=nccl forces NCCL.  nvl_setup decides collectively and leaves
+  // r->nvl NULL (NCCL) when CUDA IPC between the ranks is not available.
   const char* ar = getenv("PRB_ALLREDUCE");
-  if (comm->nranks > 1 && ar != nullptr && strcmp(ar, "nvlink") == 0) {
+  if (comm->nranks > 1 && (ar == nullptr || strcmp(ar, "nvlink") == 0)) {
     NvlCollectives nc{(void*)comm->comm, nvl_all_gather_bytes, nvl_all_min_int};
     int32_t st = nvl_setup(nc, comm->nranks, comm->rank, r->arena, arena, comm->stream, &r->nvl);
     if (st != PRB_SUCCESS) {

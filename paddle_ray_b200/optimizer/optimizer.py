@@ -80,6 +80,8 @@ class Optimizer:
         self._lr_value = None
         self._lr_feeder = None
         self._step_plans = {}
+        self._launch_events = None      # pool of (start, stop) Event pairs handed in by a benchmark
+        self._launch_events_used = []
         # True folds clear_grad(set_to_zero=True) into the update pass (gradients are zeroed as they are consumed)
         self._zero_grads_in_step = False
         # True keeps p.grad reference-visible after an AMP step (the unscaled gradient is stored back)
@@ -186,7 +188,15 @@ class Optimizer:
                     dp.wait_all_groups()
                 else:
                     dp.wait_group(gi)
-            call("prb_dp_step_tail", args[0], args[1], args[2], lr_ref, *args[4:16], stream)
+            ev = self._launch_events
+            if ev is not None:  # measurement hook: CUDA events right around each launch (after its stream wait)
+                a, b = ev.pop()
+                a.record()
+                call("prb_dp_step_tail", args[0], args[1], args[2], lr_ref, *args[4:16], stream)
+                b.record()
+                self._launch_events_used.append((a, b))
+            else:
+                call("prb_dp_step_tail", args[0], args[1], args[2], lr_ref, *args[4:16], stream)
 
     def _tensor_attrs(self, pg):
         lr_ratio = np.ones(len(pg), np.float32)

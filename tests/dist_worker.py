@@ -32,7 +32,7 @@ def main(out_dir):
             grads_all.append(per_rank)
         dp = prb.DataParallel(params, comm_buffer_size=0.4, last_comm_buffer_size=0.01)
         assert len(dp.group_indices) >= 3, dp.group_indices
-        assert dp._reducer.allreduce_backend == os.environ.get("PRB_ALLREDUCE", "nccl"), dp._reducer.allreduce_backend
+        assert dp._reducer.allreduce_backend == os.environ.get("PRB_ALLREDUCE", "nvlink"), dp._reducer.allreduce_backend
         opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, multi_precision=dtype != orc.F32)
         for step in range(2):
             dp.prepare_for_backward()
