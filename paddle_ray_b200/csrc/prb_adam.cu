@@ -98,7 +98,8 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
   const bool skipped = a.skip != nullptr && *a.skip;
   if (skipped && !a.zero_grad) return;
 
-  const int4 craw = __ldg(reinterpret_cast<const int4*>(a.chunks) + blockIdx.x);
+  const int cidx = a.reverse ? a.nchunks - 1 - (int)blockIdx.x : (int)blockIdx.x;
+  const int4 craw = __ldg(reinterpret_cast<const int4*>(a.chunks) + cidx);
   const int tensor = craw.x;
   const int n = craw.y;
   const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);

@@ -41,6 +41,9 @@ struct AdamArgs {
   float* pow_b1;             // nullptr = off
   float* pow_b2;
   unsigned int* pow_ticket;  // zero-initialised device counter, reset by the last CTA
+  // 1: CTA b takes chunk nchunks-1-b (walk the table backwards after a forward pass, hoping for L2 hits on the
+  // gradients touched last).  Measured neutral on B200, so it is off unless PRB_TAIL_REVERSE is set.
+  int32_t reverse;
 };
 
 // Elements per CTA of the active launch geometry (threads * kVec * lane-vectors per thread).
