@@ -84,8 +84,6 @@ int sm_count();            // of the current device (cached)
 int32_t workspace(size_t bytes, void** out, int slot);
 // One zero-initialised 32-bit device counter per device (ticket of the fused beta-pow update).
 int32_t ticket_counter(void** out);
-// Pinned host staging, same policy.
-int32_t host_staging(size_t bytes, void** out, int slot);
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------- element conversions

@@ -50,7 +50,6 @@ struct Slot {
 };
 std::mutex g_ws_mu;
 std::unordered_map<int, std::vector<Slot>> g_ws;    // device -> slots
-std::vector<Slot> g_host_ws;
 }  // namespace
 
 int32_t workspace(size_t bytes, void** out, int slot) {
@@ -86,22 +85,6 @@ int32_t ticket_counter(void** out) {
     it = counters.emplace(dev, p).first;
   }
   *out = it->second;
-  return PRB_SUCCESS;
-}
-
-int32_t host_staging(size_t bytes, void** out, int slot) {
-  std::lock_guard<std::mutex> lk(g_ws_mu);
-  if ((int)g_host_ws.size() <= slot) g_host_ws.resize(slot + 1);
-  Slot& s = g_host_ws[slot];
-  if (s.bytes < bytes) {
-    if (s.ptr) PRB_CUDA(cudaFreeHost(s.ptr));
-    s.ptr = nullptr;
-    s.bytes = 0;
-    size_t want = bytes < 4096 ? 4096 : bytes + bytes / 4;
-    PRB_CUDA(cudaMallocHost(&s.ptr, want));
-    s.bytes = want;
-  }
-  *out = s.ptr;
   return PRB_SUCCESS;
 }
 

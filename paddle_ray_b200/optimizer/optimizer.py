@@ -146,7 +146,6 @@ class Optimizer:
         # fill_value = beta (ref adamw.py:343-362): the first step divides by 1 - beta^1
         self._beta1_pow = Tensor.from_numpy(np.array([self._beta1], np.float32))
         self._beta2_pow = Tensor.from_numpy(np.array([self._beta2], np.float32))
-        self._found_inf_false = Tensor.zeros(1, BOOL)
         self._created = True
 
     def _find_master(self, p):
