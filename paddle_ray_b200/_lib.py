@@ -134,6 +134,9 @@ for _name, _args in SIGNATURES.items():
     _fn.restype = _RESTYPES.get(_name, _i32)
 
 
+C = C  # re-exported for callers that build ctypes arguments
+
+
 def last_error() -> str:
     return lib.prb_last_error_message().decode()
 

@@ -87,6 +87,21 @@ def main(out_dir):
         b1p, b2p = np.float32(0.9) * b1p, np.float32(0.999) * b2p
     assert opt._beta1_pow.numpy()[0] == b1p
     assert not dp._reducer.comm_error()
+    # fleet-style non-overlapped sync (hybrid_parallel_util.py:73-111): coalesce -> scale -> allreduce -> split
+    fl = []
+    for i, sz in enumerate(sizes[:6]):
+        p = prb.Tensor.zeros(sz, "float32", name="f_%d" % i)
+        p.grad = prb.Tensor.from_numpy(grads_all[i][rank])
+        fl.append(p)
+    prb.distributed.fused_allreduce_gradients_with_group(fl, group, bucket_size=1 << 14)
+    prb.current_stream().synchronize()
+    for i, p in enumerate(fl):
+        want = np.sum([orc.scale(g, orc.F32, 1.0 / n, 0.0, True).astype(np.float64) for g in grads_all[i]], axis=0)
+        if n == 2:
+            np.testing.assert_array_equal(p.grad.numpy(), want.astype(np.float32))
+        else:
+            np.testing.assert_allclose(p.grad.numpy(), want, rtol=1e-6, atol=1e-8)
+        np.save(os.path.join(out_dir, "fleet_grad_%d_r%d.npy" % (i, rank)), p.grad.numpy())
     # timing helper used by bench.py: max over ranks through the communicator
     t = prb.Tensor.from_numpy(np.array([float(rank + 1)], np.float32))
     group.all_reduce(t, "max")

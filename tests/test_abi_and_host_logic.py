@@ -229,3 +229,12 @@ def test_parallel_env_reads_reference_and_torchrun_names(monkeypatch):
     monkeypatch.setenv("MASTER_PORT", "29501")
     e = ParallelEnv()
     assert (e.rank, e.world_size, e.device_id, e.master_port, e.under_torchrun) == (1, 2, 1, 29501, True)
+
+
+def test_fleet_build_groups_matches_reference_rule(prb):
+    """parallel.py:136-153: the size check comes BEFORE adding, and a dtype change always starts a new group."""
+    mk = lambda n, dt: prb.Tensor(n, dt, device=-1)  # noqa: E731
+    vs = [mk(100, "float32"), mk(100, "float32"), mk(100, "float32"), mk(50, "bfloat16"), mk(50, "bfloat16"), mk(10, "float32")]
+    groups = prb.distributed.build_groups(vs, 700)
+    assert [[v.numel for v in g] for g in groups] == [[100, 100], [100], [50, 50], [10]]
+    assert [[v.numel for v in g] for g in prb.distributed.build_groups(vs, 10 ** 9)] == [[100, 100, 100], [50, 50], [10]]

@@ -230,3 +230,25 @@ def test_clear_grad_folded_into_the_step(prb):
     check(prb, opt, params, host, orc.F32)
     for p in params:
         assert not p.grad.numpy().any()
+
+
+def test_fleet_style_fused_allreduce_single_rank(prb):
+    """hybrid_parallel_util.py:73-111 with one rank: scale = 1.0 -> no scale, grads come back bit for bit;
+    an explicit scale goes through Tensor.scale_ (scale * x + 0); main_grad takes precedence over grad."""
+    rng = np.random.default_rng(12)
+    params, host = make_params(prb, rng, SIZES, orc.BF16)
+    params[2].main_grad = prb.Tensor.from_numpy(rng.normal(0, 1, params[2].numel).astype(np.float32))
+    mg = params[2].main_grad.numpy()
+    params[2].grad = None
+    prb.distributed.fused_allreduce_gradients_with_group(params, None, bucket_size=1 << 20)
+    for i, (p, h) in enumerate(zip(params, host)):
+        if i == 2:
+            bits_equal(p.main_grad.numpy(), mg)
+        else:
+            bits_equal(p.grad.numpy(), h["grad"])
+    prb.distributed.fused_allreduce_gradients_with_group(params, None, bucket_size=1 << 20, scale=0.25)
+    for i, (p, h) in enumerate(zip(params, host)):
+        if i == 2:
+            bits_equal(p.main_grad.numpy(), orc.scale(mg, orc.F32, 0.25, 0.0, True))
+        else:
+            bits_equal(p.grad.numpy(), orc.scale(h["grad"], orc.BF16, 0.25, 0.0, True))
