@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
 
   if (aligned) {
     const int nvec = n / kVec;
+    const uint64_t pol = l2_policy(a.l2_hints ? 1 : 0);
     Pack<T> pv[kAdamUnroll];
     Pack<float> mpv[kAdamUnroll];
     Pack<TG> gv[kAdamUnroll];
@@ -132,11 +133,11 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
       const int v = u * kAdamThreads + threadIdx.x;
       if (v < nvec) {
         const int e = v * kVec;
-        if (kMaster) load_vec<float>(mp_ptr + e, mpv[u]);
-        else load_vec<T>(p_ptr + e, pv[u]);
-        load_vec<TG>(g_ptr + e, gv[u]);
-        load_vec<float>(m1_ptr + e, m1v[u]);
-        load_vec<float>(m2_ptr + e, m2v[u]);
+        if (kMaster) load_vec_hint<float>(mp_ptr + e, mpv[u], pol);
+        else load_vec_hint<T>(p_ptr + e, pv[u], pol);
+        load_vec_hint<TG>(g_ptr + e, gv[u], pol);
+        load_vec_hint<float>(m1_ptr + e, m1v[u], pol);
+        load_vec_hint<float>(m2_ptr + e, m2v[u], pol);
       }
     }
     if (threadIdx.x == 0) {
@@ -162,10 +163,10 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
           if (kMaster) mpv[u].v[j] = p;
           go.v[j] = a.zero_grad ? Conv<TG>::from_f32(0.0f) : Conv<TG>::from_f32(gu);
         }
-        store_vec<float>(m1_ptr + e, m1v[u]);
-        store_vec<float>(m2_ptr + e, m2v[u]);
-        store_vec<T>(p_ptr + e, po);
-        if (kMaster) store_vec<float>(mp_ptr + e, mpv[u]);
+        store_vec_hint<float>(m1_ptr + e, m1v[u], pol);
+        store_vec_hint<float>(m2_ptr + e, m2v[u], pol);
+        store_vec_hint<T>(p_ptr + e, po, pol);
+        if (kMaster) store_vec_hint<float>(mp_ptr + e, mpv[u], pol);
         if (a.zero_grad) store_vec<TG>(const_cast<TG*>(g_ptr) + e, go);
         else if (go_ptr) store_vec<TG>(go_ptr + e, go);
       }

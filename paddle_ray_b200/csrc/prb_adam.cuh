@@ -44,6 +44,7 @@ struct AdamArgs {
   // 1: CTA b takes chunk nchunks-1-b (walk the table backwards after a forward pass, hoping for L2 hits on the
   // gradients touched last).  Measured neutral on B200, so it is off unless PRB_TAIL_REVERSE is set.
   int32_t reverse;
+  int32_t l2_hints;  // experiment: stream params/moments with evict_first so a bucket kept with evict_last survives
 };
 
 // Elements per CTA of the active launch geometry (threads * kVec * lane-vectors per thread).

@@ -55,7 +55,7 @@ struct ScaleOp {
 template <typename T, typename Op, int kMapThreads, int kMapUnroll, int kMinBlocks>
 __global__ void __launch_bounds__(kMapThreads, kMinBlocks) map_chunks_kernel(const MapDesc* __restrict__ descs,
                                                                              const Chunk* __restrict__ chunks,
-                                                                             const Op op) {
+                                                                             const Op op, const int l2_hints) {
   const int4 craw = __ldg(reinterpret_cast<const int4*>(chunks) + blockIdx.x);
   const int n = craw.y;
   const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
@@ -64,11 +64,14 @@ __global__ void __launch_bounds__(kMapThreads, kMinBlocks) map_chunks_kernel(con
   T* __restrict__ dst = reinterpret_cast<T*>(d->dst) + offset;
   if (d->aligned) {
     const int nvec = n / kVec;
+    // experiment (PRB_L2_HINTS): the destination (a bucket that the optimizer re-reads next) is kept, the source streamed
+    // l2_hints = percentage of the destination lines to keep (evict_last); 0 = no steering
+    const uint64_t pol_ld = l2_policy(l2_hints ? 1 : 0), pol_st = l2_hints ? l2_policy_keep(l2_hints) : l2_policy(0);
     Pack<T> v[kMapUnroll];
 #pragma unroll
     for (int u = 0; u < kMapUnroll; ++u) {
       const int i = u * kMapThreads + threadIdx.x;
-      if (i < nvec) load_vec<T>(src + i * kVec, v[u]);
+      if (i < nvec) load_vec_hint<T>(src + i * kVec, v[u], pol_ld);
     }
 #pragma unroll
     for (int u = 0; u < kMapUnroll; ++u) {
@@ -76,7 +79,7 @@ __global__ void __launch_bounds__(kMapThreads, kMinBlocks) map_chunks_kernel(con
       if (i < nvec) {
 #pragma unroll
         for (int j = 0; j < kVec; ++j) v[u].v[j] = op(v[u].v[j]);
-        store_vec<T>(dst + i * kVec, v[u]);
+        store_vec_hint<T>(dst + i * kVec, v[u], pol_st);
       }
     }
     const int e = nvec * kVec + threadIdx.x;
@@ -92,7 +95,8 @@ template <typename T, typename Op>
 int32_t launch_map_typed(const DeviceTable& tab, const Op& op, cudaStream_t stream) {
   if (tab.nchunks == 0) return PRB_SUCCESS;
   const MapDesc* d = reinterpret_cast<const MapDesc*>(tab.descs);
-#define PRB_MAP(T_, U_, B_) map_chunks_kernel<T, Op, T_, U_, B_><<<tab.nchunks, T_, 0, stream>>>(d, tab.chunks, op)
+#define PRB_MAP(T_, U_, B_) \
+  map_chunks_kernel<T, Op, T_, U_, B_><<<tab.nchunks, T_, 0, stream>>>(d, tab.chunks, op, l2_hints())
   switch (active_map_variant()) {
     case 0: PRB_MAP(256, 4, 2); break;
     case 1: PRB_MAP(256, 2, 4); break;

@@ -78,6 +78,7 @@ inline const char* dtype_name(int32_t dt) {
 
 int32_t require_device();  // PRB_EXTERNAL if no usable CUDA device (no CPU fallback exists)
 int sm_count();            // of the current device (cached)
+int l2_hints();            // PRB_L2_HINTS (experiment switch): 1 = steer L2 with eviction policies
 
 // ---------------------------------------------------------------- workspace
 // Library-owned persistent device scratch, grown on demand (never shrinks); one per device.
@@ -153,6 +154,53 @@ __device__ __forceinline__ void store_vec(T* __restrict__ p, const Pack<T>& i) {
                  : "memory");
   } else {
     asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3])
+                 : "memory");
+  }
+}
+
+// ---- the same accesses with an explicit L2 eviction policy (createpolicy + .L2::cache_hint)
+// kind: 0 = evict_normal, 1 = evict_first (streamed once), 2 = evict_last (about to be re-read)
+__device__ __forceinline__ uint64_t l2_policy(int kind) {
+  uint64_t normal, first, last;
+  asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(normal));
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(first));
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(last));
+  return kind == 1 ? first : (kind == 2 ? last : normal);
+}
+// evict_last for about `pct` percent of the lines (25/50/75/100), evict_first for the rest: keeps as much of a
+// buffer as the L2 can actually hold instead of letting an over-sized "keep" set thrash.
+__device__ __forceinline__ uint64_t l2_policy_keep(int pct) {
+  uint64_t p25, p50, p75, p100, first;
+  asm volatile("createpolicy.fractional.L2::evict_last.L2::evict_first.b64 %0, 0.25;" : "=l"(p25));
+  asm volatile("createpolicy.fractional.L2::evict_last.L2::evict_first.b64 %0, 0.5;" : "=l"(p50));
+  asm volatile("createpolicy.fractional.L2::evict_last.L2::evict_first.b64 %0, 0.75;" : "=l"(p75));
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p100));
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(first));
+  return pct >= 100 ? p100 : (pct >= 75 ? p75 : (pct >= 50 ? p50 : (pct >= 25 ? p25 : first)));
+}
+template <typename T>
+__device__ __forceinline__ void load_vec_hint(const T* __restrict__ p, Pack<T>& o, uint64_t pol) {
+  uint32_t* w = reinterpret_cast<uint32_t*>(o.v);
+  if constexpr (sizeof(T) == 4) {
+    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(p), "l"(pol));
+  } else {
+    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
+                 : "l"(p), "l"(pol));
+  }
+}
+template <typename T>
+__device__ __forceinline__ void store_vec_hint(T* __restrict__ p, const Pack<T>& i, uint64_t pol) {
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(i.v);
+  if constexpr (sizeof(T) == 4) {
+    asm volatile("st.global.L2::cache_hint.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8}, %9;" ::"l"(p), "r"(w[0]), "r"(w[1]),
+                 "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]), "l"(pol)
+                 : "memory");
+  } else {
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                 "r"(w[3]), "l"(pol)
                  : "memory");
   }
 }

@@ -43,6 +43,14 @@ int sm_count() {
   return cached[dev];
 }
 
+int l2_hints() {
+  static int v = [] {
+    const char* e = getenv("PRB_L2_HINTS");
+    return e ? atoi(e) : 0;
+  }();
+  return v;
+}
+
 namespace {
 struct Slot {
   void* ptr = nullptr;

@@ -139,6 +139,7 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   a.loss_scale = ls;
   a.clip = clip_dev;
   a.zero_grad = cfg->zero_grads;
+  a.l2_hints = l2_hints();
   a.reverse = getenv("PRB_TAIL_REVERSE") != nullptr ? 1 : 0;  // measured neutral on B200 (profiles/r1_experiments.md)
   // beta-pow accumulators advance inside the update kernel (last-CTA ticket) unless found_inf
   void* tk = nullptr;
