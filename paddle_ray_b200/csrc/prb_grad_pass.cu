@@ -26,6 +26,50 @@ int active_grad_variant() {
   return v;
 }
 
+// Two 16-bit elements at a time.  For bf16/fp16 gradients the pass is issue-bound, not HBM-bound (ncu: 64 % issue
+// slots, 39 % DRAM), so the per-element work is done on packed pairs: one cvt packs two narrowed values, the
+// non-finite test is two integer ops on the packed exponents, and the T-rounded square is ONE packed multiply --
+// exact, because the product of two 8-bit (11-bit) significands fits fp32, so rounding it once to T is what
+// "T(x) * T(x)" means.  Results are bit-identical to the element-wise code.
+template <typename T>
+struct Pair;
+template <>
+struct Pair<__nv_bfloat16> {
+  static __device__ __forceinline__ void unpack(uint32_t w, float& lo, float& hi) {
+    lo = __uint_as_float(w << 16);
+    hi = __uint_as_float(w & 0xffff0000u);
+  }
+  static __device__ __forceinline__ uint32_t pack_rn(float lo, float hi) {
+    const __nv_bfloat162 r = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&r);
+  }
+  // bit 15 / 31 set iff the exponent field of the low / high half is all ones (inf or nan)
+  static __device__ __forceinline__ uint32_t nonfinite(uint32_t w) { return ((w & 0x7F807F80u) + 0x00800080u) & 0x80008000u; }
+  static __device__ __forceinline__ uint32_t square(uint32_t w) {
+    const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&w);
+    const __nv_bfloat162 r = __hmul2(v, v);
+    return *reinterpret_cast<const uint32_t*>(&r);
+  }
+};
+template <>
+struct Pair<__half> {
+  static __device__ __forceinline__ void unpack(uint32_t w, float& lo, float& hi) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+    lo = f.x;
+    hi = f.y;
+  }
+  static __device__ __forceinline__ uint32_t pack_rn(float lo, float hi) {
+    const __half2 r = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&r);
+  }
+  static __device__ __forceinline__ uint32_t nonfinite(uint32_t w) { return ((w & 0x7C007C00u) + 0x04000400u) & 0x80008000u; }
+  static __device__ __forceinline__ uint32_t square(uint32_t w) {
+    const __half2 v = *reinterpret_cast<const __half2*>(&w);
+    const __half2 r = __hmul2(v, v);
+    return *reinterpret_cast<const uint32_t*>(&r);
+  }
+};
+
 template <typename T, bool kWrite, bool kNorm, bool kMp, int kGradThreads, int kGradUnroll, int kMinBlocks>
 __global__ void __launch_bounds__(kGradThreads, kMinBlocks) grad_pass_kernel(const GradDesc* __restrict__ descs,
                                                                  const Chunk* __restrict__ chunks,
@@ -43,6 +87,7 @@ __global__ void __launch_bounds__(kGradThreads, kMinBlocks) grad_pass_kernel(con
 
   float acc = 0.0f;
   bool bad = false;
+  uint32_t bad_bits = 0;
   float inv = 1.0f;
 
   auto elem = [&](T raw) -> T {
@@ -75,11 +120,32 @@ __global__ void __launch_bounds__(kGradThreads, kMinBlocks) grad_pass_kernel(con
     for (int u = 0; u < kGradUnroll; ++u) {
       const int i = u * kGradThreads + threadIdx.x;
       if (i < nvec) {
+        if constexpr (sizeof(T) == 2 && !kMp) {
+          uint32_t* w = reinterpret_cast<uint32_t*>(v[u].v);
 #pragma unroll
-        for (int j = 0; j < kVec; ++j) v[u].v[j] = elem(v[u].v[j]);
+          for (int j = 0; j < kVec / 2; ++j) {
+            uint32_t nw = w[j];
+            if (amp) {
+              float lo, hi;
+              Pair<T>::unpack(nw, lo, hi);
+              nw = Pair<T>::pack_rn(__fmul_rn(lo, inv), __fmul_rn(hi, inv));  // narrow = T(MT(x) * inv)
+              bad_bits |= Pair<T>::nonfinite(nw);                             // finite check on the narrowed value
+              w[j] = nw;
+            }
+            if (kNorm) {
+              float lo, hi;
+              Pair<T>::unpack(Pair<T>::square(nw), lo, hi);  // T(x)*T(x) rounded to T, both halves at once
+              acc = __fadd_rn(__fadd_rn(acc, lo), hi);       // same order as the element-wise code
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < kVec; ++j) v[u].v[j] = elem(v[u].v[j]);
+        }
         if (kWrite) store_vec<T>(out + i * kVec, v[u]);
       }
     }
+    if (bad_bits) bad = true;
     const int e = nvec * kVec + threadIdx.x;
     if (e < n) {
       const T r = elem(x[e]);

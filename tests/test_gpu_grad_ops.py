@@ -73,6 +73,42 @@ def test_check_finite_on_the_narrowed_value(prb):
     assert not bool(found.numpy()[0])
 
 
+@pytest.mark.parametrize("dtype", [orc.BF16, orc.F16])
+def test_16bit_packed_pairs_edge_values(prb, dtype):
+    """The 16-bit pass works on packed pairs: subnormal products, values that overflow when narrowed, NaN/Inf in
+    either half of a pair, odd lengths -- all must agree with the element-wise oracle bit for bit."""
+    rng = np.random.default_rng(21)
+    n = 8192 * 2 + 5
+    mag = 10.0 ** rng.uniform(-30 if dtype == orc.BF16 else -7, 3, n)
+    x32 = (mag * rng.choice([-1.0, 1.0], n)).astype(np.float32)
+    x = orc.from_f32(x32, dtype)
+    t = prb.Tensor.from_numpy(x, dtype)
+    s = prb.Tensor.from_numpy(np.array([0.37], np.float32))
+    _, found = prb._C_ops.check_finite_and_unscale_([t], s)
+    ref = x.copy()
+    f = orc.check_finite_and_unscale([ref], dtype, 0.37)
+    bits_equal(t.numpy(), ref)
+    assert bool(found.numpy()[0]) == f
+    got = orc.to_f32(prb._C_ops.squared_l2_norm(t).numpy(), dtype)[0]
+    _, want64 = orc.squared_l2_norm(ref, dtype)
+    if np.isfinite(want64) and want64 < (6e4 if dtype == orc.F16 else 3e38):
+        np.testing.assert_allclose(got, want64, rtol=8e-3 if dtype == orc.BF16 else 2e-3)
+    else:
+        assert not np.isfinite(got)
+    for pos in (0, 1, n - 1, 8191, 8192):  # a poisoned element in the low half, the high half, the ragged tail
+        for poison in (np.inf, np.nan):
+            y = x.copy()
+            y[pos] = orc.from_f32(np.array([poison], np.float32), dtype)[0]
+            t.copy_from_numpy(y)
+            _, found = prb._C_ops.check_finite_and_unscale_([t], s, found)
+            assert bool(found.numpy()[0]), (pos, poison)
+    small = orc.from_f32(np.array([3e-5, -2e-5, 1e-6, 0.0, -0.0, 7e-5, 6e-8, 1.0], np.float32), dtype)
+    ts = prb.Tensor.from_numpy(small, dtype)
+    got = prb._C_ops.squared_l2_norm(ts).numpy()
+    want, _ = orc.squared_l2_norm(small, dtype)   # sequential oracle: same order for 8 elements of one thread
+    bits_equal(got, orc.from_f32(np.array([want], np.float32), dtype))
+
+
 # ------------------------------------------------------------------ squared_l2_norm / clip
 def test_squared_l2_norm_reference_cases(prb, golden_dir):
     fx = np.load(os.path.join(golden_dir, "squared_l2_norm_optest.npz"))
