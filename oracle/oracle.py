@@ -187,7 +187,9 @@ def global_norm_clip(grads, dtypes, clip_norm: float, auto_skip_clip: bool = Fal
     for g, dt in zip(grads, dtypes):
         v, v64 = squared_l2_norm(g, dt, mp=mp)
         if dt in (F16, BF16) and not mp:
-            s16.append(v)
+            # the op's T-typed output; the order-free fp64 sum is narrowed once (a sequential float sum of
+            # millions of T-rounded squares stagnates and is NOT what a tree reduction on the GPU produces)
+            s16.append(float(to_f32(from_f32(np.array([v64], np.float32), dt), dt)[0]))
             dt16 = dt
         else:
             s32.append(v64 if dt == F32 or mp else v)

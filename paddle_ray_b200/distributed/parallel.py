@@ -91,6 +91,7 @@ class Group:
 
 
 _default_group: Group | None = None
+_init_calls = 0  # every rank makes the same sequence of calls, so the count names the communicator
 
 
 def init_parallel_env(store=None) -> Group:
@@ -99,7 +100,9 @@ def init_parallel_env(store=None) -> Group:
     Rank 0 creates the NCCL unique id and publishes it under the reference's key; peers fetch it.
     ``store`` may be any object with ``set(key, bytes)`` / ``get(key) -> bytes``.
     """
-    global _default_group
+    global _default_group, _init_calls
+    gid = _init_calls
+    _init_calls += 1
     env = ParallelEnv()
     core.set_device(env.device_id)
     h = C.c_void_p()
@@ -113,7 +116,7 @@ def init_parallel_env(store=None) -> Group:
                 store = FileStore(path)
             else:
                 store = TCPStore(env.master_addr, env.master_port, env.rank == 0, env.world_size)
-        key = "ProcessGroupNCCL/nccl_ids/0/0"
+        key = "ProcessGroupNCCL/nccl_ids/%d/0" % gid
         uid = (C.c_uint8 * _lib.UNIQUE_ID_BYTES)()
         if env.rank == 0:
             call("prb_comm_get_unique_id", uid)

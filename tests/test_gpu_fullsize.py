@@ -131,3 +131,76 @@ def test_two_billion_element_sweep_fp32(prb):
     g.view(n - 1, 1).copy_from_numpy(np.array([np.inf], np.float32))
     prb._C_ops.check_finite_and_unscale_([g], scale, found)
     assert found.numpy()[0]
+
+
+def _full_config_step(prb, shapes_name, dtype, amp, clip_norm, steps):
+    """The bench workload at its real size through the public API, every tensor checked against the oracle's
+    composition of the reference's stages (concat -> scale -> split -> unscale/check -> clip -> adamw)."""
+    numels = bench_configs.param_numels(shapes_name)
+    rng = np.random.default_rng(77)
+    params, host = [], []
+    for i, n in enumerate(numels):
+        p = orc.from_f32(rng.standard_normal(n, dtype=np.float32) * np.float32(0.02), dtype)
+        t = prb.Tensor.from_numpy(p, dtype, name="w_%d" % i)
+        t.grad = prb.Tensor.zeros(n, dtype)
+        params.append(t)
+        host.append({"param": p, "mom1": np.zeros(n, np.float32), "mom2": np.zeros(n, np.float32),
+                     "master": orc.to_f32(p, dtype) if dtype != orc.F32 else None})
+    clip = prb.nn.ClipGradByGlobalNorm(clip_norm) if clip_norm else None
+    opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, weight_decay=0.01, grad_clip=clip,
+                              multi_precision=dtype != orc.F32)
+    scaler = prb.amp.GradScaler(init_loss_scaling=2.0 ** 15) if amp else None
+    dp = prb.DataParallel(params, comm_buffer_size=25, last_comm_buffer_size=1, consume_from_buckets=True)
+    b1p, b2p = np.float32(0.9), np.float32(0.999)
+    for step in range(steps):
+        grads = []
+        for p in params:
+            g = rng.standard_normal(p.numel, dtype=np.float32) * np.float32(1e-2 * (2.0 ** 15 if amp else 1.0))
+            g = orc.from_f32(g, dtype)
+            p.grad.copy_from_numpy(g)
+            grads.append(g)
+        dp.prepare_for_backward()
+        dp.mark_all_ready()
+        if scaler is not None:
+            scaler.step(opt)
+            scaler.update()
+        else:
+            opt.step()
+        # ---- oracle, reference order
+        bucket = orc.scale(orc.concat(grads), dtype, 1.0)
+        grads = orc.split(bucket, numels)
+        if amp:
+            assert not orc.check_finite_and_unscale(grads, dtype, 2.0 ** 15)
+            assert not scaler._found_inf.numpy()[0]
+        if clip_norm:
+            norm, cl = orc.global_norm_clip([g.copy() for g in grads], [dtype] * len(grads), clip_norm)
+            got_clip = clip.last_clip.numpy()[0]
+            tol = 4e-3 if dtype != orc.F32 else 2e-6
+            np.testing.assert_allclose(clip.last_global_norm.numpy()[0], norm, rtol=tol)
+            np.testing.assert_allclose(got_clip, cl, rtol=tol)
+            for g in grads:
+                orc.clip_mul(g, dtype, float(got_clip))
+        for h, g in zip(host, grads):
+            orc.adam(h["param"], g, h["mom1"], h["mom2"], h["master"], dtype_param=dtype, dtype_grad=dtype, lr=1e-3,
+                     beta1=0.9, beta2=0.999, epsilon=1e-8, coeff=0.01, use_decay=True, beta1_pow=b1p, beta2_pow=b2p)
+        b1p, b2p = np.float32(0.9) * b1p, np.float32(0.999) * b2p
+    for p, h in zip(params, host):
+        bits_equal(p.numpy(), h["param"])
+        acc = opt._accumulators[p.name]
+        bits_equal(acc["moment1"].numpy(), h["mom1"])
+        bits_equal(acc["moment2"].numpy(), h["mom2"])
+        if h["master"] is not None:
+            bits_equal(opt._master_weights[p.name].numpy(), h["master"])
+    assert opt._beta1_pow.numpy()[0] == b1p
+
+
+def test_resnet50_config_bit_exact_vs_oracle(prb):
+    """configs[1] at full size: 161 tensors, 25,557,032 fp32 elements, DataParallel + AdamW, 2 steps."""
+    prb.distributed.init_parallel_env()
+    _full_config_step(prb, "resnet50", orc.F32, amp=False, clip_norm=None, steps=2)
+
+
+def test_bert_base_config_bit_exact_vs_oracle(prb):
+    """configs[2] at full size: 206 tensors, 110,106,428 bf16 elements + fp32 master, AMP (2^15) + clip 1.0."""
+    prb.distributed.init_parallel_env()
+    _full_config_step(prb, "bert_base", orc.BF16, amp=True, clip_norm=1.0, steps=1)
