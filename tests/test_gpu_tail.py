@@ -252,3 +252,45 @@ def test_fleet_style_fused_allreduce_single_rank(prb):
             bits_equal(p.main_grad.numpy(), orc.scale(mg, orc.F32, 0.25, 0.0, True))
         else:
             bits_equal(p.grad.numpy(), orc.scale(h["grad"], orc.BF16, 0.25, 0.0, True))
+
+
+def test_reducer_hooks_in_any_order_unused_params_and_no_sync(prb):
+    """EagerReducer on the device: hooks arriving out of order (groups still launch in index order,
+    reducer.cc:916-919), parameters without a gradient this step (zero-filled slots, :833-855) and no_sync."""
+    rng = np.random.default_rng(13)
+    params, host = make_params(prb, rng, SIZES, orc.F32)
+    dp = prb.DataParallel(params, comm_buffer_size=0.1, last_comm_buffer_size=0.01, find_unused_parameters=True)
+    ngroups = len(dp.group_indices)
+    assert ngroups >= 3
+    # 1) random hook order
+    dp.prepare_for_backward()
+    order = list(rng.permutation(len(params)))
+    for k, i in enumerate(order):
+        dp.mark_var_ready(int(i))
+        assert dp._reducer.launched_groups() == sorted(dp._reducer.launched_groups())
+        assert dp.finalized == (k == len(order) - 1)
+    assert dp._reducer.launched_groups() == list(range(ngroups))
+    for p, h in zip(params, host):
+        bits_equal(p.grad.numpy(), orc.scale(h["grad"], orc.F32, 1.0))
+    # 2) two parameters get no gradient this step: their slots are zero-filled, everything else is untouched
+    unused = [2, 7]
+    dp.prepare_for_backward(unused_vars=unused)
+    for i in reversed(range(len(params))):
+        if i not in unused:
+            dp.mark_var_ready(i)
+    assert dp.finalized
+    for i, (p, h) in enumerate(zip(params, host)):
+        if i in unused:
+            assert not p.grad.numpy().any()
+            p.grad.copy_from_numpy(h["grad"])
+        else:
+            bits_equal(p.grad.numpy(), orc.scale(h["grad"], orc.F32, 1.0))
+    # 3) no_sync: hooks do nothing, the next synchronised backward works as usual
+    with dp.no_sync():
+        dp.prepare_for_backward()
+        dp.mark_all_ready()
+    dp.prepare_for_backward()
+    dp.mark_all_ready()
+    assert dp.finalized
+    for p, h in zip(params, host):
+        bits_equal(p.grad.numpy(), orc.scale(h["grad"], orc.F32, 1.0))
