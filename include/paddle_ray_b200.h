@@ -260,10 +260,12 @@ int32_t prb_reducer_wait_group(PRB_Reducer* r, int64_t group_index, void* stream
 int32_t prb_reducer_num_groups(const PRB_Reducer* r);
 /* Index (in launch order, i.e. as passed to prb_reducer_create) of the group that holds parameter i. */
 int32_t prb_reducer_group_of(const PRB_Reducer* r, int64_t var_index, int64_t* out_group);
-/* Which allreduce runs the buckets: 0 = none (one rank / host-only), 1 = NCCL, 2 = the library's own two-shot
- * kernel over NVLink peer memory (the default on a single node; needs CUDA IPC between the ranks and falls back to
- * NCCL collectively when it cannot be set up; PRB_ALLREDUCE=nccl forces NCCL).  prb_reducer_comm_error reports (synchronously) whether
- * a wait inside that kernel ever ran into its time limit, i.e. a peer never arrived. */
+/* Which allreduce runs the buckets: 0 = none (one rank / host-only), 1 = NCCL, 2 = the library's two-shot kernel
+ * over NVLink peer memory (CUDA IPC; the default), 3 = the library's kernel over NVLink multicast (NVLS: the switch
+ * adds and replicates).  PRB_ALLREDUCE = nvls | nvlink | nccl picks the first level to try; each level falls back
+ * to the next, collectively, when it cannot be set up (single node, one GPU per process required for 2 and 3).
+ * prb_reducer_comm_error reports (synchronously) whether a wait inside those kernels ever ran into its time limit,
+ * i.e. a peer never arrived. */
 int32_t prb_reducer_allreduce_backend(const PRB_Reducer* r);
 /* Only the allreduce of one group's bucket region, in place, on `stream` (measurement aid: lets a benchmark time
  * the exchange step of ref reducer.cc:1058 by itself with either backend). */

@@ -24,30 +24,10 @@
 //
 // The default for multi-rank reducers (PRB_ALLREDUCE=nccl forces NCCL).  Needs CUDA IPC between the ranks;
 // falls back to NCCL if any rank cannot set it up -- the decision is taken collectively.
-#include "prb_nvlink.h"
+#include "prb_nvl_common.cuh"
 
 namespace prb {
 namespace {
-
-constexpr int kMaxRanks = 8;
-constexpr int kNvlThreads = 256;
-constexpr int kNvlMinCtasPerSm = 4;  // register cap (<= 64): a CTA must find room next to the optimizer's CTAs
-// CTAs launched per SM.  The kernel is NVLink-bound and its CTAs mostly wait; 1 per SM (256 threads, ~12 % of an
-// SM's thread slots) leaves the SM to the optimizer kernels that run next to it: ResNet-50 N=2 step 0.30 ms vs
-// 0.35 ms with 2 or 4 per SM, same stand-alone bandwidth (profiles/r1_multi_gpu.md).
-constexpr int kNvlCtasPerSm = 1;
-constexpr unsigned long long kWaitLimitNs = 4000000000ull;  // 4 s
-
-// Two allreduces may be in flight at once (the reducer alternates two comm streams so that one bucket's
-// barriers hide under the next bucket's transfers); call number `seq` uses slot seq & 1, and calls that share
-// a slot are ordered by their stream, so the sequence numbers seen in a slot only grow.
-constexpr int kSlots = 2;
-struct Signals {                       // lives in each rank's device memory, written by its peers
-  unsigned long long ready[kSlots][kMaxRanks];
-  unsigned long long done[kSlots][kMaxRanks];
-  unsigned int cta_counter[kSlots];    // local: CTAs of this rank that finished their stores
-  unsigned int error;                  // local: a wait ran into the time limit
-};
 
 struct NvlArgs {
   char* arena[kMaxRanks];              // every rank's bucket arena as mapped into this process
@@ -57,27 +37,6 @@ struct NvlArgs {
   long long nvec;                      // 8-element vectors in the bucket
   unsigned long long seq;
 };
-
-__device__ __forceinline__ unsigned long long now_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ bool wait_at_least(const unsigned long long* p, unsigned long long v) {
-  const unsigned long long t0 = now_ns();
-  while (ld_acquire_sys(p) < v) {
-    if (now_ns() - t0 > kWaitLimitNs) return false;
-  }
-  return true;
-}
 
 // Peer loads/stores: plain (coherent at system scope after the barriers), 8 elements per access.
 template <typename T>
@@ -226,6 +185,53 @@ int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, s
   c->ctas = sm_count() * per_sm;
   *out = c;
   return PRB_SUCCESS;
+}
+
+int32_t signals_setup(const NvlCollectives& nc, int nranks, int rank, cudaStream_t stream, SignalSet* out, int* ok_out) {
+  int ok = 1;
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  if (cudaMalloc((void**)&out->mine, sizeof(Signals)) != cudaSuccess) ok = 0;
+  if (ok && cudaMemset(out->mine, 0, sizeof(Signals)) != cudaSuccess) ok = 0;
+  if (ok && cudaIpcGetMemHandle(&mine, out->mine) != cudaSuccess) ok = 0;
+  cudaGetLastError();
+  struct Packet {
+    int ok, pad;
+    cudaIpcMemHandle_t h;
+  } pk, all[kMaxRanks];
+  memset(&pk, 0, sizeof(pk));
+  pk.ok = ok;
+  pk.h = mine;
+  void *dsend = nullptr, *drecv = nullptr;
+  PRB_CUDA(cudaMalloc(&dsend, sizeof(Packet)));
+  PRB_CUDA(cudaMalloc(&drecv, sizeof(Packet) * nranks));
+  PRB_CUDA(cudaMemcpyAsync(dsend, &pk, sizeof(Packet), cudaMemcpyHostToDevice, stream));
+  PRB_TRY(nc.all_gather_bytes(nc.comm, dsend, drecv, sizeof(Packet), stream));
+  PRB_CUDA(cudaMemcpyAsync(all, drecv, sizeof(Packet) * nranks, cudaMemcpyDeviceToHost, stream));
+  PRB_CUDA(cudaStreamSynchronize(stream));
+  cudaFree(dsend);
+  cudaFree(drecv);
+  for (int q = 0; q < nranks; ++q) ok = ok && all[q].ok;
+  for (int q = 0; q < nranks && ok; ++q) {
+    if (q == rank) {
+      out->sig[q] = out->mine;
+      continue;
+    }
+    void* ps = nullptr;
+    if (cudaIpcOpenMemHandle(&ps, all[q].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
+    if (ok) out->opened[out->nopened++] = ps;
+    out->sig[q] = reinterpret_cast<Signals*>(ps);
+  }
+  cudaGetLastError();
+  *ok_out = ok;
+  return PRB_SUCCESS;
+}
+
+void signals_destroy(SignalSet* s) {
+  for (int i = 0; i < s->nopened; ++i) cudaIpcCloseMemHandle(s->opened[i]);
+  s->nopened = 0;
+  if (s->mine) cudaFree(s->mine);
+  s->mine = nullptr;
 }
 
 int nvl_next_slot(const NvlContext* c) { return c ? (int)((c->seq + 1) & (kSlots - 1)) : 0; }

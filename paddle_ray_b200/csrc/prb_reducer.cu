@@ -21,6 +21,7 @@
 
 #include "prb_bucket.cuh"
 #include "prb_nvlink.h"
+#include "prb_nvls.h"
 
 namespace prb {
 namespace {
@@ -150,7 +151,8 @@ struct PRB_Reducer {
   char* arena = nullptr;
   size_t arena_bytes = 0;
   void* arena_reg = nullptr;  // ncclCommRegister handle of the arena (NULL when unavailable)
-  NvlContext* nvl = nullptr;  // NVLink peer-memory allreduce (PRB_ALLREDUCE=nvlink), else NCCL
+  NvlContext* nvl = nullptr;    // allreduce over NVLink peer memory (prb_nvlink.cu)
+  NvlsContext* nvls = nullptr;  // allreduce through NVLink multicast (prb_nvls.cu); owns the arena when set
   size_t next_group = 0;
   std::vector<uint8_t> ready;
   std::vector<uint8_t> unused;
@@ -226,10 +228,13 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   if (c->nranks > 1) {
     // SyncDefaultStream: comm stream waits for the calc stream (ref process_group_nccl.cc:658-667)
     cudaStream_t cs = c->stream;
-    if (r->nvl != nullptr && nvl_next_slot(r->nvl) == 1) cs = c->stream2;  // alternate: barriers hide under transfers
+    // our own kernels alternate between two comm streams: one bucket's barriers hide under the next one's transfers
+    if (r->nvls != nullptr ? nvls_next_slot(r->nvls) == 1 : (r->nvl != nullptr && nvl_next_slot(r->nvl) == 1)) cs = c->stream2;
     PRB_CUDA(cudaEventRecord(g.ready, calc));
     PRB_CUDA(cudaStreamWaitEvent(cs, g.ready, 0));
-    if (r->nvl != nullptr) {
+    if (r->nvls != nullptr) {
+      PRB_TRY(nvls_allreduce(r->nvls, g.arena_off, g.length, g.dtype, cs));
+    } else if (r->nvl != nullptr) {
       PRB_TRY(nvl_allreduce(r->nvl, g.arena_off, g.length, g.dtype, cs));
     } else {
       ncclDataType_t nt;
@@ -551,8 +556,29 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
     *out = r;
     return PRB_SUCCESS;
   }
-  cudaError_t e = cudaMalloc((void**)&r->arena, arena);
-  if (e == cudaSuccess) e = cudaMemset(r->arena, 0, arena);  // padding gaps stay zero forever
+  // Which allreduce runs the buckets of a multi-rank job (PRB_ALLREDUCE = nvls | nvlink | nccl):
+  //   nvls              NVLink multicast: the arena is multicast-bound memory and the NVSwitch does the adds
+  //                     (wins for buckets >= ~100 MiB at 8 ranks, loses below 8 ranks: profiles/r1_multi_gpu.md);
+  //   nvlink (default)  two-shot kernel over CUDA-IPC peer mappings of a cudaMalloc'ed arena;
+  //   nccl              ncclAllReduce.
+  // Each level falls back to the next when the ranks agree (collectively) that it cannot be set up.
+  const char* ar = getenv("PRB_ALLREDUCE");
+  const int mode = ar == nullptr ? 1 : (strcmp(ar, "nvls") == 0 ? 2 : (strcmp(ar, "nvlink") == 0 ? 1 : 0));
+  NvlCollectives nc{comm->nranks > 1 ? (void*)comm->comm : nullptr, nvl_all_gather_bytes, nvl_all_min_int};
+  if (comm->nranks > 1 && mode >= 2) {
+    void* a = nullptr;
+    int32_t st = nvls_setup(nc, comm->nranks, comm->rank, comm->device, arena, comm->stream, &r->nvls, &a);
+    if (st != PRB_SUCCESS) {
+      prb_reducer_destroy(r);
+      return st;
+    }
+    if (r->nvls != nullptr) r->arena = reinterpret_cast<char*>(a);  // zero-filled by nvls_setup
+  }
+  cudaError_t e = cudaSuccess;
+  if (r->arena == nullptr) {
+    e = cudaMalloc((void**)&r->arena, arena);
+    if (e == cudaSuccess) e = cudaMemset(r->arena, 0, arena);  // padding gaps stay zero forever
+  }
   for (Group& g : r->groups) {
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.ready, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.done, cudaEventDisableTiming);
@@ -567,12 +593,7 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
   if (comm->nranks > 1 && g_nccl.CommRegister != nullptr && getenv("PRB_NCCL_REGISTER") != nullptr) {
     if (g_nccl.CommRegister(comm->comm, r->arena, arena, &r->arena_reg) != ncclSuccess) r->arena_reg = nullptr;
   }
-  // Optional: allreduce written as our own kernel over NVLink peer memory instead of NCCL.
-  // Default on a single NVSwitch node; PRB_ALLREDUCE=nccl forces NCCL.  nvl_setup decides collectively and leaves
-  // r->nvl NULL (NCCL) when CUDA IPC between the ranks is not available.
-  const char* ar = getenv("PRB_ALLREDUCE");
-  if (comm->nranks > 1 && (ar == nullptr || strcmp(ar, "nvlink") == 0)) {
-    NvlCollectives nc{(void*)comm->comm, nvl_all_gather_bytes, nvl_all_min_int};
+  if (comm->nranks > 1 && r->nvls == nullptr && mode >= 1) {
     int32_t st = nvl_setup(nc, comm->nranks, comm->rank, r->arena, arena, comm->stream, &r->nvl);
     if (st != PRB_SUCCESS) {
       prb_reducer_destroy(r);
@@ -592,6 +613,10 @@ int32_t prb_reducer_destroy(PRB_Reducer* r) {
   for (Group& g : r->groups) {
     if (g.ready) cudaEventDestroy(g.ready);
     if (g.done) cudaEventDestroy(g.done);
+  }
+  if (r->nvls) {
+    nvls_destroy(r->nvls);  // unmaps and releases the arena it allocated
+    r->arena = nullptr;
   }
   if (r->arena) cudaFree(r->arena);
   delete r;
@@ -669,7 +694,7 @@ int32_t prb_reducer_is_finalized(const PRB_Reducer* r) { return r && r->finalize
 
 int32_t prb_reducer_allreduce_backend(const PRB_Reducer* r) {
   if (r == nullptr || r->dry || r->comm->nranks == 1) return 0;
-  return r->nvl != nullptr ? 2 : 1;
+  return r->nvls != nullptr ? 3 : (r->nvl != nullptr ? 2 : 1);
 }
 
 int32_t prb_reducer_allreduce_group(PRB_Reducer* r, int64_t gi, void* stream) {
@@ -678,6 +703,7 @@ int32_t prb_reducer_allreduce_group(PRB_Reducer* r, int64_t gi, void* stream) {
   Group& g = r->groups[(size_t)gi];
   PRB_Comm* c = r->comm;
   if (c->nranks == 1) return PRB_SUCCESS;
+  if (r->nvls != nullptr) return nvls_allreduce(r->nvls, g.arena_off, g.length, g.dtype, (cudaStream_t)stream);
   if (r->nvl != nullptr) {
     // stand-alone calls all go to the caller's one stream, which orders them whatever slot they use
     return nvl_allreduce(r->nvl, g.arena_off, g.length, g.dtype, (cudaStream_t)stream);
@@ -692,7 +718,11 @@ int32_t prb_reducer_allreduce_group(PRB_Reducer* r, int64_t gi, void* stream) {
 int32_t prb_reducer_comm_error(PRB_Reducer* r, int32_t* out) {
   PRB_ENFORCE(r && out, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
   *out = 0;
-  if (r->nvl != nullptr) {
+  if (r->nvls != nullptr) {
+    int e = 0;
+    PRB_TRY(nvls_error_flag(r->nvls, &e));
+    *out = e;
+  } else if (r->nvl != nullptr) {
     int e = 0;
     PRB_TRY(nvl_error_flag(r->nvl, &e));
     *out = e;

@@ -211,7 +211,7 @@ class EagerReducer:
 
     @property
     def allreduce_backend(self) -> str:
-        return {0: "none", 1: "nccl", 2: "nvlink"}[lib.prb_reducer_allreduce_backend(self.handle)]
+        return {0: "none", 1: "nccl", 2: "nvlink", 3: "nvls"}[lib.prb_reducer_allreduce_backend(self.handle)]
 
     def allreduce_group(self, group_index: int, stream=None):
         call("prb_reducer_allreduce_group", self.handle, int(group_index), core._stream_handle(stream))

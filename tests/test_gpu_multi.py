@@ -17,7 +17,7 @@ def _ngpus():
     return prb.device_count()
 
 
-@pytest.mark.parametrize("backend", ["nccl", "nvlink"])
+@pytest.mark.parametrize("backend", ["nccl", "nvlink", "nvls"])
 @pytest.mark.parametrize("nranks", [2, 4, 8])
 def test_dataparallel_grads_equal_across_ranks(tmp_path, nranks, backend):
     if _ngpus() < nranks:
