@@ -46,6 +46,33 @@ __device__ __forceinline__ bool wait_at_least(const unsigned long long* p, unsig
   return true;
 }
 
+// Done barrier of an allreduce kernel (Args has sig[], nranks, rank, seq, parallel_release).  Every thread fences
+// its own peer stores, the rank's last CTA publishes "all my stores are out" to every peer, and a rank's kernel
+// ends only when every peer has published.  parallel_release: one publishing thread per peer, so the release
+// fences run side by side instead of one after the other (PRB_NVL_PARALLEL_RELEASE=0 restores the loop).
+template <typename Args>
+__device__ __forceinline__ void done_barrier(const Args& a, Signals* mine, int slot) {
+  __threadfence_system();
+  __syncthreads();
+  if (a.parallel_release) {
+    __shared__ unsigned int s_last;
+    if (threadIdx.x == 0) {
+      const unsigned int t = atomicAdd(&mine->cta_counter[slot], 1u);
+      s_last = (t == gridDim.x - 1) ? 1u : 0u;
+      if (s_last) mine->cta_counter[slot] = 0u;
+    }
+    __syncthreads();
+    if (threadIdx.x < a.nranks && s_last) st_release_sys(&a.sig[threadIdx.x]->done[slot][a.rank], a.seq);
+  } else if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(&mine->cta_counter[slot], 1u);
+    if (t == gridDim.x - 1) {
+      mine->cta_counter[slot] = 0u;
+      __threadfence_system();
+      for (int q = 0; q < a.nranks; ++q) st_release_sys(&a.sig[q]->done[slot][a.rank], a.seq);
+    }
+  }
+  if (threadIdx.x < a.nranks && !wait_at_least(&mine->done[slot][threadIdx.x], a.seq)) mine->error = 1;
+}
 
 // Host side: allocate this rank's signal block, exchange IPC handles through the communicator and map the peers'.
 // Collective.  *ok is the rank-local result; the caller agrees on it across ranks.

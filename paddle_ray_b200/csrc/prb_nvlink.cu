@@ -33,6 +33,7 @@ struct NvlArgs {
   char* arena[kMaxRanks];              // every rank's bucket arena as mapped into this process
   Signals* sig[kMaxRanks];             // every rank's signal block
   int nranks, rank;
+  int parallel_release;        // see done_barrier
   size_t region_off;                   // byte offset of the bucket inside the arena
   long long nvec;                      // 8-element vectors in the bucket
   unsigned long long seq;
@@ -95,17 +96,7 @@ __global__ void __launch_bounds__(kNvlThreads, kNvlMinCtasPerSm) nvl_allreduce_k
   }
 
   // ---- done barrier: my stores are out (last CTA publishes), then wait for every peer's
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned int t = atomicAdd(&mine->cta_counter[slot], 1u);
-    if (t == gridDim.x - 1) {
-      mine->cta_counter[slot] = 0u;
-      __threadfence_system();
-      for (int q = 0; q < a.nranks; ++q) st_release_sys(&a.sig[q]->done[slot][a.rank], a.seq);
-    }
-  }
-  if (threadIdx.x < a.nranks && !wait_at_least(&mine->done[slot][threadIdx.x], a.seq)) mine->error = 1;
+  done_barrier(a, mine, slot);
 }
 
 }  // namespace
@@ -180,6 +171,8 @@ int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, s
   }
   c->args.nranks = nranks;
   c->args.rank = rank;
+  c->args.parallel_release = 1;
+  if (const char* e = getenv("PRB_NVL_PARALLEL_RELEASE")) c->args.parallel_release = atoi(e) != 0;
   int per_sm = kNvlCtasPerSm;
   if (const char* e = getenv("PRB_NVL_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
   c->ctas = sm_count() * per_sm;

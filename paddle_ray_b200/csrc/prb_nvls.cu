@@ -165,6 +165,7 @@ struct NvlsArgs {
   char* mc;                  // multicast address of the arena
   Signals* sig[kMaxRanks];
   int nranks, rank;
+  int parallel_release;        // see done_barrier
   size_t region_off;
   long long nvec;            // 16-byte vectors in the bucket
   unsigned long long seq;
@@ -217,17 +218,7 @@ __global__ void __launch_bounds__(kNvlThreads, 2) nvls_allreduce_kernel(const Nv
       if (v + u * stride < v1) mc_store(base + (size_t)(v + u * stride) * 16, r[u]);
   }
   // ---- done barrier
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned int t = atomicAdd(&mine->cta_counter[slot], 1u);
-    if (t == gridDim.x - 1) {
-      mine->cta_counter[slot] = 0u;
-      __threadfence_system();
-      for (int q = 0; q < a.nranks; ++q) st_release_sys(&a.sig[q]->done[slot][a.rank], a.seq);
-    }
-  }
-  if (threadIdx.x < a.nranks && !wait_at_least(&mine->done[slot][threadIdx.x], a.seq)) mine->error = 1;
+  done_barrier(a, mine, slot);
 }
 
 }  // namespace
@@ -389,6 +380,8 @@ int32_t nvls_setup(const NvlCollectives& nc, int nranks, int rank, int device, s
   for (int q = 0; q < nranks; ++q) c->args.sig[q] = c->sigs.sig[q];
   c->args.nranks = nranks;
   c->args.rank = rank;
+  c->args.parallel_release = 1;
+  if (const char* e = getenv("PRB_NVL_PARALLEL_RELEASE")) c->args.parallel_release = atoi(e) != 0;
   int per_sm = kNvlCtasPerSm;
   if (const char* e = getenv("PRB_NVL_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
   c->ctas = sm_count() * per_sm;
