@@ -72,8 +72,7 @@ def worker(args):
             one()
         b.record()
         b.synchronize()
-        if group.rank == 0:
-            print("rank 0 plain: %.1f us per step" % (a.elapsed_ms(b) * 1e3 / 20), flush=True)
+        print("rank %d plain: %.1f us per step" % (group.rank, a.elapsed_ms(b) * 1e3 / 20), flush=True)
     for rep in range(args.reps):
         ev = {n: prb.Event() for n in names}
         for _ in range(6):
@@ -106,7 +105,7 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=2)
     ap.add_argument("--t-bwd-us", type=float, default=460.0)
-    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--reps", type=int, default=3, help="instrumented steps to print (0 = plain timing only)")
     args = ap.parse_args()
     if "WORLD_SIZE" in os.environ:
         worker(args)
