@@ -1,8 +1,6 @@
 // Cross-GPU signalling shared by the NVLink peer-memory allreduce (prb_nvlink.cu) and the NVLS multicast
 // allreduce (prb_nvls.cu): per-rank signal blocks exported through CUDA IPC, sequence-number barriers.
 #pragma once
-#include <cstring>
-
 #include "prb_nvlink.h"
 
 namespace prb {
@@ -40,56 +38,12 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-// poll_mode 0 (default, the validated path): ld.acquire.sys in the loop.  1: relaxed loads in the loop and ONE
-// acquire fence after the value has arrived (no L1 invalidation per iteration); 2: as 1 with a __nanosleep
-// back-off.  1 and 2 are next round's experiments for the calc-stream stall seen at 8 ranks
-// (profiles/r1_multi_gpu.md); PRB_NVL_POLL selects.
-__device__ __forceinline__ bool wait_at_least(const unsigned long long* p, unsigned long long v, int poll_mode = 0) {
+__device__ __forceinline__ bool wait_at_least(const unsigned long long* p, unsigned long long v) {
   const unsigned long long t0 = now_ns();
-  if (poll_mode == 0) {
-    while (ld_acquire_sys(p) < v) {
-      if (now_ns() - t0 > kWaitLimitNs) return false;
-    }
-    return true;
-  }
-  while (ld_relaxed_sys(p) < v) {
-    if (poll_mode == 2) __nanosleep(100);
+  while (ld_acquire_sys(p) < v) {
     if (now_ns() - t0 > kWaitLimitNs) return false;
   }
-  asm volatile("fence.acq_rel.sys;" ::: "memory");
   return true;
-}
-
-// Launch-time experiment switches shared by both kernels (read once per process).
-struct NvlTuning {
-  int poll_mode = 0;       // PRB_NVL_POLL = acquire | relaxed | sleep
-  bool remote_domain = false;  // PRB_NVL_DOMAIN = remote: launch into the remote memory-synchronisation domain (as NCCL does)
-  int cta_cap = 0;         // PRB_NVL_CTAS = absolute cap on the grid (0 = sm_count * CTAs per SM)
-};
-const NvlTuning& nvl_tuning();
-
-template <typename Kernel, typename Args>
-inline cudaError_t nvl_launch(Kernel kernel, int ctas, int threads, cudaStream_t stream, const Args& a) {
-  if (!nvl_tuning().remote_domain) {
-    kernel<<<ctas, threads, 0, stream>>>(a);
-    return cudaGetLastError();
-  }
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeMemSyncDomain;
-  attr[0].val.memSyncDomain = cudaLaunchMemSyncDomainRemote;
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3((unsigned)ctas);
-  cfg.blockDim = dim3((unsigned)threads);
-  cfg.stream = stream;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, kernel, a);
 }
 
 // Done barrier of an allreduce kernel (Args has sig[], nranks, rank, seq, parallel_release).  Every thread fences
@@ -117,7 +71,7 @@ __device__ __forceinline__ void done_barrier(const Args& a, Signals* mine, int s
       for (int q = 0; q < a.nranks; ++q) st_release_sys(&a.sig[q]->done[slot][a.rank], a.seq);
     }
   }
-  if (threadIdx.x < a.nranks && !wait_at_least(&mine->done[slot][threadIdx.x], a.seq, a.poll_mode)) mine->error = 1;
+  if (threadIdx.x < a.nranks && !wait_at_least(&mine->done[slot][threadIdx.x], a.seq)) mine->error = 1;
 }
 
 // Host side: allocate this rank's signal block, exchange IPC handles through the communicator and map the peers'.

@@ -34,7 +34,6 @@ struct NvlArgs {
   Signals* sig[kMaxRanks];             // every rank's signal block
   int nranks, rank;
   int parallel_release;        // see done_barrier
-  int poll_mode;               // see wait_at_least
   size_t region_off;                   // byte offset of the bucket inside the arena
   long long nvec;                      // 8-element vectors in the bucket
   unsigned long long seq;
@@ -59,7 +58,7 @@ __global__ void __launch_bounds__(kNvlThreads, kNvlMinCtasPerSm) nvl_allreduce_k
   const int slot = (int)(a.seq & (kSlots - 1));
   // ---- ready barrier
   if (blockIdx.x == 0 && threadIdx.x < a.nranks) st_release_sys(&a.sig[threadIdx.x]->ready[slot][a.rank], a.seq);
-  if (threadIdx.x < a.nranks && !wait_at_least(&mine->ready[slot][threadIdx.x], a.seq, a.poll_mode)) mine->error = 1;
+  if (threadIdx.x < a.nranks && !wait_at_least(&mine->ready[slot][threadIdx.x], a.seq)) mine->error = 1;
   __syncthreads();
 
   // ---- reduce-scatter + all-gather of my slice
@@ -177,8 +176,6 @@ int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, s
   int per_sm = kNvlCtasPerSm;
   if (const char* e = getenv("PRB_NVL_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
   c->ctas = sm_count() * per_sm;
-  if (nvl_tuning().cta_cap > 0) c->ctas = nvl_tuning().cta_cap;
-  c->args.poll_mode = nvl_tuning().poll_mode;
   *out = c;
   return PRB_SUCCESS;
 }
@@ -230,17 +227,6 @@ void signals_destroy(SignalSet* s) {
   s->mine = nullptr;
 }
 
-const NvlTuning& nvl_tuning() {
-  static const NvlTuning t = [] {
-    NvlTuning v;
-    if (const char* e = getenv("PRB_NVL_POLL")) v.poll_mode = strcmp(e, "relaxed") == 0 ? 1 : (strcmp(e, "sleep") == 0 ? 2 : 0);
-    if (const char* e = getenv("PRB_NVL_DOMAIN")) v.remote_domain = strcmp(e, "remote") == 0;
-    if (const char* e = getenv("PRB_NVL_CTAS")) v.cta_cap = atoi(e) > 0 ? atoi(e) : 0;
-    return v;
-  }();
-  return t;
-}
-
 int nvl_next_slot(const NvlContext* c) { return c ? (int)((c->seq + 1) & (kSlots - 1)) : 0; }
 
 int32_t nvl_allreduce(NvlContext* c, size_t region_off_bytes, int64_t numel, int32_t dtype, cudaStream_t stream) {
@@ -255,11 +241,11 @@ int32_t nvl_allreduce(NvlContext* c, size_t region_off_bytes, int64_t numel, int
   int ctas = (int)((per_rank + kNvlThreads - 1) / kNvlThreads);
   if (ctas > c->ctas) ctas = c->ctas;  // a few CTAs per SM, each looping over its share of the slice
   if (ctas < 1) ctas = 1;
-#define PRB_NVL(T_)                                                                                        \
-  do {                                                                                                     \
-    if (a.nranks <= 2) PRB_CUDA(nvl_launch(nvl_allreduce_kernel<T_, 2>, ctas, kNvlThreads, stream, a));      \
-    else if (a.nranks <= 4) PRB_CUDA(nvl_launch(nvl_allreduce_kernel<T_, 4>, ctas, kNvlThreads, stream, a)); \
-    else PRB_CUDA(nvl_launch(nvl_allreduce_kernel<T_, 8>, ctas, kNvlThreads, stream, a));                    \
+#define PRB_NVL(T_)                                                                              \
+  do {                                                                                           \
+    if (a.nranks <= 2) nvl_allreduce_kernel<T_, 2><<<ctas, kNvlThreads, 0, stream>>>(a);         \
+    else if (a.nranks <= 4) nvl_allreduce_kernel<T_, 4><<<ctas, kNvlThreads, 0, stream>>>(a);    \
+    else nvl_allreduce_kernel<T_, 8><<<ctas, kNvlThreads, 0, stream>>>(a);                       \
   } while (0)
   switch (dtype) {
     case PRB_FLOAT32: PRB_NVL(float); break;

@@ -166,7 +166,6 @@ struct NvlsArgs {
   Signals* sig[kMaxRanks];
   int nranks, rank;
   int parallel_release;        // see done_barrier
-  int poll_mode;               // see wait_at_least
   size_t region_off;
   long long nvec;            // 16-byte vectors in the bucket
   unsigned long long seq;
@@ -203,7 +202,7 @@ __global__ void __launch_bounds__(kNvlThreads, 2) nvls_allreduce_kernel(const Nv
   const int slot = (int)(a.seq & (kSlots - 1));
   // ---- ready barrier: every rank's packed bucket is complete
   if (blockIdx.x == 0 && threadIdx.x < a.nranks) st_release_sys(&a.sig[threadIdx.x]->ready[slot][a.rank], a.seq);
-  if (threadIdx.x < a.nranks && !wait_at_least(&mine->ready[slot][threadIdx.x], a.seq, a.poll_mode)) mine->error = 1;
+  if (threadIdx.x < a.nranks && !wait_at_least(&mine->ready[slot][threadIdx.x], a.seq)) mine->error = 1;
   __syncthreads();
   // ---- my slice: the switch reduces on the way in and replicates on the way out
   const long long v0 = a.nvec * a.rank / a.nranks, v1 = a.nvec * (a.rank + 1) / a.nranks;
@@ -386,8 +385,6 @@ int32_t nvls_setup(const NvlCollectives& nc, int nranks, int rank, int device, s
   int per_sm = kNvlCtasPerSm;
   if (const char* e = getenv("PRB_NVL_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
   c->ctas = sm_count() * per_sm;
-  if (nvl_tuning().cta_cap > 0) c->ctas = nvl_tuning().cta_cap;
-  c->args.poll_mode = nvl_tuning().poll_mode;
   *out = c;
   *arena_out = reinterpret_cast<void*>(c->uc);
   return PRB_SUCCESS;
@@ -409,9 +406,9 @@ int32_t nvls_allreduce(NvlsContext* c, size_t region_off_bytes, int64_t numel, i
   if (ctas > c->ctas) ctas = c->ctas;
   if (ctas < 1) ctas = 1;
   switch (dtype) {
-    case PRB_FLOAT32: PRB_CUDA(nvl_launch(nvls_allreduce_kernel<float>, ctas, kNvlThreads, stream, a)); break;
-    case PRB_BFLOAT16: PRB_CUDA(nvl_launch(nvls_allreduce_kernel<__nv_bfloat16>, ctas, kNvlThreads, stream, a)); break;
-    case PRB_FLOAT16: PRB_CUDA(nvl_launch(nvls_allreduce_kernel<__half>, ctas, kNvlThreads, stream, a)); break;
+    case PRB_FLOAT32: nvls_allreduce_kernel<float><<<ctas, kNvlThreads, 0, stream>>>(a); break;
+    case PRB_BFLOAT16: nvls_allreduce_kernel<__nv_bfloat16><<<ctas, kNvlThreads, 0, stream>>>(a); break;
+    case PRB_FLOAT16: nvls_allreduce_kernel<__half><<<ctas, kNvlThreads, 0, stream>>>(a); break;
     default: PRB_FAIL(PRB_UNIMPLEMENTED, "nvls allreduce: dtype %s is not built", dtype_name(dtype));
   }
   PRB_LAUNCH_CHECK();
