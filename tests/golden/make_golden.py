@@ -204,6 +204,134 @@ def gen_bucket_cases():
         json.dump(cases, f, indent=1)
 
 
+def gen_fused_adam():
+    """TestFusedAdamOp (test_fused_adam_op.py:88-175) with its numpy oracle fused_adam_step (:23-85).
+
+    The reference builds its six input lists as ``[[0] * num] * 6`` -- six references to ONE list -- so every
+    assignment in its setUp loop lands in the same slot and all six "lists" end up holding the last value written,
+    ``np.array([beta2_pow])``.  The draws still consume the generator.  Reproduced here statement for statement, so
+    the fixture holds exactly the tensors that test feeds the operator.
+
+    That accident is also why the reference's test passes: fused_adam_step adds ``epsilon`` to ``sqrt(m2)`` unscaled,
+    while the kernel (fused_adam_kernel.cu:213-227, like adam_step in test_adam_op.py) uses
+    ``epsilon * sqrt(1 - beta2_pow)``; on (102, 105) uniform data the two differ by up to 2e-4 where m2 is tiny,
+    far outside the OpTest tolerance, on the one-element tensors the test really feeds they agree.  The oracle
+    follows the kernel, so only the inputs the reference really tests are pinned here.
+    """
+    fused_adam_step = extract_function(f"{REF}/test_fused_adam_op.py", "fused_adam_step")
+    np.random.seed(123)
+    num = 10
+    inputs_list = [[0] * num] * 6
+    learning_rate, beta1, beta2, epsilon = 0.004, 0.78, 0.836, 1e-4
+    beta1_pow, beta2_pow = beta1**10, beta2**10
+    attrs = {"epsilon": epsilon, "beta1": beta1, "beta2": beta2, "chunk_size": 32 * 2048}
+    for i in range(num):
+        inputs_list[0][i] = np.random.uniform(-1, 1, (102, 105)).astype("float32")
+        inputs_list[1][i] = np.random.uniform(-1, 1, (102, 105)).astype("float32")
+        inputs_list[2][i] = np.random.uniform(-1, 1, (102, 105)).astype("float32")
+        inputs_list[3][i] = np.random.random((102, 105)).astype("float32")
+        inputs_list[4][i] = np.array([beta1_pow]).astype("float32")
+        inputs_list[5][i] = np.array([beta2_pow]).astype("float32")
+    names = ("Params", "Grads", "Moments1", "Moments2", "Beta1Pows", "Beta2Pows")
+    inputs = {n: [(n.lower() + str(i), inputs_list[k][i]) for i in range(num)] for k, n in enumerate(names)}
+    inputs["LearningRate"] = np.array([learning_rate]).astype("float32")
+    outs = fused_adam_step(inputs, attrs, num)
+    store = {"num": np.array([num]), "LearningRate": inputs["LearningRate"]}
+    for k, v in attrs.items():
+        store[f"attr/{k}"] = np.asarray(v)
+    for n in names:
+        for i in range(num):
+            store[f"in/{n}/{i}"] = np.asarray(inputs[n][i][1])
+    for n, arrs in zip(("ParamsOut", "Moments1Out", "Moments2Out", "Beta1PowsOut", "Beta2PowsOut"), outs):
+        for i in range(num):
+            store[f"out/{n}/{i}"] = np.asarray(arrs[i])
+    np.savez_compressed(f"{OUT}/fused_adam_optest.npz", **store)
+
+
+def gen_adamw_layerwise():
+    """TestAdamWOpLayerwiseLR.test_adamw_op_dygraph (test_adamw_op.py:628-755): five AdamW steps over two Linear
+    layers with lr_ratio = simple_lr_setting (:614-622), checked there with rtol 1e-6 against adamw_step.  The
+    reference's gradients come from its autograd; here they are drawn (seed 2022 as in its setUp), everything
+    else -- parameter names, shapes, hyper-parameters, the per-step beta powers, the two reference functions --
+    is the reference's."""
+    from functools import partial
+    from types import SimpleNamespace
+
+    adamw_step = extract_function(f"{REF}/test_adamw_op.py", "adamw_step")
+    simple_lr_setting = extract_function(f"{REF}/test_adamw_op.py", "simple_lr_setting")
+    simple_lr_fun = partial(simple_lr_setting, decay_rate=0.8, n_layers=2)
+    np.random.seed(2022)
+    learning_rate, weight_decay, beta1, beta2 = 0.001, 0.01, 0.9, 0.999
+    shapes = {"linear_1.w_0": (13, 8), "linear_1.b_0": (8,), "linear_2.w_0": (8, 5), "linear_2.b_0": (5,)}
+    store = {"steps": np.array([5])}
+    state = {}
+    for name, shape in shapes.items():
+        w = np.random.uniform(-0.5, 0.5, shape).astype("float32") if name.endswith("w_0") else np.ones(shape, "float32")
+        state[name] = [w, np.zeros_like(w), np.zeros_like(w)]
+        store[f"{name}/lr_ratio"] = np.array([simple_lr_fun(SimpleNamespace(name=name))])
+        store[f"{name}/param0"] = w.copy()
+    for t in range(1, 6):
+        for name, shape in shapes.items():
+            grad = np.random.uniform(-1, 1, shape).astype("float32")
+            param, m1, m2 = state[name]
+            np_inputs = {"Param": param, "Grad": grad, "Moment1": m1, "Moment2": m2,
+                         "LearningRate": np.array([learning_rate]).astype("float32"),
+                         "Beta1Pow": np.array([beta1**t]).astype("float32"),
+                         "Beta2Pow": np.array([beta2**t]).astype("float32")}
+            np_attrs = {"epsilon": 1e-8, "beta1": beta1, "beta2": beta2,
+                        "lr_ratio": float(store[f"{name}/lr_ratio"][0]), "coeff": weight_decay, "with_decay": True}
+            state[name] = list(adamw_step(np_inputs, np_attrs))
+            store[f"{name}/step{t}/Grad"] = grad
+            store[f"{name}/step{t}/ParamOut"] = np.asarray(state[name][0])
+    store["hyper"] = np.array([learning_rate, weight_decay, beta1, beta2, 1e-8])
+    np.savez_compressed(f"{OUT}/adamw_layerwise.npz", **store)
+
+
+def _class_literals(path, cls_name, fn_name):
+    """{attribute: literal} for the ``self.x = <literal or np.array([literal])...>`` lines of cls.fn."""
+    tree = ast.parse(open(path).read())
+    out = {}
+    for cls in tree.body:
+        if isinstance(cls, ast.ClassDef) and cls.name == cls_name:
+            for fn in cls.body:
+                if isinstance(fn, ast.FunctionDef) and fn.name == fn_name:
+                    for node in ast.walk(fn):
+                        if isinstance(node, ast.Assign) and isinstance(node.targets[0], ast.Attribute):
+                            for sub in ast.walk(node.value):
+                                if isinstance(sub, ast.Constant) and isinstance(sub.value, (int, float, bool)):
+                                    out[node.targets[0].attr] = sub.value
+                                    break
+                        if isinstance(node, ast.Dict):
+                            for k, v in zip(node.keys, node.values):
+                                if isinstance(k, ast.Constant) and isinstance(v, ast.Constant):
+                                    out[k.value] = v.value
+    return out
+
+
+def gen_update_loss_scaling():
+    """Known answers of test_update_loss_scaling_op.py: TestUpdateLossScalingOp (:52-104, found_inf False at
+    good = 999 of 1000 -> scale * incr_ratio, counters 0) and TestUpdateLossScalingOpBad (:107-136, found_inf True
+    at bad = 1 of 2 -> scale * decr_ratio, counters 0, Out zeroed).  The literals are read from the AST of init()."""
+    lit = _class_literals(f"{REF}/test_update_loss_scaling_op.py", "TestUpdateLossScalingOp", "init")
+    need = ("incr_ratio", "decr_ratio", "prev_loss_scaling", "num_good_steps", "num_bad_steps",
+            "incr_every_n_steps", "decr_every_n_nan_or_inf")
+    assert all(k in lit for k in need), lit
+    prev = np.array([lit["prev_loss_scaling"]]).astype(np.float32)
+    cases = []
+    for name, found, ratio, zero_out in (("TestUpdateLossScalingOp", False, lit["incr_ratio"], False),
+                                         ("TestUpdateLossScalingOpBad", True, lit["decr_ratio"], True)):
+        cases.append({
+            "name": name, "found_inf": found, "prev_loss_scaling": float(prev[0]),
+            "in_good_steps": lit["num_good_steps"], "in_bad_steps": lit["num_bad_steps"],
+            "incr_every_n_steps": lit["incr_every_n_steps"], "decr_every_n_nan_or_inf": lit["decr_every_n_nan_or_inf"],
+            "incr_ratio": lit["incr_ratio"], "decr_ratio": lit["decr_ratio"],
+            "expected_loss_scaling": float((prev * ratio)[0]), "expected_good_steps": 0, "expected_bad_steps": 0,
+            "expected_out_zeroed": zero_out,
+        })
+    with open(f"{OUT}/update_loss_scaling_cases.json", "w") as f:
+        json.dump(cases, f, indent=1)
+
+
 if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("reference tree not present; fixtures can only be regenerated in the build container")
@@ -212,4 +340,7 @@ if __name__ == "__main__":
     gen_check_finite()
     gen_squared_l2_norm()
     gen_bucket_cases()
+    gen_fused_adam()
+    gen_adamw_layerwise()
+    gen_update_loss_scaling()
     print("fixtures written to", OUT)

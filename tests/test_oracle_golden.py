@@ -246,3 +246,73 @@ def test_update_loss_scaling_state_machine():
     assert (ls, good, bad) == (32768.0, 0, 0)
     ls, good, bad = orc.update_loss_scaling(True, 1.5, 0, 1, 1000, 2, 2.0, 0.5)
     assert ls == 1.0
+
+
+# ------------------------------------------------------------------ further fixtures from the reference's tests
+def test_fused_adam_matches_reference_numpy_oracle(golden_dir):
+    """test_fused_adam_op.py: the operator's OpTest inputs (as that test really builds them, aliasing included)
+    and its numpy oracle; OpTest tolerance."""
+    npz = np.load(os.path.join(golden_dir, "fused_adam_optest.npz"))
+    num = int(npz["num"][0])
+    attrs = {k: float(npz["attr/" + k]) for k in ("epsilon", "beta1", "beta2")}
+    lr = float(npz["LearningRate"][0])
+    for i in range(num):
+        ins = {"Param": npz[f"in/Params/{i}"], "Grad": npz[f"in/Grads/{i}"], "Moment1": npz[f"in/Moments1/{i}"],
+               "Moment2": npz[f"in/Moments2/{i}"], "LearningRate": np.array([lr], np.float32),
+               "Beta1Pow": npz[f"in/Beta1Pows/{i}"], "Beta2Pow": npz[f"in/Beta2Pows/{i}"]}
+        p, m1, m2 = _run_oracle_adam(ins, attrs, adamw=False)
+        np.testing.assert_allclose(p, npz[f"out/ParamsOut/{i}"].ravel(), atol=1e-5, rtol=0)
+        np.testing.assert_allclose(m1, npz[f"out/Moments1Out/{i}"].ravel(), atol=1e-5, rtol=0)
+        np.testing.assert_allclose(m2, npz[f"out/Moments2Out/{i}"].ravel(), atol=1e-5, rtol=0)
+        # beta-pow outputs: in * beta, rounded to fp32 (ref fused_adam_kernel.cu:230-238)
+        b1 = np.float32(ins["Beta1Pow"][0]) * np.float32(attrs["beta1"])
+        np.testing.assert_allclose(b1, npz[f"out/Beta1PowsOut/{i}"][0], rtol=1e-6)
+
+
+def test_adamw_layerwise_lr_ratio_five_steps(golden_dir):
+    """test_adamw_op.py:628-755: lr_ratio per layer, five steps, the reference's own tolerance (rtol 1e-6)."""
+    npz = np.load(os.path.join(golden_dir, "adamw_layerwise.npz"))
+    lr, wd, beta1, beta2, eps = (float(v) for v in npz["hyper"])
+    for name in ("linear_1.w_0", "linear_1.b_0", "linear_2.w_0", "linear_2.b_0"):
+        ratio = float(npz[f"{name}/lr_ratio"][0])
+        p = npz[f"{name}/param0"].astype(np.float32).ravel().copy()
+        m1 = np.zeros_like(p)
+        m2 = np.zeros_like(p)
+        for t in range(1, int(npz["steps"][0]) + 1):
+            g = npz[f"{name}/step{t}/Grad"].astype(np.float32).ravel().copy()
+            orc.adam(p, g, m1, m2, None, dtype_param=orc.F32, dtype_grad=orc.F32, lr=float(np.float32(lr)),
+                     lr_ratio=ratio, beta1=beta1, beta2=beta2, epsilon=eps, coeff=wd, use_decay=True,
+                     beta1_pow=float(np.float32(beta1 ** t)), beta2_pow=float(np.float32(beta2 ** t)))
+            # rtol is the reference's.  atol: adamw_step multiplies by float32(1 - beta2) = 0.001, the kernel (and
+            # the oracle) by 1.0f - float32(beta2) = 0.00100004673 (adamw_kernel.cu:65-66); that moves every update
+            # by ~2e-5 of its size (5e-4 here), which only shows on the few weights that happen to be ~1e-4 small
+            np.testing.assert_allclose(p, npz[f"{name}/step{t}/ParamOut"].ravel(), rtol=1e-6, atol=5e-8)
+    # the depth rule itself (test_adamw_op.py:614-622): decay_rate ** (n_layers + 2 - depth)
+    assert float(npz["linear_1.w_0/lr_ratio"][0]) == pytest.approx(0.8 ** 3)
+    assert float(npz["linear_2.b_0/lr_ratio"][0]) == pytest.approx(0.8 ** 2)
+
+
+def test_update_loss_scaling_known_answers(golden_dir):
+    """test_update_loss_scaling_op.py:52-136: the two OpTest cases, literal expectations."""
+    import json
+    with open(os.path.join(golden_dir, "update_loss_scaling_cases.json")) as f:
+        cases = json.load(f)
+    assert [c["name"] for c in cases] == ["TestUpdateLossScalingOp", "TestUpdateLossScalingOpBad"]
+    for c in cases:
+        ls, good, bad = orc.update_loss_scaling(c["found_inf"], c["prev_loss_scaling"], c["in_good_steps"],
+                                                c["in_bad_steps"], c["incr_every_n_steps"],
+                                                c["decr_every_n_nan_or_inf"], c["incr_ratio"], c["decr_ratio"])
+        assert ls == pytest.approx(c["expected_loss_scaling"], rel=1e-6), c["name"]
+        assert (good, bad) == (c["expected_good_steps"], c["expected_bad_steps"]), c["name"]
+
+
+def test_global_norm_clip_property_of_the_reference_test():
+    """test_gradient_clip.py:442-482: ||clip(g)|| == min(||g||, clip_norm) (rtol 1e-6, atol 1e-8) on a Linear(5, 5)."""
+    rng = np.random.default_rng(7)
+    for scale in (10.0, 0.01):  # one case that clips, one that does not
+        grads = [(rng.normal(0, scale, 25)).astype(np.float32), (rng.normal(0, scale, 5)).astype(np.float32)]
+        before = np.sqrt(sum(np.sum(np.power(g.astype(np.float64), 2)) for g in grads))
+        out = [g.copy() for g in grads]
+        orc.global_norm_clip(out, [orc.F32, orc.F32], 0.8)  # in place
+        after = np.sqrt(sum(np.sum(np.power(np.asarray(g, np.float64), 2)) for g in out))
+        assert np.isclose(min(before, 0.8), after, rtol=1e-6, atol=1e-8), (before, after)
