@@ -316,3 +316,64 @@ def test_global_norm_clip_property_of_the_reference_test():
         orc.global_norm_clip(out, [orc.F32, orc.F32], 0.8)  # in place
         after = np.sqrt(sum(np.sum(np.power(np.asarray(g, np.float64), 2)) for g in out))
         assert np.isclose(min(before, 0.8), after, rtol=1e-6, atol=1e-8), (before, after)
+
+
+# ------------------------------------------------------------------ the timed CPU baseline computes the right thing
+def test_cpu_baseline_port_agrees_with_the_gpu_semantics():
+    """The CPU path (cpu/adamw_kernel.cc:96-189, refer.h:539-563) factors the update differently from the GPU
+    kernel but is the same mathematics: the baseline that bench.py times must land within a few ulp
+    of the parity oracle, and must not depend on the thread count (ref jit/test.cc:690-900 holds every CPU
+    implementation to the refer one the same way)."""
+    rng = np.random.default_rng(5)
+    n = 512 * 37 + 129  # whole chunks plus a tail (cpu/adamw_kernel.cc:147-189)
+    p0 = rng.normal(0, 0.02, n).astype(np.float32)
+    g = rng.normal(0, 1e-2, n).astype(np.float32)
+    m10 = rng.normal(0, 1e-3, n).astype(np.float32)
+    m20 = rng.uniform(0, 1e-3, n).astype(np.float32)
+    kw = dict(lr=1e-3, lr_ratio=1.0, beta1=0.9, beta2=0.999, epsilon=1e-8, coeff=0.01,
+              beta1_pow=float(np.float32(0.9 ** 10)), beta2_pow=float(np.float32(0.999 ** 10)))
+    outs = []
+    for threads in (1, max(2, orc.max_threads())):
+        p, m1, m2 = p0.copy(), m10.copy(), m20.copy()
+        orc.cpu_adamw(p, g, m1, m2, nthreads=threads, **kw)
+        outs.append((p, m1, m2))
+    for a, b in zip(*outs):
+        np.testing.assert_array_equal(a, b)  # element-wise work: the thread count cannot matter
+    p, m1, m2 = p0.copy(), m10.copy(), m20.copy()
+    orc.adam(p, g.copy(), m1, m2, None, dtype_param=orc.F32, dtype_grad=orc.F32, use_decay=True, **kw)
+    np.testing.assert_allclose(outs[0][0], p, rtol=2e-6, atol=1e-9)
+    np.testing.assert_allclose(outs[0][1], m1, rtol=1e-6, atol=1e-12)
+    np.testing.assert_allclose(outs[0][2], m2, rtol=1e-6, atol=1e-12)
+    x = rng.normal(0, 1, 1000).astype(np.float32)
+    x[0] = -0.0
+    y = x.copy()
+    orc.cpu_scale_f32(y, np.float32(0.25), 2)
+    np.testing.assert_array_equal(y, np.float32(0.25) * (x + np.float32(0)))
+
+
+@pytest.mark.parametrize("dt", [orc.BF16, orc.F16])
+@pytest.mark.parametrize("main_grad", [False, True])
+def test_multi_precision_master_follows_the_fp32_run(dt, main_grad):
+    """test_adamw_op.py:323-459: with fp32 master weights the master after the step equals an fp32 AdamW on the
+    same numbers (rtol 1e-6 there; exactly here), and the 16-bit parameter is its rounding (rtol 1e-2 there)."""
+    rng = np.random.default_rng(11)
+    n = 1000
+    master0 = rng.normal(0, 1, n).astype(np.float32)
+    g32 = rng.normal(0, 1, n).astype(np.float32)
+    g16 = orc.from_f32(g32, dt)
+    g_as_f32 = g32 if main_grad else orc.to_f32(g16, dt)
+    m1 = rng.normal(0, 1, n).astype(np.float32)
+    m2 = np.abs(rng.normal(0, 1, n)).astype(np.float32)
+    kw = dict(lr=1e-8, lr_ratio=1.0, beta1=0.9, beta2=0.99, epsilon=1e-8, coeff=0.1, use_decay=True,
+              beta1_pow=float(np.float32(0.9 ** 10)), beta2_pow=float(np.float32(0.99 ** 10)))
+    ref_p, ref_m1, ref_m2 = master0.copy(), m1.copy(), m2.copy()
+    orc.adam(ref_p, g_as_f32.copy(), ref_m1, ref_m2, None, dtype_param=orc.F32, dtype_grad=orc.F32, **kw)
+    p16 = orc.from_f32(master0, dt)
+    master, a1, a2 = master0.copy(), m1.copy(), m2.copy()
+    grad = g32.copy() if main_grad else g16.copy()
+    orc.adam(p16, grad, a1, a2, master, dtype_param=dt, dtype_grad=orc.F32 if main_grad else dt, **kw)
+    np.testing.assert_array_equal(master, ref_p)
+    np.testing.assert_array_equal(a1, ref_m1)
+    np.testing.assert_array_equal(a2, ref_m2)
+    np.testing.assert_array_equal(p16, orc.from_f32(master, dt))
+    np.testing.assert_allclose(orc.to_f32(p16, dt), ref_p, rtol=1e-2)
