@@ -193,7 +193,7 @@ def make_step(w):
 # --------------------------------------------------------------------------------------------
 # CPU baseline: the reference's CPU path restated in oracle/ (kind "port"), all host threads
 # --------------------------------------------------------------------------------------------
-def cpu_reference_run(workload, nranks, budget_s, min_steps=2, max_steps=10 ** 9):
+def cpu_reference_run(workload, nranks, budget_s, min_steps=2, max_steps=10 ** 9, warmup=1):
     """concat -> scale(1/nranks) -> [allreduce: one process, nothing to exchange] -> split -> AdamW per tensor.
     ref: reducer.cc:1037-1070 on CPUPlace, cpu/adamw_kernel.cc:96-189.  fp32 only (the CPU kernel
     registers float/double only), so bf16 workloads are timed with fp32 storage of the same shapes."""
@@ -221,7 +221,8 @@ def cpu_reference_run(workload, nranks, budget_s, min_steps=2, max_steps=10 ** 9
             orc.cpu_adamw(p, g, m1, m2, lr=1e-3, lr_ratio=1.0, beta1=0.9, beta2=0.999, epsilon=1e-8, coeff=0.01,
                           beta1_pow=b1p, beta2_pow=b2p, nthreads=threads)
 
-    one_step()  # warm-up (page faults, thread pool)
+    for _ in range(max(1, warmup)):  # untimed warm-up (page faults, thread pool)
+        one_step()
     t0 = time.perf_counter()
     steps = 0
     while steps < max_steps and (steps < min_steps or time.perf_counter() - t0 < budget_s):
@@ -237,12 +238,15 @@ def run_reference_arm(args):
     if rank != 0:
         return 0  # only rank 0 runs the CPU arm
     # each "step" of this arm = one full CPU pass over the workload; bounded so the run ends within minutes
-    budget = 60.0
-    r = cpu_reference_run(args.workload, args.gpus, budget_s=budget, min_steps=1, max_steps=args.steps + args.warmup)
+    # W untimed warm-up steps, then K timed ones; the time budget only cuts K short for workloads where K full CPU
+    # passes would take more than two minutes (the line then reports the steps really timed)
+    budget = 120.0
+    r = cpu_reference_run(args.workload, args.gpus, budget_s=budget, min_steps=1, max_steps=args.steps,
+                          warmup=args.warmup)
     desc = WORKLOADS[args.workload][7] if args.workload in WORKLOADS else args.workload
     line = {
         "impl": "reference", "metric": METRIC, "value": r["gbs"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
-        "warmup": 1, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "warmup": max(1, args.warmup), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "path": "CPU: concat -> scale(1/nranks) -> split -> AdamW (oracle port of the "
                    "reference's CPU kernels; Paddle itself cannot be built here)", "allreduce": "none (one process)"},
