@@ -1,25 +1,31 @@
 #!/usr/bin/env python
 """Benchmark of the data-parallel step tail (BASELINE.json metric: AdamW+grad-sync step GB/s & ms/step).
 
-    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload resnet50]
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload bert_base] [--no-configs]
 
-One "step" = one pass of the hot path over one batch of synthetic gradients:
+One "step" = one pass of the hot path over one batch of synthetic gradients, all four north-star stages:
     prepare_for_backward -> every gradient marked ready (reverse parameter order) ->
-    per bucket: pack + 1/nranks scale -> NCCL allreduce on the comm stream (N > 1) ->
-    one fused multi-tensor AdamW launch that reads the reduced gradients straight from the bucket arena.
-Default workload = BASELINE.json configs[1]: ResNet-50 parameter shapes (161 tensors, 25,557,032 fp32
-elements), paddle.DataParallel + paddle.optimizer.AdamW, fp32, no AMP, no clip.
+    per bucket: pack + 1/nranks scale (+ AMP inf/nan check + squared-norm partials in the same kernel) ->
+    bucket allreduce on the comm stream (N > 1; there the check + partials ride in the exchange kernel) ->
+    norm finalize -> one fused multi-tensor AdamW launch that reads the reduced gradients from the bucket arena.
+Headline workload = BASELINE.json configs[2]: BERT-base parameter shapes (206 tensors, 110,106,428 elements),
+AMP bf16 with fp32 master weights, global-norm clip, paddle.DataParallel + paddle.optimizer.AdamW + GradScaler.
+The other configs (ResNet-50 fp32 = configs[1], GPT-2 medium = configs[3], the flat sweep = configs[4], and the
+"gradients produced in the arena" mode) are measured with few steps and nested under `configs` of the same line.
 
-`value` = whole-job algorithmic GB/s with inputs resident in HBM; `e2e` = the same metric through the
-public Python API with the gradients coming from pinned HOST memory every step (H2D inside the timed
-region) and a result read back (D2H).  Algorithmic bytes per element: pack r4+w4, AdamW
-r16+w12 -> 36 B/elem for fp32; bf16+master AMP+clip: pack r2+w2, norm pass r2, update r14+w14 -> 34 B/elem.
+`value` = whole-job algorithmic GB/s with inputs resident in HBM; `e2e` = the same metric through the public Python
+API with the gradients coming from pinned HOST memory every step (H2D per bucket inside the timed region) and the
+step's metric (global grad norm, found_inf, loss scale) read back.  Algorithmic bytes per element:
+update r14+w14 (bf16 + master) or r16+w12 (fp32) = 28, pack r s + w s; the check + norm ride in the pack, so a
+bf16 AMP+clip step is 32 B/elem (SURVEY 8d's floor with a separate norm read is 34), fp32 without AMP/clip 36.
 
-The oracle (oracle/) is imported only by the cpu_baseline / --impl reference legs.
+The oracle (oracle/) is imported only by the cpu_baseline / --impl reference legs and by the N>1 parity preamble
+(as the checker of a tiny step, outside every timed region).
 """
 from __future__ import annotations
 
 import argparse
+import ctypes as C
 import json
 import os
 import subprocess
@@ -38,16 +44,39 @@ METRIC = "adamw_grad_sync_step_throughput"
 UNIT = "GB/s"
 
 WORKLOADS = {
-    # name: (shape list, param dtype, grad dtype, amp, clip, multi_precision, bytes/elem, human description)
-    "resnet50": ("resnet50", "float32", "float32", False, False, False, 36,
+    # name: (shape list, param dtype, grad dtype, amp, clip, multi_precision, human description)
+    "resnet50": ("resnet50", "float32", "float32", False, False, False,
                  "ResNet-50 param shapes (161 tensors, 25,557,032 elems), DataParallel + AdamW fp32"),
-    "resnet18": ("resnet18", "float32", "float32", False, False, False, 36,
+    "resnet18": ("resnet18", "float32", "float32", False, False, False,
                  "ResNet-18 param shapes (62 tensors, 11,689,512 elems), DataParallel + AdamW fp32"),
-    "bert_base": ("bert_base", "bfloat16", "bfloat16", True, True, True, 34,
+    "bert_base": ("bert_base", "bfloat16", "bfloat16", True, True, True,
                   "BERT-base shapes (206 tensors, 110,106,428 elems), AMP bf16 + fp32 master, global-norm clip"),
-    "gpt2_medium": ("gpt2_medium", "bfloat16", "bfloat16", True, True, True, 34,
+    "gpt2_medium": ("gpt2_medium", "bfloat16", "bfloat16", True, True, True,
                     "GPT-2 medium shapes (292 tensors, 354,823,168 elems), multi_precision bf16, 25 MB buckets"),
 }
+DEFAULT_WORKLOAD = "bert_base"
+# configs[4]: the flat sweep (name = flat<log2 n | 2e9>x<tensors>[r = ragged sizes][:bf16])
+FLAT_SWEEP = ["flat20x1", "flat22x1", "flat24x1", "flat26x1", "flat28x1", "flat30x1", "flat2e9x1", "flat26x1000r",
+              "flat26x1:bf16", "flat30x1:bf16", "flat26x1000r:bf16"]
+
+
+def workload_spec(name):
+    """-> (shape list name, param dtype, grad dtype, amp, clip, multi_precision, description)"""
+    if name in WORKLOADS:
+        return WORKLOADS[name]
+    base, _, dt = name.partition(":")
+    if dt == "bf16":
+        return (base, "bfloat16", "bfloat16", False, False, True, "flat sweep %s, bf16 + fp32 master, fused AdamW" % base)
+    return (base, "float32", "float32", False, False, False, "flat sweep %s, fp32, fused AdamW" % base)
+
+
+def bytes_per_elem(pdt, gdt, amp, clip, arena, fused_pass1=True):
+    """Algorithmic HBM bytes per gradient element of one step."""
+    s = 4 if gdt == "float32" else 2
+    upd = 28 + (2 if (pdt != "float32" and gdt == "float32") else 0)   # fp32 main-grad next to a 16-bit param: 30
+    pack = 0 if arena else 2 * s
+    norm_read = s if ((amp or clip) and (arena or not fused_pass1)) else 0
+    return upd + pack + norm_read
 
 
 def measured_peak():
@@ -56,6 +85,13 @@ def measured_peak():
             return float(json.load(f)["hbm_gbs"]), "measured"
     except Exception:
         return 6650.0, "fallback"
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
 
 
 # --------------------------------------------------------------------------------------------
@@ -115,61 +151,79 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------
 # workload construction (product API only)
 # --------------------------------------------------------------------------------------------
-def build_workload(prb, name, rank):
-    shapes_name, pdt, gdt, amp, clip, mp, bpe, desc = WORKLOADS[name] if name in WORKLOADS else \
-        (name, "float32", "float32", False, False, False, 36, "flat sweep " + name)
+_TILE = 1 << 22
+
+
+def _fill(prb, t, rng, mean_scale, uniform=False):
+    """Synthetic values.  Tensors above 16 M elements are filled by tiling one random
+    4 M-element block on the device (host RNG for 2e9 elements would take minutes; throughput does not care)."""
+    n = t.numel
+    nb = n if n <= (1 << 24) else _TILE
+    blk = (rng.random(nb, dtype=np.float32) if uniform else rng.standard_normal(nb, dtype=np.float32)) * np.float32(mean_scale)
+    first = t if nb == n else t.view(0, nb)
+    if t.dtype == prb._lib.FLOAT32:
+        first.copy_from_numpy(blk)
+    else:
+        first.copy_(prb.Tensor.from_numpy(blk).astype(t.dtype))
+        prb.current_stream().synchronize()
+    es = prb._lib.DTYPE_SIZE[t.dtype]
+    done = nb
+    while done < n:
+        m = min(done, n - done)
+        prb._lib.call("prb_memcpy_d2d", t.data_ptr + done * es, t.data_ptr, m * es, prb.current_stream().handle)
+        done += m
+    return blk if nb == n else None
+
+
+def build_workload(prb, name, rank, arena=False, host_mirror=False, producer_pass1=True):
+    shapes_name, pdt, gdt, amp, clip, mp, desc = workload_spec(name)
     numels = bench_configs.param_numels(shapes_name)
     rng = np.random.default_rng(1234 + rank)
-    # gradients live in ONE device arena (256-byte aligned views), mirrored by one pinned host arena, so the
-    # e2e leg moves them with a single H2D copy -- what a caller that controls allocation would do
     gsz = 4 if gdt == "float32" else 2
-    align = 256 // gsz
-    offs, total = [], 0
-    for n in numels:
-        offs.append(total)
-        total += (n + align - 1) // align * align
-    grad_arena = prb.Tensor.zeros(total, gdt)
-    host_arena = prb.PinnedBuffer(total, np.float32 if gsz == 4 else np.uint16)
-    host_arena.array[:] = 0
     params = []
-    for i, (n, off) in enumerate(zip(numels, offs)):
-        p32 = rng.normal(0, 0.02, n).astype(np.float32)
-        g32 = rng.normal(0, 1e-2, n).astype(np.float32)
-        if amp:
-            g32 *= np.float32(2.0 ** 15)
-        if pdt == "float32":
-            p = prb.Tensor.from_numpy(p32, name="w_%d" % i)
-        else:
-            p = prb.Tensor.from_numpy(p32).astype(pdt)
-            p.name = "w_%d" % i
-        g = grad_arena.view(off, n)
-        if gdt == "float32":
-            g.copy_from_numpy(g32)
-        else:
-            tmp = prb.Tensor.from_numpy(g32).astype(gdt)
-            g.copy_(tmp)
-            prb.current_stream().synchronize()
-        host_arena.array[off:off + n] = g.numpy()
-        p.grad = g
+    for i, n in enumerate(numels):
+        p = prb.Tensor(n, pdt, name="w_%d" % i)
+        _fill(prb, p, rng, 0.02)
         params.append(p)
+    grad_arena = host_arena = None
+    offs, total = [], 0
+    if not arena:
+        # gradients live in ONE device arena (256-byte aligned views, parameter order), mirrored by one pinned host
+        # arena, so the e2e leg moves each bucket's gradients with a single H2D copy
+        align = 256 // gsz
+        for n in numels:
+            offs.append(total)
+            total += (n + align - 1) // align * align
+        grad_arena = prb.Tensor.zeros(total, gdt)
+        for p, off in zip(params, offs):
+            p.grad = grad_arena.view(off, p.numel)
     grad_clip = prb.nn.ClipGradByGlobalNorm(1.0) if clip else None
     opt = prb.optimizer.AdamW(learning_rate=1e-3, beta1=0.9, beta2=0.999, epsilon=1e-8, parameters=params,
                               weight_decay=0.01, grad_clip=grad_clip, multi_precision=mp)
     # the reduced gradients are consumed from the bucket arena; nothing reads an unscaled copy back
     opt._write_back_unscaled_grads = False
+    opt._use_producer_pass1 = producer_pass1
     opt._create_accumulators()
     # moments start away from zero (BASELINE.md section 3: m1 N(0,1e-3), m2 U(0,1e-3), step 10)
     for p in params:
         acc = opt._accumulators[p.name]
-        acc["moment1"].copy_from_numpy(rng.normal(0, 1e-3, p.numel).astype(np.float32))
-        acc["moment2"].copy_from_numpy(rng.uniform(0, 1e-3, p.numel).astype(np.float32))
+        _fill(prb, acc["moment1"], rng, 1e-3)
+        _fill(prb, acc["moment2"], rng, 1e-3, uniform=True)
     opt._beta1_pow.copy_from_numpy(np.array([0.9 ** 10], np.float32))
     opt._beta2_pow.copy_from_numpy(np.array([0.999 ** 10], np.float32))
     scaler = prb.amp.GradScaler(init_loss_scaling=2.0 ** 15) if amp else None
-    dp = prb.DataParallel(params, comm_buffer_size=25, last_comm_buffer_size=1, consume_from_buckets=True)
-    return {"params": params, "opt": opt, "scaler": scaler, "dp": dp, "numels": numels, "bpe": bpe, "desc": desc,
-            "grad_arena": grad_arena, "host_arena": host_arena, "amp": amp, "clip": clip, "pdt": pdt, "gdt": gdt,
-            "elems": int(sum(numels)), "buckets": len(dp.group_indices)}
+    dp = prb.DataParallel(params, comm_buffer_size=25, last_comm_buffer_size=1, consume_from_buckets=True,
+                          grads_in_arena=arena)
+    for p in params:  # grads ~ N(0, 1e-2), times the loss scale for AMP runs
+        _fill(prb, p.grad, rng, 1e-2 * (2.0 ** 15 if amp else 1.0))
+    if host_mirror and not arena:
+        host_arena = prb.PinnedBuffer(total, np.float32 if gsz == 4 else np.uint16)
+        prb._lib.call("prb_memcpy_d2h", host_arena.ptr, grad_arena.data_ptr, grad_arena.nbytes, prb.current_stream().handle)
+    prb.current_stream().synchronize()
+    return {"name": name, "params": params, "opt": opt, "scaler": scaler, "dp": dp, "numels": numels, "desc": desc,
+            "grad_arena": grad_arena, "host_arena": host_arena, "offs": offs, "amp": amp, "clip": clip, "pdt": pdt,
+            "gdt": gdt, "arena": arena, "elems": int(sum(numels)), "buckets": len(dp.group_indices), "gsz": gsz,
+            "bpe": bytes_per_elem(pdt, gdt, amp, clip, arena, producer_pass1), "clip_obj": grad_clip}
 
 
 def make_step(w):
@@ -190,94 +244,51 @@ def make_step(w):
     return step, tail
 
 
-# --------------------------------------------------------------------------------------------
-# CPU baseline: the reference's CPU path restated in oracle/ (kind "port"), all host threads
-# --------------------------------------------------------------------------------------------
-def cpu_reference_run(workload, nranks, budget_s, min_steps=2, max_steps=10 ** 9, warmup=1):
-    """concat -> scale(1/nranks) -> [allreduce: one process, nothing to exchange] -> split -> AdamW per tensor.
-    ref: reducer.cc:1037-1070 on CPUPlace, cpu/adamw_kernel.cc:96-189.  fp32 only (the CPU kernel
-    registers float/double only), so bf16 workloads are timed with fp32 storage of the same shapes."""
-    from oracle import oracle as orc
-    shapes_name = WORKLOADS[workload][0] if workload in WORKLOADS else workload
-    bpe = WORKLOADS[workload][6] if workload in WORKLOADS else 36
-    numels = bench_configs.param_numels(shapes_name)
-    rng = np.random.default_rng(1234)
-    threads = orc.max_threads()
-    P = [rng.normal(0, 0.02, n).astype(np.float32) for n in numels]
-    G = [rng.normal(0, 1e-2, n).astype(np.float32) for n in numels]
-    M1 = [rng.normal(0, 1e-3, n).astype(np.float32) for n in numels]
-    M2 = [rng.uniform(0, 1e-3, n).astype(np.float32) for n in numels]
-    b1p, b2p = np.float32(0.9 ** 10), np.float32(0.999 ** 10)
-    elems = int(sum(numels))
-
-    bucket = np.empty(elems, np.float32)  # a caching allocator would hand the same pages back every step
-    grads = [np.empty(n, np.float32) for n in numels]
-
-    def one_step():
-        orc.concat(G, out=bucket)                                # memcpy-loop concat
-        orc.cpu_scale_f32(bucket, np.float32(1.0 / nranks), threads)
-        orc.split(bucket, numels, outs=grads)                    # memcpy-loop split
-        for p, g, m1, m2 in zip(P, grads, M1, M2):
-            orc.cpu_adamw(p, g, m1, m2, lr=1e-3, lr_ratio=1.0, beta1=0.9, beta2=0.999, epsilon=1e-8, coeff=0.01,
-                          beta1_pow=b1p, beta2_pow=b2p, nthreads=threads)
-
-    for _ in range(max(1, warmup)):  # untimed warm-up (page faults, thread pool)
-        one_step()
-    t0 = time.perf_counter()
-    steps = 0
-    while steps < max_steps and (steps < min_steps or time.perf_counter() - t0 < budget_s):
-        one_step()
-        steps += 1
-    dt = time.perf_counter() - t0
-    return {"gbs": elems * bpe * steps / dt / 1e9, "ms_per_step": dt / steps * 1e3, "steps": steps, "threads": threads,
-            "elems": elems, "seconds": dt}
+KERNEL_KINDS = 6
+# algorithmic bytes per element each kernel kind moves (s = gradient element size, upd = 28 / 30)
+def kernel_bytes(kind_name, w, nranks):
+    s = w["gsz"]
+    upd = 28 + (2 if (w["pdt"] != "float32" and w["gdt"] == "float32") else 0)
+    return {"map_chunks_kernel": 2 * s, "grad_pass_kernel": s, "grad_pass_kernel<pack>": 2 * s,
+            "adam_chunks_kernel": upd, "norm_finalize_kernel": 0,
+            # exchange, per rank: reads its slice from n ranks, writes it to n ranks (HBM + NVLink together)
+            "nvl_exchange_kernel": 2 * s}[kind_name]
 
 
-def run_reference_arm(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return 0  # only rank 0 runs the CPU arm
-    # each "step" of this arm = one full CPU pass over the workload; bounded so the run ends within minutes
-    # W untimed warm-up steps, then K timed ones; the time budget only cuts K short for workloads where K full CPU
-    # passes would take more than two minutes (the line then reports the steps really timed)
-    budget = 120.0
-    r = cpu_reference_run(args.workload, args.gpus, budget_s=budget, min_steps=1, max_steps=args.steps,
-                          warmup=args.warmup)
-    desc = WORKLOADS[args.workload][7] if args.workload in WORKLOADS else args.workload
-    line = {
-        "impl": "reference", "metric": METRIC, "value": r["gbs"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
-        "warmup": max(1, args.warmup), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "path": "CPU: concat -> scale(1/nranks) -> split -> AdamW (oracle port of the "
-                   "reference's CPU kernels; Paddle itself cannot be built here)", "allreduce": "none (one process)"},
-        "cpu_baseline": {"value": r["gbs"], "unit": UNIT, "cores": r["threads"], "kind": "port",
-                         "sample": "%d full steps of the workload in %.1f s" % (r["steps"], r["seconds"])},
-        "e2e": {"value": r["gbs"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }
-    print(json.dumps(line), flush=True)
-    return 0
+def read_kernel_timing(prb, w, nranks, steps, peak):
+    """Per-kernel rooflines from the CUDA events the library recorded around every launch (prb_kernel_timing)."""
+    lib = prb._lib.lib
+    out = {}
+    for k in range(KERNEL_KINDS):
+        ms, n = C.c_double(), C.c_int64()
+        prb._lib.call("prb_kernel_timing_read", k, C.byref(ms), C.byref(n))
+        if n.value == 0:
+            continue
+        name = lib.prb_kernel_kind_name(k).decode()
+        per_step = ms.value / steps
+        bpe = kernel_bytes(name, w, nranks)
+        e = {"launches_per_step": n.value / steps, "ms_per_step": per_step}
+        if bpe:
+            e["algorithmic_bytes_per_step"] = bpe * w["elems"]
+            e["achieved_gbs"] = bpe * w["elems"] / (per_step * 1e-3) / 1e9
+            e["frac_of_measured_hbm_peak"] = e["achieved_gbs"] / peak
+        out[name] = e
+    return out
 
 
-# --------------------------------------------------------------------------------------------
-# the GPU arm
-# --------------------------------------------------------------------------------------------
-def run_gpu_arm(args):
-    import paddle_ray_b200 as prb  # fails loudly if the CUDA library is missing
-    from paddle_ray_b200._lib import lib
-
-    if prb.device_count() == 0:
-        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
-    group = prb.distributed.init_parallel_env()
-    rank, nranks = group.rank, group.nranks
-    if nranks != args.gpus:
-        raise SystemExit("bench.py: --gpus %d but WORLD_SIZE=%d (launch N>1 through torch.distributed.run)" % (args.gpus, nranks))
-    w = build_workload(prb, args.workload, rank)
+def measure_workload(prb, group, w, steps, warmup, peak, instrumented=True, sample_clocks=False):
+    """K timed steps between two CUDA events on the launching stream (barrier + synchronize on both sides, start
+    events lined up on the device, max over ranks), then the same K steps once more with the library's per-kernel
+    event timing switched on (for the per-kernel rooflines; the instrumented step time is reported next to the
+    clean one so that the cost of the instrumentation is visible)."""
+    lib = prb._lib.lib
+    nranks = group.nranks
     step, tail = make_step(w)
     stream = prb.current_stream()
-    peak, peak_kind = measured_peak()
-    bytes_per_step = w["elems"] * w["bpe"]
 
     def rank_max(x: float) -> float:
+        if nranks == 1:
+            return x
         t = prb.Tensor.from_numpy(np.array([x], np.float32))
         group.all_reduce(t, "max")
         return float(t.numpy()[0])
@@ -291,138 +302,366 @@ def run_gpu_arm(args):
         if nranks > 1:
             group.all_reduce(sync_t)
 
-    # ---- warm-up (also builds every cached plan)
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(max(warmup, 3)):   # also builds every cached plan and arms the producer-side pass 1
         step()
     stream.synchronize()
 
-    # ---- timed region: exactly K steps, barrier + sync on both sides, CUDA events on the launching stream
-    group.barrier()
-    prb.synchronize()
-    sampler = ClockSampler(group.device)
-    ev0, ev1 = prb.Event(), prb.Event()
-    # CUDA events right around every optimizer launch (after its per-bucket stream wait), from a pre-built pool
-    ncalls = max(1, w["buckets"]) if w["dp"].pipelined else 1
-    w["opt"]._launch_events = [(prb.Event(), prb.Event()) for _ in range(args.steps * ncalls + 8)]
-    w["opt"]._launch_events_used = []
+    def timed(k):
+        group.barrier()
+        prb.synchronize()
+        ev0, ev1 = prb.Event(), prb.Event()
+        device_barrier()
+        ev0.record()
+        for _ in range(k):
+            step()
+        ev1.record()
+        ev1.synchronize()
+        group.barrier()
+        prb.synchronize()
+        return rank_max(ev0.elapsed_ms(ev1)) / k
+
+    sampler = ClockSampler(group.device) if sample_clocks else None
     launches0 = lib.prb_launch_count()
-    sampler.start()
-    device_barrier()   # ranks leave the host barrier at different moments; this lines the START events up on the device
-    ev0.record()
-    for i in range(args.steps):
-        w["dp"].prepare_for_backward()
-        w["dp"].mark_all_ready()
-        tail()            # the dominant kernel: the fused multi-tensor AdamW launch (one per bucket when pipelined)
-    ev1.record()
-    ev1.synchronize()
-    clocks = sampler.stop()
+    if sampler:
+        sampler.start()
+    ms_per_step = timed(steps)
+    clocks = sampler.stop() if sampler else None
     launches = lib.prb_launch_count() - launches0
-    group.barrier()
-    prb.synchronize()
-    ms_total = rank_max(ev0.elapsed_ms(ev1))
-    ms_per_step = ms_total / args.steps
-    value = bytes_per_step * nranks / (ms_per_step * 1e-3) / 1e9
-    used = w["opt"]._launch_events_used
-    w["opt"]._launch_events = None
-    tail_ms = float(sum(a.elapsed_ms(b) for a, b in used)) / args.steps   # optimizer launch time per step
+    out = {"ms_per_step": ms_per_step, "value": w["elems"] * w["bpe"] * nranks / (ms_per_step * 1e-3) / 1e9,
+           "bytes_per_elem": w["bpe"], "launches_per_step": launches / steps, "clocks": clocks, "gpu_launches": int(launches),
+           "rank_max": rank_max, "device_barrier": device_barrier}
+    if instrumented:
+        prb._lib.call("prb_kernel_timing", 1)
+        out["ms_per_step_instrumented"] = timed(steps)
+        prb._lib.call("prb_kernel_timing", 0)
+        out["kernels"] = read_kernel_timing(prb, w, nranks, steps, peak)
+    return out
 
-    # ---- host cost of issuing a step (diagnostic): 10 steps issued into an empty queue, clock stopped before the sync
-    prb.synchronize()
+
+def nested_result(m, peak, nranks):
+    """The part of a measurement that goes under `configs` of the JSON line."""
+    r = {"ms_per_step": m["ms_per_step"], "value": m["value"], "bytes_per_elem": m["bytes_per_elem"],
+         "pct_of_measured_hbm_peak_per_gpu": 100.0 * m["value"] / nranks / peak,
+         "launches_per_step": m["launches_per_step"]}
+    if "kernels" in m:
+        r["kernels"] = m["kernels"]
+        adam = m["kernels"].get("adam_chunks_kernel")
+        if adam:
+            r["roofline"] = {"bound": "hbm", "kernel": "adam_chunks_kernel", "achieved": adam["achieved_gbs"],
+                             "peak": peak, "unit": "GB/s", "frac": adam["achieved_gbs"] / peak, "traffic": None}
+    return r
+
+
+# --------------------------------------------------------------------------------------------
+# CPU baseline: the reference's CPU path restated in oracle/ (kind "port"), all host threads
+# --------------------------------------------------------------------------------------------
+def cpu_reference_run(workload, nranks, budget_s, threads, min_steps=2, max_steps=10 ** 9, warmup=1, dist=None, rank=0):
+    """Per bucket: concat -> scale(1/nranks) -> allreduce (gloo, when nranks > 1) -> split; then AdamW per tensor.
+    ref: reducer.cc:1037-1070 on CPUPlace, process_group_gloo.cc:279-343, cpu/adamw_kernel.cc:96-189.  fp32 only
+    (the CPU kernel registers float/double only), so bf16 workloads are timed with fp32 storage of the same shapes;
+    AMP unscale and the clip are left out (the CPU arm would only get slower)."""
+    from oracle import oracle as orc
+    shapes_name, pdt, gdt, amp, clip, mp, desc = workload_spec(workload)
+    bpe = bytes_per_elem(pdt, gdt, amp, clip, False)
+    numels = bench_configs.param_numels(shapes_name)
+    rng = np.random.default_rng(1234 + rank)
+    P = [rng.standard_normal(n, dtype=np.float32) * np.float32(0.02) for n in numels]
+    G = [rng.standard_normal(n, dtype=np.float32) * np.float32(1e-2) for n in numels]
+    M1 = [rng.standard_normal(n, dtype=np.float32) * np.float32(1e-3) for n in numels]
+    M2 = [rng.random(n, dtype=np.float32) * np.float32(1e-3) for n in numels]
+    b1p, b2p = np.float32(0.9 ** 10), np.float32(0.999 ** 10)
+    elems = int(sum(numels))
+    # the reference's buckets: 1 MiB for the last parameters, 25 MiB otherwise, launched in reverse order
+    groups = orc.assign_group_by_size(numels, [orc.F32] * len(numels), [False] * len(numels), [1 << 20, 25 << 20])
+    groups = list(reversed(groups))
+    buckets = [np.empty(sum(numels[v] for v in g), np.float32) for g in groups]  # a caching allocator reuses them
+    grads = [np.empty(n, np.float32) for n in numels]
+    torch = None
+    if dist is not None:
+        import torch
+
+    def one_step():
+        for g, bucket in zip(groups, buckets):
+            orc.concat([G[v] for v in g], out=bucket)                  # memcpy-loop concat
+            orc.cpu_scale_f32(bucket, np.float32(1.0 / nranks), threads)
+            if dist is not None:
+                dist.all_reduce(torch.from_numpy(bucket))              # gloo, in place, sum
+            orc.split(bucket, [numels[v] for v in g], outs=[grads[v] for v in g])   # memcpy-loop split
+        for p, g, m1, m2 in zip(P, grads, M1, M2):
+            orc.cpu_adamw(p, g, m1, m2, lr=1e-3, lr_ratio=1.0, beta1=0.9, beta2=0.999, epsilon=1e-8, coeff=0.01,
+                          beta1_pow=b1p, beta2_pow=b2p, nthreads=threads)
+
+    for _ in range(max(1, warmup)):  # untimed warm-up (page faults, thread pool, gloo connections)
+        one_step()
+    if dist is not None:
+        dist.barrier()
     t0 = time.perf_counter()
-    for i in range(10):
-        step()
-    host_issue_ms = (time.perf_counter() - t0) * 1e3 / 10
-    prb.synchronize()
+    steps = 0
+    while steps < max_steps:
+        go = steps < min_steps or time.perf_counter() - t0 < budget_s
+        if dist is not None:  # every rank must take the same decision
+            flag = torch.tensor([1 if go else 0])
+            dist.broadcast(flag, 0)
+            go = bool(flag.item())
+        if not go:
+            break
+        one_step()
+        steps += 1
+    if dist is not None:
+        dist.barrier()
+    dt = time.perf_counter() - t0
+    return {"gbs": elems * bpe * nranks * steps / dt / 1e9, "ms_per_step": dt / steps * 1e3, "steps": steps,
+            "threads": threads, "elems": elems, "seconds": dt, "bpe": bpe, "desc": desc, "buckets": len(groups)}
 
-    # ---- roofline of the dominant kernel (AdamW update pass): algorithmic bytes / live launch duration
-    upd_bpe = 28 if w["gdt"] == w["pdt"] else 30
-    tail_bytes = w["elems"] * (upd_bpe + (2 if w["clip"] or w["amp"] else 0))  # + the norm pass read for AMP/clip runs
-    achieved = tail_bytes / (tail_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "adam_chunks_kernel (+grad_pass_kernel when AMP/clip)",
-                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peak_kind == "measured" else "profiling-recipe fallback",
-                "algorithmic_bytes_per_launch": tail_bytes, "avg_launch_ms": tail_ms,
-                "frac_of_nominal_8TBps": achieved / 8000.0}
-    try:  # dram bytes per launch from the committed ncu capture, when one exists for this workload
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            roofline["traffic"] = json.load(f).get(args.workload)
-    except Exception:
-        pass
 
-    # ---- e2e: gradients arrive from pinned host memory every step, a result is read back every step
-    res_host = prb.PinnedBuffer(w["numels"][0] + 2, np.float32 if w["pdt"] == "float32" else np.uint16)
-    h2d = w["host_arena"].nbytes
-    p0 = w["params"][0]
-    d2h = p0.nbytes + 8
+def reference_worker(args):
+    """One of N local CPU processes of `--impl reference --gpus N` (N > 1): gloo over 127.0.0.1."""
+    rank, world = int(os.environ["PRB_REF_RANK"]), int(os.environ["PRB_REF_WORLD"])
+    threads = int(os.environ["PRB_REF_THREADS"])
+    import torch
+    import torch.distributed as dist
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % os.environ["PRB_REF_PORT"], rank=rank,
+                            world_size=world)
+    r = cpu_reference_run(args.workload, world, budget_s=120.0, threads=threads, min_steps=1, max_steps=args.steps,
+                          warmup=args.warmup, dist=dist, rank=rank)
+    if rank == 0:
+        print("PRB_REF_RESULT " + json.dumps(r), flush=True)
+    dist.destroy_process_group()
+    return 0
+
+
+def config_block(desc, elems, tensors, buckets, pdt, gdt, amp, clip, bpe, nranks):
+    """The `config` object: identical (keys and values) in both arms for the same workload and N -- the driver compares
+    them.  Arm-specific facts (which allreduce, percentages of peak, the CPU path) go to `details` instead."""
+    return {"workload": desc, "elements_per_gpu": elems, "tensors": tensors, "buckets": buckets, "bucket_mb": [25, 1],
+            "param_dtype": pdt, "grad_dtype": gdt, "amp": amp, "clip": clip, "algorithmic_bytes_per_elem": bpe,
+            "parallelism": "dp%d" % nranks,
+            "l2": "working set %.0f MB per step > 126 MB L2 (inputs larger than L2, no flush)" % (elems * (bpe + 8) / 1e6)}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0  # only rank 0 runs the CPU arm
+    # each "step" of this arm = one full CPU pass over the workload: W untimed warm-up steps, then K timed ones; a time
+    # budget cuts K short where K full CPU passes would take more than two minutes (the line reports the steps timed)
+    cores = host_cores()
+    n = args.gpus
+    if n == 1:
+        r = cpu_reference_run(args.workload, 1, budget_s=120.0, threads=cores, min_steps=1, max_steps=args.steps,
+                              warmup=args.warmup)
+        allreduce = "none (one process)"
+    else:
+        import socket
+        s = socket.socket()
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+        s.close()
+        per = max(1, cores // n)
+        procs = []
+        for q in range(n):
+            env = {k: v for k, v in os.environ.items() if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR",
+                                                                     "MASTER_PORT", "OMP_NUM_THREADS", "TORCHELASTIC_RUN_ID")}
+            env.update({"PRB_REF_RANK": str(q), "PRB_REF_WORLD": str(n), "PRB_REF_PORT": str(port),
+                        "PRB_REF_THREADS": str(per), "OMP_NUM_THREADS": str(per)})
+            procs.append(subprocess.Popen([sys.executable, os.path.abspath(__file__), "--impl", "reference-worker",
+                                           "--workload", args.workload, "--steps", str(args.steps), "--warmup",
+                                           str(args.warmup), "--gpus", str(n)], env=env, stdout=subprocess.PIPE))
+        outs = [p.communicate()[0].decode() for p in procs]
+        if any(p.returncode for p in procs):
+            print(json.dumps({"impl": "reference", "unavailable": "a gloo worker of the CPU arm failed"}), flush=True)
+            return 0
+        line = [ln for ln in outs[0].splitlines() if ln.startswith("PRB_REF_RESULT ")][0]
+        r = json.loads(line[len("PRB_REF_RESULT "):])
+        r["threads"] = per * n
+        allreduce = "gloo (torch wheel), %d local processes x %d threads" % (n, per)
+    shapes_name, pdt, gdt, amp, clip, mp, desc = workload_spec(args.workload)
+    cfg = config_block(desc, r["elems"], len(bench_configs.param_numels(shapes_name)), r["buckets"], pdt, gdt, amp, clip,
+                       r["bpe"], n)
+    details = {"allreduce": allreduce,
+               "path": ("CPU: per bucket concat -> scale(1/nranks) -> allreduce -> split, then AdamW per tensor (oracle "
+                        "port of the reference's CPU kernels in fp32 storage; Paddle itself cannot be built here)")}
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["gbs"], "unit": UNIT, "n_gpus": n, "steps": r["steps"],
+        "warmup": max(1, args.warmup), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg, "details": details,
+        "cpu_baseline": {"value": r["gbs"], "unit": UNIT, "cores": r["threads"], "kind": "port",
+                         "sample": "%d full steps of the workload in %.1f s" % (r["steps"], r["seconds"])},
+        "e2e": {"value": r["gbs"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------------
+# N > 1 parity preamble (untimed, < 1 s): the GPU-test box has one GPU, so the multi-rank path proves itself here
+# --------------------------------------------------------------------------------------------
+def parity_preamble(prb, group):
+    """A tiny AMP bf16 + master + clip job through the same API on all ranks: one clean step, one step with an Inf
+    injected on ONE rank (every rank must skip and halve its loss scale), one more clean step.  After each step
+    parameters, masters, moments and the scaler state must be bit-equal across ranks (checksums compared through
+    the communicator); with two ranks (one addition, so the order cannot matter) they must also equal the oracle's
+    composition of the reference's stages bit for bit.  Returns "ok" or "fail: <what>"."""
+    from oracle import oracle as orc
+    rank, n = group.rank, group.nranks
+    sizes = [64, 3 * 3 * 64 * 16, 1000, 7, 4096, 4097, 250000, 1, 300000]
+    try:
+        params, host = [], []
+        for i, sz in enumerate(sizes):
+            p0 = orc.from_f32(np.random.default_rng(100 + i).normal(0, 0.02, sz).astype(np.float32), orc.BF16)
+            p = prb.Tensor.from_numpy(p0, orc.BF16, name="pp_%d" % i)
+            p.grad = prb.Tensor.zeros(sz, orc.BF16)
+            params.append(p)
+            host.append({"param": p0.copy(), "mom1": np.zeros(sz, np.float32), "mom2": np.zeros(sz, np.float32),
+                         "master": orc.to_f32(p0, orc.BF16)})
+        clip = prb.nn.ClipGradByGlobalNorm(1.0)
+        opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, weight_decay=0.01, grad_clip=clip,
+                                  multi_precision=True)
+        scaler = prb.amp.GradScaler(init_loss_scaling=2.0 ** 15, decr_every_n_nan_or_inf=1)
+        dp = prb.DataParallel(params, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True)
+        scale, b1p, b2p = 2.0 ** 15, np.float32(0.9), np.float32(0.999)
+        for step in range(4):
+            per_rank = [[orc.from_f32((np.random.default_rng(1000 * r + 10 * step + i).normal(0, 1e-2, sz) * 2.0 ** 15 * 30)
+                                      .astype(np.float32), orc.BF16) for i, sz in enumerate(sizes)] for r in range(n)]
+            if step == 1:
+                per_rank[n - 1][4][17] = orc.from_f32(np.array([np.inf], np.float32), orc.BF16)[0]   # one rank only
+            for p, g in zip(params, per_rank[rank]):
+                p.grad.copy_from_numpy(g)
+            dp.prepare_for_backward()
+            dp.mark_all_ready()
+            scaler.step(opt)
+            scaler.update()
+            prb.current_stream().synchronize()
+            found = bool(scaler._found_inf.numpy()[0])
+            if found != (step == 1):
+                return "fail: step %d found_inf=%s on rank %d" % (step, found, rank)
+            # cross-rank bit equality through a checksum
+            h = 0
+            for p in params:
+                for t in (p, opt._master_weights[p.name], opt._accumulators[p.name]["moment1"],
+                          opt._accumulators[p.name]["moment2"]):
+                    a = t.numpy()
+                    h = (h * 1000003 + int(np.bitwise_xor.reduce(a.view(np.uint16 if a.dtype.itemsize == 2 else np.uint32)
+                                                                 .astype(np.uint64) * np.arange(1, a.size + 1, dtype=np.uint64)))) % (1 << 52)
+            h = (h * 1000003 + int(scaler._scale.numpy().view(np.uint32)[0])) % (1 << 52)
+            t = prb.Tensor.from_numpy(np.array([h, -h], np.float64))
+            group.all_reduce(t, "max")
+            mx, mn = t.numpy()
+            if mx != -mn:
+                return "fail: step %d state differs across ranks" % step
+            if n == 2:
+                red = []
+                for i in range(len(sizes)):
+                    s = sum(orc.to_f32(orc.scale(per_rank[r][i], orc.BF16, 1.0 / n), orc.BF16).astype(np.float64) for r in range(n))
+                    red.append(orc.from_f32(s.astype(np.float32), orc.BF16))
+                if orc.check_finite_and_unscale(red, orc.BF16, scale) != found:
+                    return "fail: step %d oracle found_inf differs" % step
+                if found:
+                    scale /= 2
+                else:
+                    c = float(clip.last_clip.numpy()[0])
+                    _, c_or = orc.global_norm_clip([g.copy() for g in red], [orc.BF16] * len(red), 1.0)
+                    if abs(c - c_or) > 4e-3 * abs(c_or):
+                        return "fail: step %d clip factor %g vs oracle %g" % (step, c, c_or)
+                    for hst, g, p in zip(host, red, params):
+                        orc.clip_mul(g, orc.BF16, c)
+                        orc.adam(hst["param"], g, hst["mom1"], hst["mom2"], hst["master"], dtype_param=orc.BF16,
+                                 dtype_grad=orc.BF16, lr=1e-3, beta1=0.9, beta2=0.999, epsilon=1e-8, coeff=0.01,
+                                 use_decay=True, beta1_pow=b1p, beta2_pow=b2p)
+                        if p.numpy().tobytes() != hst["param"].tobytes() or \
+                                opt._master_weights[p.name].numpy().tobytes() != hst["master"].tobytes():
+                            return "fail: step %d %s differs from the oracle" % (step, p.name)
+                    b1p, b2p = np.float32(0.9) * b1p, np.float32(0.999) * b2p
+        if float(scaler._scale.numpy()[0]) != 2.0 ** 14:
+            return "fail: loss scale %g" % float(scaler._scale.numpy()[0])
+        if dp._reducer.comm_error():
+            return "fail: exchange kernel reported an error"
+        return "ok"
+    except Exception as e:  # noqa: BLE001
+        return "fail: %s: %s" % (type(e).__name__, str(e)[:200])
+
+
+# --------------------------------------------------------------------------------------------
+# e2e: gradients arrive from pinned host memory every step, the step's metric is read back every step
+# --------------------------------------------------------------------------------------------
+def measure_e2e(prb, group, w, steps, rank_max):
+    """Public API, host buffers: per bucket (launch order) one H2D copy of that bucket's gradients on a copy stream,
+    an event, and mark_vars_ready for the bucket's parameters on the calc stream -- so the copy of bucket k+1 runs
+    under the pack of bucket k, and the step costs max(copy, kernels) + the update, not their sum.  Read back: what
+    a training loop logs every step -- global gradient norm, found_inf, loss scale (9 bytes)."""
+    dp, opt, scaler = w["dp"], w["opt"], w["scaler"]
+    stream = prb.current_stream()
+    copy_stream = prb.Stream()
+    groups = list(reversed(dp.group_indices))   # launch order
+    gsz = w["gsz"]
+    plan = []
+    for g in groups:
+        lo, hi = min(g), max(g)
+        assert sorted(g) == list(range(lo, hi + 1))   # a bucket is a contiguous parameter range
+        off0 = w["offs"][lo] * gsz
+        off1 = (w["offs"][hi] + w["numels"][hi]) * gsz
+        plan.append((off0, off1 - off0, (C.c_int64 * len(g))(*sorted(g, reverse=True)), prb.Event()))
+    h2d = sum(p[1] for p in plan)
+    res_host = prb.PinnedBuffer(4, np.float32)
+    reads = []
+    if w["clip_obj"] is not None:
+        reads.append((w["clip_obj"].last_global_norm.data_ptr, 4))
+    if scaler is not None:
+        reads += [(scaler._found_inf.data_ptr, 1), (scaler._scale.data_ptr, 4)]
+    if not reads:
+        reads = [(opt._beta1_pow.data_ptr, 4), (opt._beta2_pow.data_ptr, 4)]
+    d2h = sum(n for _, n in reads)
+    done = prb.Event()
+    _, tail = make_step(w)
 
     def e2e_step():
-        prb._lib.call("prb_memcpy_h2d", w["grad_arena"].data_ptr, w["host_arena"].ptr, h2d, stream.handle)
-        step()
-        prb._lib.call("prb_memcpy_d2h", res_host.ptr, p0.data_ptr, p0.nbytes, stream.handle)
-        prb._lib.call("prb_memcpy_d2h", res_host.ptr + p0.nbytes, w["opt"]._beta1_pow.data_ptr, 4, stream.handle)
-        prb._lib.call("prb_memcpy_d2h", res_host.ptr + p0.nbytes + 4, w["opt"]._beta2_pow.data_ptr, 4, stream.handle)
+        copy_stream.wait_event(done)   # the previous step's packs have consumed the gradient arena
+        dp.prepare_for_backward()
+        for off, nbytes, vars_, ev in plan:
+            prb._lib.call("prb_memcpy_h2d", w["grad_arena"].data_ptr + off, w["host_arena"].ptr + off, nbytes,
+                          copy_stream.handle)
+            ev.record(copy_stream)
+            stream.wait_event(ev)
+            dp._reducer.mark_vars_ready(vars_)
+        done.record(stream)
+        tail()
+        at = 0
+        for ptr, n in reads:
+            prb._lib.call("prb_memcpy_d2h", res_host.ptr + at, ptr, n, stream.handle)
+            at += 4
         stream.synchronize()  # the caller consumes the result on the host
 
+    done.record(stream)
     for _ in range(3):
         e2e_step()
     group.barrier()
     prb.synchronize()
-    e2e_steps = max(3, min(args.steps, 20))
+    k = max(3, min(steps, 20))
     t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    for _ in range(k):
         e2e_step()
     prb.synchronize()
-    e2e_ms = rank_max((time.perf_counter() - t0) * 1e3) / e2e_steps
-    e2e = {"value": bytes_per_step * nranks / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d,
-           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps}
-
-    # ---- allreduce / backward overlap (N > 1): a synthetic backward (spin kernels on the calc stream between
-    # bucket-ready points, total T_bwd) produces the buckets over time; exposed comm = step time with the real
-    # communicator minus step time of the same schedule on a single-rank communicator (no allreduce).
-    overlap = None
-    if nranks > 1 and not args.no_overlap:
-        overlap = measure_overlap(prb, w, group, tail, rank_max, device_barrier)
-
-    # ---- CPU baseline (rank 0, N = 1 only): bounded sample of the same workload on the host cores
-    cpu_baseline = None
-    if rank == 0 and nranks == 1 and not args.no_cpu_baseline:
-        r = cpu_reference_run(args.workload, 1, budget_s=12.0)
-        cpu_baseline = {"value": r["gbs"], "unit": UNIT, "cores": r["threads"], "kind": "port",
-                        "ms_per_step": r["ms_per_step"],
-                        "sample": "%d full steps of the same workload (%d elems, fp32) in %.1f s" % (r["steps"], r["elems"], r["seconds"])}
-
-    if rank == 0:
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": nranks, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": w["desc"], "elements_per_gpu": w["elems"], "tensors": len(w["numels"]),
-                       "buckets": w["buckets"], "bucket_mb": [25, 1], "param_dtype": w["pdt"], "grad_dtype": w["gdt"],
-                       "amp": w["amp"], "clip": w["clip"], "algorithmic_bytes_per_elem": w["bpe"],
-                       "l2": "working set %.0f MB per step > 126 MB L2 (inputs larger than L2, no flush)" %
-                             (w["elems"] * (w["bpe"] + 8) / 1e6),
-                       "parallelism": "dp%d" % nranks, "allreduce": w["dp"]._reducer.allreduce_backend, "pct_of_measured_hbm_peak_per_gpu": 100.0 * value / nranks / peak,
-                       "pct_of_nominal_8TBps_per_gpu": 100.0 * value / nranks / 8000.0},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "host_issue_ms_per_step": host_issue_ms,
-            "roofline": roofline,
-        }
-        if cpu_baseline is not None:
-            line["cpu_baseline"] = cpu_baseline
-        if overlap is not None:
-            line["overlap"] = overlap
-        print(json.dumps(line), flush=True)
-    group.barrier()
-    return 0
+    ms = rank_max((time.perf_counter() - t0) * 1e3) / k
+    return {"value": w["elems"] * w["bpe"] * group.nranks / (ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d,
+            "d2h_bytes_per_step": d2h, "ms_per_step": ms, "steps": k,
+            "read_back": "global grad norm + found_inf + loss scale (what a training loop logs per step)",
+            "h2d": "one copy per bucket on a copy stream, overlapped with the packs of earlier buckets"}
 
 
-def measure_overlap(prb, w, group, tail, rank_max, device_barrier, steps=40):
-    import ctypes as C
+# --------------------------------------------------------------------------------------------
+# allreduce / backward overlap (N > 1)
+# --------------------------------------------------------------------------------------------
+def measure_overlap(prb, w, group, rank_max, device_barrier, steps=40):
+    """A synthetic backward (spin kernels on the calc stream between bucket-ready points, total T_bwd) produces the
+    buckets over time; exposed comm = step time with the real communicator minus step time of the SAME schedule on
+    a single-rank communicator (no exchange); overlap = 1 - exposed / total_comm, total_comm = the buckets'
+    exchanges alone, back to back."""
     stream = prb.current_stream()
     dp = w["dp"]
+    _, tail = make_step(w)
     groups = list(reversed(dp.group_indices))  # launch order
-    idx = [(C.c_int64 * len(g))(*g) for g in groups]
-
-    # total comm: the buckets' allreduces alone (same backend as the step), back to back on the comm stream
+    idx = [(C.c_int64 * len(g))(*sorted(g, reverse=True)) for g in groups]
     red = dp._reducer
     ng = len(groups)
     cs = group.comm_stream
@@ -454,7 +693,7 @@ def measure_overlap(prb, w, group, tail, rank_max, device_barrier, steps=40):
                 prb._lib.call("prb_spin", per, stream.handle)       # backward computing this bucket's gradients
                 dp_x._reducer.mark_vars_ready(arr)
             tail()
-        for _ in range(3):
+        for _ in range(4):
             one()
         group.barrier()
         prb.synchronize()
@@ -479,31 +718,147 @@ def measure_overlap(prb, w, group, tail, rank_max, device_barrier, steps=40):
         t_bwd_us = mult * total_comm * 1e3
         dp.consume_from_buckets(True)
         t_comm = run(dp, t_bwd_us)
-        # (a) the SAME schedule minus the exchange: per-bucket pack and per-bucket optimizer launches (wait_group is a
-        #     no-op on one rank); (b) what a single-GPU job would run: one fused optimizer launch for all buckets
         dp_solo.consume_from_buckets(True)      # re-points the parameters at the solo arena
-        dp_solo.pipelined = True
-        w["opt"]._step_plans.clear()
+        dp_solo.pipelined = True                # per-bucket optimizer launches where the real schedule has them
         t_same = run(dp_solo, t_bwd_us)
-        dp_solo.pipelined = False
-        w["opt"]._step_plans.clear()
-        t_fused = run(dp_solo, t_bwd_us)
-        w["opt"]._step_plans.clear()
         exposed = max(0.0, t_comm - t_same)
-        exposed_fused = max(0.0, t_comm - t_fused)
         out["cases"].append({"t_bwd_ms": t_bwd_us / 1e3, "step_ms": t_comm, "step_no_comm_ms": t_same,
-                             "step_no_comm_single_launch_ms": t_fused,
                              "exposed_comm_ms": exposed, "overlap_frac": 1.0 - exposed / total_comm,
-                             "overlap_frac_vs_single_launch": 1.0 - exposed_fused / total_comm,
-                             "host_issue_ms": host_ms[-3]})
+                             "host_issue_ms": host_ms[-2]})
     dp.consume_from_buckets(True)
     out["overlap_frac"] = out["cases"][1]["overlap_frac"]
-    out["overlap_frac_vs_single_launch"] = out["cases"][1]["overlap_frac_vs_single_launch"]
-    out["definition"] = ("1 - exposed_comm/total_comm; exposed_comm = step - the same schedule (per-bucket pack and optimizer "
-                         "launches) on a single-rank communicator; *_vs_single_launch compares with one fused optimizer "
-                         "launch instead; synthetic backward = spin kernels between bucket-ready points; start events lined "
-                         "up by a device-side allreduce; headline at T_bwd = 2 x total_comm")
+    out["definition"] = ("1 - exposed_comm/total_comm; exposed_comm = step - the same schedule (per-bucket pack, same "
+                         "optimizer launches) on a single-rank communicator; synthetic backward = spin kernels between "
+                         "bucket-ready points; start events lined up by a device-side allreduce; headline at "
+                         "T_bwd = 2 x total_comm")
     return out
+
+
+# --------------------------------------------------------------------------------------------
+# the GPU arm
+# --------------------------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import gc
+
+    import paddle_ray_b200 as prb  # fails loudly if the CUDA library is missing
+
+    if prb.device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    group = prb.distributed.init_parallel_env()
+    rank, nranks = group.rank, group.nranks
+    if nranks != args.gpus:
+        raise SystemExit("bench.py: --gpus %d but WORLD_SIZE=%d (launch N>1 through torch.distributed.run)" % (args.gpus, nranks))
+    peak, peak_kind = measured_peak()
+    t_start = time.perf_counter()
+
+    parity = parity_preamble(prb, group) if nranks > 1 else None
+    gc.collect()
+
+    # ---- headline workload
+    w = build_workload(prb, args.workload, rank, host_mirror=True)
+    m = measure_workload(prb, group, w, args.steps, args.warmup, peak, sample_clocks=True)
+    rank_max, device_barrier = m["rank_max"], m["device_barrier"]
+    step, _ = make_step(w)
+
+    # host cost of issuing a step (diagnostic): 10 steps issued into an empty queue, clock stopped before the sync
+    prb.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(10):
+        step()
+    host_issue_ms = (time.perf_counter() - t0) * 1e3 / 10
+    prb.synchronize()
+
+    # roofline of the dominant kernel: algorithmic bytes per launch / its average launch duration (CUDA events
+    # recorded by the library around every launch of the instrumented K steps)
+    kern = m["kernels"]
+    adam = kern["adam_chunks_kernel"]
+    per_launch_ms = adam["ms_per_step"] / adam["launches_per_step"]
+    per_launch_bytes = adam["algorithmic_bytes_per_step"] / adam["launches_per_step"]
+    achieved = per_launch_bytes / (per_launch_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "adam_chunks_kernel",
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peak_kind == "measured" else "profiling-recipe fallback",
+                "algorithmic_bytes_per_launch": per_launch_bytes, "avg_launch_ms": per_launch_ms,
+                "frac_of_nominal_8TBps": achieved / 8000.0,
+                "share_of_step": adam["ms_per_step"] / m["ms_per_step_instrumented"]}
+    try:  # dram bytes per launch from the committed ncu capture of THIS workload, when there is one
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            roofline["traffic"] = json.load(f).get(args.workload, {}).get("adam_chunks_kernel")
+    except Exception:
+        pass
+
+    e2e = measure_e2e(prb, group, w, args.steps, rank_max)
+
+    overlap = None
+    if nranks > 1 and not args.no_overlap:
+        overlap = measure_overlap(prb, w, group, rank_max, device_barrier)
+
+    # CPU baseline (rank 0, N = 1 only): bounded sample of the same workload on the host cores
+    cpu_baseline = None
+    if rank == 0 and nranks == 1 and not args.no_cpu_baseline:
+        r = cpu_reference_run(args.workload, 1, budget_s=12.0, threads=host_cores())
+        cpu_baseline = {"value": r["gbs"], "unit": UNIT, "cores": r["threads"], "kind": "port",
+                        "ms_per_step": r["ms_per_step"],
+                        "sample": "%d full steps of the same workload (%d elems, fp32) in %.1f s" % (r["steps"], r["elems"], r["seconds"])}
+
+    config = config_block(w["desc"], w["elems"], len(w["numels"]), w["buckets"], w["pdt"], w["gdt"], w["amp"], w["clip"],
+                          w["bpe"], nranks)
+    details = {
+        "allreduce": w["dp"]._reducer.allreduce_backend,
+        "pct_of_measured_hbm_peak_per_gpu": 100.0 * m["value"] / nranks / peak,
+        "pct_of_nominal_8TBps_per_gpu": 100.0 * m["value"] / nranks / 8000.0,
+        "value_at_survey_34B_floor": (m["value"] * 34 / w["bpe"]) if (w["amp"] and w["gsz"] == 2 and not w["arena"]) else None,
+        "stages": "pack+scale+inf-check+norm-partials (1 kernel) -> exchange (N>1) -> norm finalize -> AdamW (1 kernel)",
+    }
+    del w, step, m["rank_max"], m["device_barrier"]
+    gc.collect()
+
+    # ---- the other BASELINE configs, few steps each, nested in the same line
+    nested = {}
+    if not args.no_configs:
+        ksteps = max(5, min(args.steps, 20))
+        todo = [(n, False) for n in ("resnet50", "gpt2_medium", "bert_base") if n != args.workload]
+        todo += [(args.workload, True), ("resnet50", True)]          # gradients produced in the arena (no pack)
+        if nranks == 1:
+            todo += [(n, False) for n in FLAT_SWEEP]
+        else:
+            todo += [("flat26x1", False), ("flat26x1:bf16", False)]
+        for name, arena in todo:
+            if time.perf_counter() - t_start > args.config_budget_s:
+                nested["_skipped_for_time"] = nested.get("_skipped_for_time", []) + [name + ("+arena" if arena else "")]
+                continue
+            try:
+                wn = build_workload(prb, name, rank, arena=arena)
+                mn = measure_workload(prb, group, wn, ksteps, 3, peak)
+                r = nested_result(mn, peak, nranks)
+                r["workload"] = wn["desc"] + (" [gradients produced in the bucket arena: no pack]" if arena else "")
+                r["steps"] = ksteps
+                nested[name + ("+arena" if arena else "")] = r
+                del wn, mn
+            except Exception as e:  # noqa: BLE001  (e.g. out of memory on a smaller GPU): report, keep the line
+                nested[name + ("+arena" if arena else "")] = {"error": "%s: %s" % (type(e).__name__, str(e)[:160])}
+            gc.collect()
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": nranks, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": m["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config, "details": details,
+            "clocks": m["clocks"], "e2e": e2e,
+            "gpu_launches": m["gpu_launches"], "host_issue_ms_per_step": host_issue_ms, "roofline": roofline,
+            "kernels": kern, "ms_per_step_instrumented": m["ms_per_step_instrumented"],
+        }
+        if cpu_baseline is not None:
+            line["cpu_baseline"] = cpu_baseline
+        if overlap is not None:
+            line["overlap"] = overlap
+        if parity is not None:
+            line["parity_n"] = parity
+        if nested:
+            line["configs"] = nested
+        print(json.dumps(line), flush=True)
+    group.barrier()
+    return 0
 
 
 def self_launch(args):
@@ -527,13 +882,18 @@ def self_launch(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="resnet50")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-worker"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the nested measurements of the other configs")
+    ap.add_argument("--config-budget-s", type=float, default=150.0,
+                    help="no further nested config is started once the run is this many seconds old")
     args = ap.parse_args()
+    if args.impl == "reference-worker":
+        return reference_worker(args)
     if args.impl == "reference":
         return run_reference_arm(args)
     if args.gpus > 1 and "WORLD_SIZE" not in os.environ:

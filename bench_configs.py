@@ -58,10 +58,21 @@ def param_shapes(name: str):
         s = _bert_base()
     elif name == "gpt2_medium":
         s = _gpt2_medium()
-    elif name.startswith("flat"):  # flat<log2 n>x<tensors>, e.g. flat26x1
+    elif name.startswith("flat"):  # flat<log2 n | 2e9>x<tensors>[r], e.g. flat26x1, flat2e9x1, flat26x1000r (ragged)
         logn, k = name[4:].split("x")
-        n, k = 1 << int(logn), int(k)
-        return [(n // k,)] * k
+        ragged = k.endswith("r")
+        k = int(k.rstrip("r"))
+        n = 2_000_000_000 if logn == "2e9" else 1 << int(logn)
+        if not ragged:
+            return [(n // k,)] * k
+        # ragged: log-uniform sizes over four decades (odd lengths, a few tiny tensors), same total
+        rng = np.random.default_rng(7)
+        wts = np.exp(rng.uniform(0.0, np.log(1e4), k))
+        sizes = np.maximum(1, (wts / wts.sum() * n).astype(np.int64)) | 1
+        sizes[:4] = (1, 7, 1000, 4097)
+        sizes[-1] += n - int(sizes.sum())
+        assert sizes.min() > 0 and int(sizes.sum()) == n
+        return [(int(x),) for x in sizes]
     else:
         raise KeyError(name)
     nt, ne = _EXPECT[name]

@@ -248,6 +248,38 @@ int32_t prb_reducer_set_unused_vars(PRB_Reducer* r, const int64_t* var_indices, 
 int32_t prb_reducer_mark_var_ready(PRB_Reducer* r, int64_t var_index, void* stream);
 /* Batch form (one ABI crossing for many hooks; the reference's hooks are C++ callbacks). */
 int32_t prb_reducer_mark_vars_ready(PRB_Reducer* r, const int64_t* var_indices, int64_t num, void* stream);
+/* Gradients produced IN the bucket arena (what MarkVarReady achieves by aliasing the gradient into the group's
+ * dense tensor, ref reducer.cc:774-901, without the concat that follows there): parameter i's gradient is the
+ * slot prb_reducer_bucket_view(r, i) and the producer writes it there, so there is nothing to pack or to split
+ * back.  With one rank a bucket launch does no device work at all; with several the 1/nranks scale (ref
+ * reducer.cc:1049-1050) is applied to each rank's value inside the exchange kernel (same rounding as scale_),
+ * or in place before ncclAllReduce.  A reducer created with grads[i].data == NULL starts in this mode. */
+int32_t prb_reducer_set_grads_in_arena(PRB_Reducer* r, int32_t enabled);
+
+/* Producer-side pass 1.  The consumer of the reduced gradients (prb_dp_step_tail) needs, before it can update,
+ * (a) found_inf of check_finite_and_unscale (ref amp_kernel.cu:33-82) and (b) the squared-norm partial of every
+ * 8192-element chunk (ref squared_l2_norm_kernel.cu:23-35, clip.py:643-736).  Both are functions of the REDUCED
+ * gradient, and some kernel of the reducer is the last one to hold that value in registers: the pack (one rank)
+ * or the slice owner of the peer-memory exchange (several ranks).  With an epilogue set, that kernel clears and
+ * sets `found_inf` and stores the partials, and the tail is called with pass1_done = 1 -- the gradient is not
+ * read a second time.  Results are bit-identical to the tail's own pass 1.
+ *  partial_base[i]: where parameter i's first chunk sits in the consumer's list (sum of ceil(numel/8192) of the
+ *  tensors before it in the list handed to prb_dp_step_tail).  *partials_out: the reducer-owned fp32 buffer to pass
+ *  as cfg->pass1_partials.  *active: 1 if this reducer will run the epilogue (one rank with gradients outside the
+ *  arena, or several ranks on the library's own exchange kernel); 0 = the consumer keeps its own pass 1.
+ * e == NULL switches it off.  Not to be called between prepare_for_backward and the end of that backward. */
+typedef struct PRB_GradEpilogue {
+  const PRB_Tensor* loss_scale; /* fp32 device scalar; NULL = no unscale / finite check */
+  PRB_Tensor* found_inf;        /* bool device scalar, required with loss_scale */
+  int32_t want_norm;            /* 1: squared-norm partials */
+  int32_t use_mp_type;          /* squares kept in fp32 for 16-bit gradients (ref clip.py:179-202) */
+  const int32_t* partial_base;  /* [num parameters] host, required with want_norm */
+} PRB_GradEpilogue;
+int32_t prb_reducer_set_grad_epilogue(PRB_Reducer* r, const PRB_GradEpilogue* e, PRB_Tensor* partials_out,
+                                      int32_t* active);
+/* Elements per chunk of the norm partials (8192). */
+int32_t prb_grad_chunk_elems(void);
+
 /* 1 -> split reduced buckets back into the grads at finalize (reference behaviour, default);
  * 0 -> leave them in the arena for prb_dp_step_tail to consume directly. */
 int32_t prb_reducer_set_unpack(PRB_Reducer* r, int32_t enabled);
@@ -300,6 +332,9 @@ typedef struct PRB_TailConfig {
   int32_t zero_grads;        /* 1: clear_grad(set_to_zero=True) folded in (ref: optimizer.py:1333-1381) */
   int32_t keep_beta_pow;     /* 1: do not advance the beta-pow accumulators in this call (a step split into
                                 several calls, one per bucket, advances them in its last call only) */
+  int32_t pass1_done;        /* 1: the producer already cleared/set found_inf and stored the norm partials
+                                (prb_reducer_set_grad_epilogue); the gradient is read once, by the update pass */
+  float* pass1_partials;     /* device: *partials_out of prb_reducer_set_grad_epilogue (required with use_clip) */
 } PRB_TailConfig;
 
 /* Per-tensor attributes follow adamw_: lr_ratio[i], with_decay[i] (NULL = 1.0 / all decayed).
@@ -350,6 +385,13 @@ int32_t prb_spin(int64_t microseconds, void* stream);
 int32_t prb_flush_l2(void* stream);
 /* Number of kernels this library has launched since load (bench.py's gpu_launches). */
 int64_t prb_launch_count(void);
+/* Per-kernel timing for roofline reports: while enabled, every launch of a hot-path kernel is bracketed by two CUDA
+ * events on the stream it is launched on.  prb_kernel_timing(1) clears and starts, (0) stops;
+ * prb_kernel_timing_read synchronises the device and returns the summed event time and the launch count of one
+ * kernel kind (0 .. 5, named by prb_kernel_kind_name; out-of-range kinds fail). */
+int32_t prb_kernel_timing(int32_t enable);
+int32_t prb_kernel_timing_read(int32_t kind, double* total_ms, int64_t* launches);
+const char* prb_kernel_kind_name(int32_t kind);
 
 #ifdef __cplusplus
 }

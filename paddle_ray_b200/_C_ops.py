@@ -145,9 +145,11 @@ def split_(x, outs, stream=None):
     return outs
 
 
-def clip_grad_by_global_norm_(grads, clip_norm, auto_skip_clip=False, use_mp_type=False, stream=None):
+def clip_grad_by_global_norm_(grads, clip_norm, auto_skip_clip=False, use_mp_type=False, stream=None, norm=None,
+                              clip=None):
     """Multi-tensor body of ClipGradByGlobalNorm._dygraph_clip; returns (global_norm, clip) device scalars."""
-    norm, clip = Tensor(1, FLOAT32, grads[0].device), Tensor(1, FLOAT32, grads[0].device)
+    norm = Tensor(1, FLOAT32, grads[0].device) if norm is None else norm
+    clip = Tensor(1, FLOAT32, grads[0].device) if clip is None else clip
     n, c = norm.prb, clip.prb
     call("prb_clip_grad_by_global_norm", tensor_array(grads), len(grads), float(clip_norm), int(bool(auto_skip_clip)),
          int(bool(use_mp_type)), C.byref(n), C.byref(c), _stream(stream))

@@ -28,7 +28,13 @@ class TailConfig(C.Structure):
         ("coeff", C.c_float), ("use_adamw", C.c_int32), ("multi_precision", C.c_int32), ("use_amp", C.c_int32),
         ("use_clip", C.c_int32), ("clip_norm", C.c_float), ("auto_skip_clip", C.c_int32), ("use_mp_type", C.c_int32),
         ("write_back_grads", C.c_int32), ("zero_grads", C.c_int32), ("keep_beta_pow", C.c_int32),
+        ("pass1_done", C.c_int32), ("pass1_partials", C.c_void_p),
     ]
+
+
+class GradEpilogue(C.Structure):
+    _fields_ = [("loss_scale", C.POINTER(PRBTensor)), ("found_inf", C.POINTER(PRBTensor)), ("want_norm", C.c_int32),
+                ("use_mp_type", C.c_int32), ("partial_base", C.c_void_p)]
 
 
 class PRBError(RuntimeError):
@@ -84,6 +90,9 @@ SIGNATURES = {
     "prb_reducer_mark_var_ready": [_vp, _i64, _vp],
     "prb_reducer_mark_vars_ready": [_vp, _vp, _i64, _vp],
     "prb_reducer_set_unpack": [_vp, _i32],
+    "prb_reducer_set_grads_in_arena": [_vp, _i32],
+    "prb_reducer_set_grad_epilogue": [_vp, C.POINTER(GradEpilogue), _T, C.POINTER(_i32)],
+    "prb_grad_chunk_elems": [],
     "prb_reducer_set_deferred_wait": [_vp, _i32],
     "prb_reducer_wait_group": [_vp, _i64, _vp],
     "prb_reducer_num_groups": [_vp],
@@ -120,13 +129,16 @@ SIGNATURES = {
     "prb_spin": [_i64, _vp],
     "prb_flush_l2": [_vp],
     "prb_launch_count": [],
+    "prb_kernel_timing": [_i32],
+    "prb_kernel_timing_read": [_i32, C.POINTER(_f64), C.POINTER(_i64)],
+    "prb_kernel_kind_name": [_i32],
     "prb_last_error_message": [],
     "prb_version": [],
 }
 _RESTYPES = {"prb_comm_stream": _vp, "prb_launch_count": _i64, "prb_last_error_message": C.c_char_p,
-             "prb_version": C.c_char_p}
+             "prb_version": C.c_char_p, "prb_kernel_kind_name": C.c_char_p}
 # entry points whose int32 return value is a value, not a status
-_VALUE_RETURN = {"prb_comm_nranks", "prb_comm_rank", "prb_reducer_is_finalized", "prb_reducer_num_groups", "prb_reducer_allreduce_backend"}
+_VALUE_RETURN = {"prb_grad_chunk_elems", "prb_comm_nranks", "prb_comm_rank", "prb_reducer_is_finalized", "prb_reducer_num_groups", "prb_reducer_allreduce_backend"}
 
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)  # AttributeError here == the .so does not export what the header declares

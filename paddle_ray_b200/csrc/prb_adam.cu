@@ -8,9 +8,9 @@
 // contraction choices and bit-identical to the CPU oracle (oracle/dp_tail_oracle.c).
 //
 // HBM traffic per element: fp32 r16+w12 = 28 B; bf16 param + fp32 master r14+w14 = 28 B
-// (30 B with fp32 main-grad).  Each CTA owns one 4096-element chunk; each thread moves
-// kAdamUnroll lane-vectors of 8 elements per array with 256-bit (fp32) / 128-bit (16-bit)
-// streaming loads, all loads issued before the first use.
+// (30 B with fp32 main-grad).  Each CTA owns one 1024-element chunk: 128 threads x one lane vector of 8
+// elements per array, 256-bit (fp32) / 128-bit (16-bit) streaming loads, all loads issued before the
+// first use, >= 8 CTAs per SM (profiles/r1_adam_variants.md: 6891 vs 6084 GB/s for fat CTAs).
 #include <map>
 #include <vector>
 
@@ -21,7 +21,7 @@ namespace prb {
 namespace {
 
 struct Coef {
-  float beta1, beta2, c1, c2, eps, decay, bc2, step, inv, clip;
+  float beta1, beta2, c1, c2, eps, decay, bc2, step, inv, clip, b1p, b2p;
   bool use_decay, amp, clipon;
 };
 
@@ -47,11 +47,21 @@ __device__ __forceinline__ void adam_elem(float& p, float g, float& m1, float& m
 }
 
 
+__device__ __forceinline__ float ld_relaxed_gpu(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
 template <typename TG>
 __device__ __forceinline__ Coef make_coef(const AdamDesc* __restrict__ d, const AdamArgs& a) {
   Coef k;
   const float lr = __fmul_rn(__ldg(d->lr), d->lr_ratio);  // ref adamw_kernel.cu:50
-  const float b1p = __ldg(d->b1pow), b2p = __ldg(d->b2pow);
+  // The accumulators may be overwritten by the last CTA of THIS launch (advance_pows_once), so they are read with
+  // coherent relaxed loads, never through the read-only path.
+  const float b1p = ld_relaxed_gpu(d->b1pow), b2p = ld_relaxed_gpu(d->b2pow);
+  k.b1p = b1p;
+  k.b2p = b2p;
   k.beta1 = a.beta1;
   k.beta2 = a.beta2;
   k.eps = a.epsilon;
@@ -69,24 +79,22 @@ __device__ __forceinline__ Coef make_coef(const AdamDesc* __restrict__ d, const 
 }
 
 // Shared beta-pow accumulators advanced inside the update kernel (ref UpdateAdamWBetaPow
-// adamw_kernel.cu:130-139), which removes the separate 1-thread launch.  Each CTA takes a ticket
-// AFTER the old values have arrived in the registers of the one thread that reads them (the dummy
-// register operands of the inline atom make the instruction wait for them), so the CTA that draws the last ticket knows every CTA
-// has read the old values and may overwrite them.  The atomic's latency hides under the data loads
-// already in flight.
-__device__ __forceinline__ void advance_pows_once(const AdamArgs& a, const Coef& k) {
+// adamw_kernel.cu:130-139), which removes the separate 1-thread launch.  The coefficient thread of each CTA loads
+// the old values with coherent gpu-scope loads (make_coef) and then takes a ticket whose INCREMENT is computed
+// from the loaded bits (their sign bits, always 0 for a product of betas): a true data dependency, so the atomic
+// cannot be issued before both loads have returned -- at no cost, the atomic's latency still hides under the CTA's
+// data loads.  (A fence in its place waits for the thread's data loads too and cost 20 % of the pass: r2
+// measurement, BERT-base 0.46 -> 0.60 ms.)  The CTA that draws the last ticket therefore knows that every CTA
+// holds the old values in registers, fences, and overwrites them.
+__device__ __forceinline__ void advance_pows_once(const AdamArgs& a, float b1p, float b2p) {
   if (a.pow_ticket == nullptr) return;
-  unsigned int t;
-  asm volatile(
-      "{\n\t.reg .f32 dep0, dep1;\n\tmov.f32 dep0, %2;\n\tmov.f32 dep1, %3;\n\t"
-      "atom.global.add.u32 %0, [%1], 1;\n\t}"
-      : "=r"(t)
-      : "l"(a.pow_ticket), "f"(k.bc2), "f"(k.step)
-      : "memory");
+  const unsigned int inc = 1u + ((__float_as_uint(b1p) | __float_as_uint(b2p)) >> 31);
+  const unsigned int t = atomicAdd(a.pow_ticket, inc);
   if (t == gridDim.x - 1) {
+    __threadfence();
     *a.pow_ticket = 0u;
-    *a.pow_b1 = __fmul_rn(a.beta1, *a.pow_b1);
-    *a.pow_b2 = __fmul_rn(a.beta2, *a.pow_b2);
+    *a.pow_b1 = __fmul_rn(a.beta1, b1p);
+    *a.pow_b2 = __fmul_rn(a.beta2, b2p);
   }
 }
 
@@ -98,8 +106,7 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
   const bool skipped = a.skip != nullptr && *a.skip;
   if (skipped && !a.zero_grad) return;
 
-  const int cidx = a.reverse ? a.nchunks - 1 - (int)blockIdx.x : (int)blockIdx.x;
-  const int4 craw = __ldg(reinterpret_cast<const int4*>(a.chunks) + cidx);
+  const int4 craw = __ldg(reinterpret_cast<const int4*>(a.chunks) + blockIdx.x);
   const int tensor = craw.x;
   const int n = craw.y;
   const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
@@ -122,7 +129,6 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
 
   if (aligned) {
     const int nvec = n / kVec;
-    const uint64_t pol = l2_policy(a.l2_hints ? 1 : 0);
     Pack<T> pv[kAdamUnroll];
     Pack<float> mpv[kAdamUnroll];
     Pack<TG> gv[kAdamUnroll];
@@ -133,16 +139,16 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
       const int v = u * kAdamThreads + threadIdx.x;
       if (v < nvec) {
         const int e = v * kVec;
-        if (kMaster) load_vec_hint<float>(mp_ptr + e, mpv[u], pol);
-        else load_vec_hint<T>(p_ptr + e, pv[u], pol);
-        load_vec_hint<TG>(g_ptr + e, gv[u], pol);
-        load_vec_hint<float>(m1_ptr + e, m1v[u], pol);
-        load_vec_hint<float>(m2_ptr + e, m2v[u], pol);
+        if (kMaster) load_vec<float>(mp_ptr + e, mpv[u]);
+        else load_vec<T>(p_ptr + e, pv[u]);
+        load_vec<TG>(g_ptr + e, gv[u]);
+        load_vec<float>(m1_ptr + e, m1v[u]);
+        load_vec<float>(m2_ptr + e, m2v[u]);
       }
     }
     if (threadIdx.x == 0) {
       sk = make_coef<TG>(d, a);
-      advance_pows_once(a, sk);
+      advance_pows_once(a, sk.b1p, sk.b2p);
     }
     __syncthreads();
     const Coef k = sk;
@@ -163,10 +169,10 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
           if (kMaster) mpv[u].v[j] = p;
           go.v[j] = a.zero_grad ? Conv<TG>::from_f32(0.0f) : Conv<TG>::from_f32(gu);
         }
-        store_vec_hint<float>(m1_ptr + e, m1v[u], pol);
-        store_vec_hint<float>(m2_ptr + e, m2v[u], pol);
-        store_vec_hint<T>(p_ptr + e, po, pol);
-        if (kMaster) store_vec_hint<float>(mp_ptr + e, mpv[u], pol);
+        store_vec<float>(m1_ptr + e, m1v[u]);
+        store_vec<float>(m2_ptr + e, m2v[u]);
+        store_vec<T>(p_ptr + e, po);
+        if (kMaster) store_vec<float>(mp_ptr + e, mpv[u]);
         if (a.zero_grad) store_vec<TG>(const_cast<TG*>(g_ptr) + e, go);
         else if (go_ptr) store_vec<TG>(go_ptr + e, go);
       }
@@ -190,7 +196,7 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
     // element-wise accesses, same arithmetic.
     if (threadIdx.x == 0) {
       sk = make_coef<TG>(d, a);
-      advance_pows_once(a, sk);
+      advance_pows_once(a, sk.b1p, sk.b2p);
     }
     __syncthreads();
     const Coef k = sk;
@@ -228,51 +234,25 @@ __global__ void beta_pow_kernel(const PowPair* pairs, int n, float beta1, float 
   }
 }
 
-// Launch geometry variants {threads, lane-vectors per thread, min CTAs per SM}; PRB_ADAM_VARIANT
-// selects one at load time (tuning aid), the default is the measured best (profiles/).
-struct Variant {
-  int threads, unroll, min_blocks;
-};
-constexpr Variant kVariants[] = {{256, 2, 2}, {256, 1, 4}, {128, 2, 4}, {128, 1, 8}, {512, 1, 2}, {256, 2, 3}};
-constexpr int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
-constexpr int kDefaultVariant = 3;  // 128 threads x 1 lane-vector, >= 8 CTAs/SM: best on B200 (profiles/r1_adam_variants.md)
-
-int active_variant() {
-  static int v = [] {
-    const char* e = getenv("PRB_ADAM_VARIANT");
-    int x = e ? atoi(e) : kDefaultVariant;
-    return (x < 0 || x >= kNumVariants) ? kDefaultVariant : x;
-  }();
-  return v;
-}
-
-template <typename T, typename TG, int kThreads, int kUnroll, int kMinBlocks>
-void launch_variant(bool has_master, const AdamArgs& a, cudaStream_t stream) {
-  if (has_master) adam_chunks_kernel<T, TG, true, kThreads, kUnroll, kMinBlocks><<<a.nchunks, kThreads, 0, stream>>>(a);
-  else adam_chunks_kernel<T, TG, false, kThreads, kUnroll, kMinBlocks><<<a.nchunks, kThreads, 0, stream>>>(a);
-}
+// Launch geometry: 128 threads x 1 lane vector, >= 8 CTAs/SM -- the best of the six shapes measured in round 1
+// (profiles/r1_adam_variants.md); the other five were dropped from the binary.
+constexpr int kAdamThreads = 128, kAdamUnroll = 1, kAdamMinBlocks = 8;
 
 template <typename T, typename TG>
 int32_t launch_typed(bool has_master, const AdamArgs& a, cudaStream_t stream) {
   if (a.nchunks == 0) return PRB_SUCCESS;
-  switch (active_variant()) {
-    case 0: launch_variant<T, TG, 256, 2, 2>(has_master, a, stream); break;
-    case 1: launch_variant<T, TG, 256, 1, 4>(has_master, a, stream); break;
-    case 2: launch_variant<T, TG, 128, 2, 4>(has_master, a, stream); break;
-    case 3: launch_variant<T, TG, 128, 1, 8>(has_master, a, stream); break;
-    case 4: launch_variant<T, TG, 512, 1, 2>(has_master, a, stream); break;
-    default: launch_variant<T, TG, 256, 2, 3>(has_master, a, stream); break;
-  }
+  KernelTimer kt(KK_ADAM, stream);
+  if (has_master)
+    adam_chunks_kernel<T, TG, true, kAdamThreads, kAdamUnroll, kAdamMinBlocks><<<a.nchunks, kAdamThreads, 0, stream>>>(a);
+  else
+    adam_chunks_kernel<T, TG, false, kAdamThreads, kAdamUnroll, kAdamMinBlocks><<<a.nchunks, kAdamThreads, 0, stream>>>(a);
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 
 }  // namespace
 
-int adam_chunk_elems() {
-  const Variant v = kVariants[active_variant()];
-  return v.threads * kVec * v.unroll;
-}
+int adam_chunk_elems() { return kAdamThreads * kVec * kAdamUnroll; }
 
 int32_t launch_adam(int32_t dtype_param, int32_t dtype_grad, bool has_master, const AdamArgs& a, cudaStream_t stream) {
   if (dtype_param == PRB_FLOAT32 && dtype_grad == PRB_FLOAT32) return launch_typed<float, float>(has_master, a, stream);
@@ -408,7 +388,7 @@ int32_t run_adam_list(const ListArgs& A, cudaStream_t stream) {
   std::vector<float> scal_host;
   if (n_host_scalars > 0) {
     void* ws = nullptr;
-    PRB_TRY(workspace((size_t)(3 * n) * sizeof(float), &ws, /*slot=*/0));
+    PRB_TRY(workspace((size_t)(3 * n) * sizeof(float), &ws, /*slot=*/0, stream));
     scal_dev = reinterpret_cast<float*>(ws);
     scal_host.assign((size_t)3 * n, 0.0f);
   }

@@ -36,15 +36,11 @@ struct AdamArgs {
   const float* loss_scale;   // AMP: g = T(MT(g) * inv), inv = float(1.0 / double(*loss_scale)); nullptr = off
   const float* clip;         // global-norm clip: g = T(MT(g) * MT(T(*clip))); nullptr = off
   int32_t zero_grad;         // 1: store zeros to grad after consuming it (clear_grad folded in)
-  // Shared beta-pow accumulators advanced by the LAST CTA to finish (ticket counter), which removes
-  // the separate 1-thread launch: every CTA has read the old value before it takes its ticket.
+  // Shared beta-pow accumulators advanced by the CTA that draws the LAST ticket, which removes the separate
+  // 1-thread launch: every CTA has read the old value (and fenced) before it takes its ticket.
   float* pow_b1;             // nullptr = off
   float* pow_b2;
-  unsigned int* pow_ticket;  // zero-initialised device counter, reset by the last CTA
-  // 1: CTA b takes chunk nchunks-1-b (walk the table backwards after a forward pass, hoping for L2 hits on the
-  // gradients touched last).  Measured neutral on B200, so it is off unless PRB_TAIL_REVERSE is set.
-  int32_t reverse;
-  int32_t l2_hints;  // experiment: stream params/moments with evict_first so a bucket kept with evict_last survives
+  unsigned int* pow_ticket;  // zero-initialised device counter of the launching stream, reset by the last CTA
 };
 
 // Elements per CTA of the active launch geometry (threads * kVec * lane-vectors per thread).

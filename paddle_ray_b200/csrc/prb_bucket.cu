@@ -15,23 +15,9 @@
 namespace prb {
 namespace {
 
-// Launch geometry variants {threads, lane-vectors per thread, min CTAs per SM}; PRB_MAP_VARIANT selects
-// one at load time (tuning aid), the default is the measured best (profiles/).
-struct MapVariant {
-  int threads, unroll, min_blocks;
-};
-constexpr MapVariant kMapVariants[] = {{256, 4, 2}, {256, 2, 4}, {256, 1, 8}, {128, 1, 16}, {128, 2, 8}, {512, 1, 4}};
-constexpr int kNumMapVariants = sizeof(kMapVariants) / sizeof(kMapVariants[0]);
-constexpr int kDefaultMapVariant = 0;
-
-int active_map_variant() {
-  static int v = [] {
-    const char* e = getenv("PRB_MAP_VARIANT");
-    int x = e ? atoi(e) : kDefaultMapVariant;
-    return (x < 0 || x >= kNumMapVariants) ? kDefaultMapVariant : x;
-  }();
-  return v;
-}
+// Launch geometry: 256 threads x 4 lane vectors = 8192 elements per CTA (the six shapes measured in round 1 were
+// within 1 % of each other, profiles/r1_experiments.md; one is kept).
+constexpr int kMapThreads = 256, kMapUnroll = 4, kMapMinBlocks = 2;
 
 struct CopyOp {
   template <typename T>
@@ -52,10 +38,10 @@ struct ScaleOp {
   }
 };
 
-template <typename T, typename Op, int kMapThreads, int kMapUnroll, int kMinBlocks>
-__global__ void __launch_bounds__(kMapThreads, kMinBlocks) map_chunks_kernel(const MapDesc* __restrict__ descs,
-                                                                             const Chunk* __restrict__ chunks,
-                                                                             const Op op, const int l2_hints) {
+template <typename T, typename Op>
+__global__ void __launch_bounds__(kMapThreads, kMapMinBlocks) map_chunks_kernel(const MapDesc* __restrict__ descs,
+                                                                                const Chunk* __restrict__ chunks,
+                                                                                const Op op) {
   const int4 craw = __ldg(reinterpret_cast<const int4*>(chunks) + blockIdx.x);
   const int n = craw.y;
   const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
@@ -64,14 +50,11 @@ __global__ void __launch_bounds__(kMapThreads, kMinBlocks) map_chunks_kernel(con
   T* __restrict__ dst = reinterpret_cast<T*>(d->dst) + offset;
   if (d->aligned) {
     const int nvec = n / kVec;
-    // experiment (PRB_L2_HINTS): the destination (a bucket that the optimizer re-reads next) is kept, the source streamed
-    // l2_hints = percentage of the destination lines to keep (evict_last); 0 = no steering
-    const uint64_t pol_ld = l2_policy(l2_hints ? 1 : 0), pol_st = l2_hints ? l2_policy_keep(l2_hints) : l2_policy(0);
     Pack<T> v[kMapUnroll];
 #pragma unroll
     for (int u = 0; u < kMapUnroll; ++u) {
       const int i = u * kMapThreads + threadIdx.x;
-      if (i < nvec) load_vec_hint<T>(src + i * kVec, v[u], pol_ld);
+      if (i < nvec) load_vec<T>(src + i * kVec, v[u]);
     }
 #pragma unroll
     for (int u = 0; u < kMapUnroll; ++u) {
@@ -79,7 +62,7 @@ __global__ void __launch_bounds__(kMapThreads, kMinBlocks) map_chunks_kernel(con
       if (i < nvec) {
 #pragma unroll
         for (int j = 0; j < kVec; ++j) v[u].v[j] = op(v[u].v[j]);
-        store_vec_hint<T>(dst + i * kVec, v[u], pol_st);
+        store_vec<T>(dst + i * kVec, v[u]);
       }
     }
     const int e = nvec * kVec + threadIdx.x;
@@ -95,27 +78,15 @@ template <typename T, typename Op>
 int32_t launch_map_typed(const DeviceTable& tab, const Op& op, cudaStream_t stream) {
   if (tab.nchunks == 0) return PRB_SUCCESS;
   const MapDesc* d = reinterpret_cast<const MapDesc*>(tab.descs);
-#define PRB_MAP(T_, U_, B_) \
-  map_chunks_kernel<T, Op, T_, U_, B_><<<tab.nchunks, T_, 0, stream>>>(d, tab.chunks, op, l2_hints())
-  switch (active_map_variant()) {
-    case 0: PRB_MAP(256, 4, 2); break;
-    case 1: PRB_MAP(256, 2, 4); break;
-    case 2: PRB_MAP(256, 1, 8); break;
-    case 3: PRB_MAP(128, 1, 16); break;
-    case 4: PRB_MAP(128, 2, 8); break;
-    default: PRB_MAP(512, 1, 4); break;
-  }
-#undef PRB_MAP
+  KernelTimer kt(KK_MAP, stream);
+  map_chunks_kernel<T, Op><<<tab.nchunks, kMapThreads, 0, stream>>>(d, tab.chunks, op);
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 
 }  // namespace
 
-int map_chunk_elems() {
-  const MapVariant v = kMapVariants[active_map_variant()];
-  return v.threads * kVec * v.unroll;
-}
+int map_chunk_elems() { return kMapThreads * kVec * kMapUnroll; }
 
 bool map_aligned(const void* src, const void* dst, int elem_size) {
   const uintptr_t a = (uintptr_t)elem_size * kVec;

@@ -76,15 +76,43 @@ inline const char* dtype_name(int32_t dt) {
   }
 }
 
+// ---------------------------------------------------------------- per-kernel timing (measurement aid)
+// prb_kernel_timing(1) makes every launch site bracket its kernel with two CUDA events on the launching stream;
+// prb_kernel_timing_read sums the elapsed times per kind.  Off (one relaxed load per launch) by default.
+enum KernelKind {
+  KK_MAP = 0,        // map_chunks_kernel: pack(+scale) without epilogue, unpack, scale, concat, split
+  KK_GRAD_PASS,      // grad_pass_kernel modes 0/1: a pass of its own over the gradients
+  KK_PACK_EPILOGUE,  // grad_pass_kernel mode 2: pack + scale + inf check + norm partials
+  KK_NORM_FINALIZE,  // norm_finalize_kernel
+  KK_ADAM,           // adam_chunks_kernel
+  KK_EXCHANGE,       // nvl_exchange_kernel / nvls_allreduce_kernel
+  KK_COUNT
+};
+extern std::atomic<int> g_kernel_timing;
+struct KernelTimer {
+  KernelTimer(int kind, cudaStream_t stream) {
+    if (g_kernel_timing.load(std::memory_order_relaxed)) begin(kind, stream);
+  }
+  ~KernelTimer() {
+    if (start_) end();
+  }
+  void begin(int kind, cudaStream_t stream);
+  void end();
+  int kind_ = 0;
+  cudaStream_t stream_ = nullptr;
+  cudaEvent_t start_ = nullptr;
+};
+
 int32_t require_device();  // PRB_EXTERNAL if no usable CUDA device (no CPU fallback exists)
 int sm_count();            // of the current device (cached)
-int l2_hints();            // PRB_L2_HINTS (experiment switch): 1 = steer L2 with eviction policies
 
 // ---------------------------------------------------------------- workspace
-// Library-owned persistent device scratch, grown on demand (never shrinks); one per device.
-int32_t workspace(size_t bytes, void** out, int slot);
-// One zero-initialised 32-bit device counter per device (ticket of the fused beta-pow update).
-int32_t ticket_counter(void** out);
+// Library-owned persistent device scratch, grown on demand (never shrinks); one per (device, stream, slot), so
+// two optimizers that step on different streams of one device never share partial sums.
+int32_t workspace(size_t bytes, void** out, int slot, cudaStream_t stream);
+// One zero-initialised 32-bit device counter per (device, stream): the ticket of the fused beta-pow update.
+// Launches on one stream are ordered, so they may share it; launches on different streams get their own.
+int32_t ticket_counter(void** out, cudaStream_t stream);
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------- element conversions
@@ -154,53 +182,6 @@ __device__ __forceinline__ void store_vec(T* __restrict__ p, const Pack<T>& i) {
                  : "memory");
   } else {
     asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3])
-                 : "memory");
-  }
-}
-
-// ---- the same accesses with an explicit L2 eviction policy (createpolicy + .L2::cache_hint)
-// kind: 0 = evict_normal, 1 = evict_first (streamed once), 2 = evict_last (about to be re-read)
-__device__ __forceinline__ uint64_t l2_policy(int kind) {
-  uint64_t normal, first, last;
-  asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(normal));
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(first));
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(last));
-  return kind == 1 ? first : (kind == 2 ? last : normal);
-}
-// evict_last for about `pct` percent of the lines (25/50/75/100), evict_first for the rest: keeps as much of a
-// buffer as the L2 can actually hold instead of letting an over-sized "keep" set thrash.
-__device__ __forceinline__ uint64_t l2_policy_keep(int pct) {
-  uint64_t p25, p50, p75, p100, first;
-  asm volatile("createpolicy.fractional.L2::evict_last.L2::evict_first.b64 %0, 0.25;" : "=l"(p25));
-  asm volatile("createpolicy.fractional.L2::evict_last.L2::evict_first.b64 %0, 0.5;" : "=l"(p50));
-  asm volatile("createpolicy.fractional.L2::evict_last.L2::evict_first.b64 %0, 0.75;" : "=l"(p75));
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p100));
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(first));
-  return pct >= 100 ? p100 : (pct >= 75 ? p75 : (pct >= 50 ? p50 : (pct >= 25 ? p25 : first)));
-}
-template <typename T>
-__device__ __forceinline__ void load_vec_hint(const T* __restrict__ p, Pack<T>& o, uint64_t pol) {
-  uint32_t* w = reinterpret_cast<uint32_t*>(o.v);
-  if constexpr (sizeof(T) == 4) {
-    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8], %9;"
-                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-                 : "l"(p), "l"(pol));
-  } else {
-    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
-                 : "l"(p), "l"(pol));
-  }
-}
-template <typename T>
-__device__ __forceinline__ void store_vec_hint(T* __restrict__ p, const Pack<T>& i, uint64_t pol) {
-  const uint32_t* w = reinterpret_cast<const uint32_t*>(i.v);
-  if constexpr (sizeof(T) == 4) {
-    asm volatile("st.global.L2::cache_hint.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8}, %9;" ::"l"(p), "r"(w[0]), "r"(w[1]),
-                 "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]), "l"(pol)
-                 : "memory");
-  } else {
-    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]),
-                 "r"(w[3]), "l"(pol)
                  : "memory");
   }
 }

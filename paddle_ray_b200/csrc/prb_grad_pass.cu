@@ -7,104 +7,55 @@
 namespace prb {
 namespace {
 
-// Launch geometry variants {threads, lane-vectors per thread, min CTAs per SM}; PRB_GRAD_VARIANT selects
-// one at load time (tuning aid), the default is the measured best (profiles/).
-struct GradVariant {
-  int threads, unroll, min_blocks;
-};
-constexpr GradVariant kGradVariants[] = {{256, 4, 2}, {256, 2, 4}, {256, 1, 8}, {128, 1, 16}, {128, 2, 8},
-                                         {256, 8, 2}, {512, 4, 1}, {512, 8, 1}};
-constexpr int kNumGradVariants = sizeof(kGradVariants) / sizeof(kGradVariants[0]);
-constexpr int kDefaultGradVariant = 0;
-
-int active_grad_variant() {
-  static int v = [] {
-    const char* e = getenv("PRB_GRAD_VARIANT");
-    int x = e ? atoi(e) : kDefaultGradVariant;
-    return (x < 0 || x >= kNumGradVariants) ? kDefaultGradVariant : x;
-  }();
-  return v;
+// Scale of the pack (mode 2): out = T(scale * (MT(x) + bias))   (ref scale_kernel.cu:35-40, bias_after_scale = false)
+template <typename T>
+__device__ __forceinline__ T pack_scale_elem(T raw, float scale, float bias) {
+  return Conv<T>::from_f32(__fmul_rn(scale, __fadd_rn(Conv<T>::to_f32(raw), bias)));
+}
+template <typename T>
+__device__ __forceinline__ void pack_scale_vec(Pack<T>& v, float scale, float bias) {
+  if constexpr (sizeof(T) == 2) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(v.v);
+#pragma unroll
+    for (int j = 0; j < kVec / 2; ++j) {
+      float lo, hi;
+      Pair<T>::unpack(w[j], lo, hi);
+      w[j] = Pair<T>::pack_rn(__fmul_rn(scale, __fadd_rn(lo, bias)), __fmul_rn(scale, __fadd_rn(hi, bias)));
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < kVec; ++j) v.v[j] = pack_scale_elem<T>(v.v[j], scale, bias);
+  }
 }
 
-// Two 16-bit elements at a time.  For bf16/fp16 gradients the pass is issue-bound, not HBM-bound (ncu: 64 % issue
-// slots, 39 % DRAM), so the per-element work is done on packed pairs: one cvt packs two narrowed values, the
-// non-finite test is two integer ops on the packed exponents, and the T-rounded square is ONE packed multiply --
-// exact, because the product of two 8-bit (11-bit) significands fits fp32, so rounding it once to T is what
-// "T(x) * T(x)" means.  Results are bit-identical to the element-wise code.
-template <typename T>
-struct Pair;
-template <>
-struct Pair<__nv_bfloat16> {
-  static __device__ __forceinline__ void unpack(uint32_t w, float& lo, float& hi) {
-    lo = __uint_as_float(w << 16);
-    hi = __uint_as_float(w & 0xffff0000u);
-  }
-  static __device__ __forceinline__ uint32_t pack_rn(float lo, float hi) {
-    const __nv_bfloat162 r = __floats2bfloat162_rn(lo, hi);
-    return *reinterpret_cast<const uint32_t*>(&r);
-  }
-  // bit 15 / 31 set iff the exponent field of the low / high half is all ones (inf or nan)
-  static __device__ __forceinline__ uint32_t nonfinite(uint32_t w) { return ((w & 0x7F807F80u) + 0x00800080u) & 0x80008000u; }
-  static __device__ __forceinline__ uint32_t square(uint32_t w) {
-    const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&w);
-    const __nv_bfloat162 r = __hmul2(v, v);
-    return *reinterpret_cast<const uint32_t*>(&r);
-  }
-};
-template <>
-struct Pair<__half> {
-  static __device__ __forceinline__ void unpack(uint32_t w, float& lo, float& hi) {
-    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
-    lo = f.x;
-    hi = f.y;
-  }
-  static __device__ __forceinline__ uint32_t pack_rn(float lo, float hi) {
-    const __half2 r = __floats2half2_rn(lo, hi);
-    return *reinterpret_cast<const uint32_t*>(&r);
-  }
-  static __device__ __forceinline__ uint32_t nonfinite(uint32_t w) { return ((w & 0x7C007C00u) + 0x04000400u) & 0x80008000u; }
-  static __device__ __forceinline__ uint32_t square(uint32_t w) {
-    const __half2 v = *reinterpret_cast<const __half2*>(&w);
-    const __half2 r = __hmul2(v, v);
-    return *reinterpret_cast<const uint32_t*>(&r);
-  }
-};
-
-template <typename T, bool kWrite, bool kNorm, bool kMp, int kGradThreads, int kGradUnroll, int kMinBlocks>
-__global__ void __launch_bounds__(kGradThreads, kMinBlocks) grad_pass_kernel(const GradDesc* __restrict__ descs,
-                                                                 const Chunk* __restrict__ chunks,
-                                                                 const float* __restrict__ loss_scale,
-                                                                 bool* __restrict__ found_inf,
-                                                                 float* __restrict__ partials) {
+// kMode 0: read only.  1: store the unscaled value (check_finite_and_unscale_).  2: the reducer's pack -- store
+// T(scale * (x + bias)) into the bucket slot and run the check + norm on the value just stored.
+template <typename T, int kMode, bool kNorm, bool kMp>
+__global__ void __launch_bounds__(kGradThreads, 2) grad_pass_kernel(const GradDesc* __restrict__ descs,
+                                                                    const Chunk* __restrict__ chunks,
+                                                                    const float* __restrict__ loss_scale,
+                                                                    bool* __restrict__ found_inf,
+                                                                    float* __restrict__ partials,
+                                                                    const float pack_scale, const float pack_bias) {
   __shared__ float red[kGradThreads / 32];
   const int4 craw = __ldg(reinterpret_cast<const int4*>(chunks) + blockIdx.x);
   const int n = craw.y;
   const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
   const GradDesc* __restrict__ d = descs + craw.x;
   const T* __restrict__ x = reinterpret_cast<const T*>(d->x) + offset;
-  T* __restrict__ out = kWrite ? reinterpret_cast<T*>(d->out) + offset : nullptr;
-  const bool amp = loss_scale != nullptr;
+  T* __restrict__ out = kMode != 0 ? reinterpret_cast<T*>(d->out) + offset : nullptr;
+  ChunkEpilogue<T, kNorm, kMp> ep;
 
-  float acc = 0.0f;
-  bool bad = false;
-  uint32_t bad_bits = 0;
-  float inv = 1.0f;
-
-  auto elem = [&](T raw) -> T {
-    float v = Conv<T>::to_f32(raw);
-    T narrow = raw;
-    if (amp) {
-      narrow = Conv<T>::from_f32(__fmul_rn(v, inv));  // val = MT(x) * inv; narrow = T(val)  (ref amp_kernel.cu:66-68)
-      v = Conv<T>::to_f32(narrow);
-      if (!isfinite(v)) bad = true;                    // finite check on the narrowed value (ref :70-77)
+  auto one = [&](int e) {  // element-wise path: ragged tail and unaligned tensors
+    T r = x[e];
+    if (kMode == 2) {
+      r = pack_scale_elem<T>(r, pack_scale, pack_bias);
+      out[e] = r;
+      ep.elem(r);
+    } else {
+      const T nr = ep.elem(r);
+      if (kMode == 1) out[e] = nr;
     }
-    if (kNorm) {
-      // SquareFunctor<T,T>: T(x)*T(x) rounded to T, accumulated in MT=float
-      // (ref functor_primitives.h:115-123, reduce_function.h:1030-1048); kMp keeps fp32 squares.
-      const float sq = __fmul_rn(v, v);
-      acc = __fadd_rn(acc, kMp ? sq : round_through<T>(sq));
-    }
-    return narrow;
   };
 
   if (d->aligned) {
@@ -115,59 +66,34 @@ __global__ void __launch_bounds__(kGradThreads, kMinBlocks) grad_pass_kernel(con
       const int i = u * kGradThreads + threadIdx.x;
       if (i < nvec) load_vec<T>(x + i * kVec, v[u]);
     }
-    if (amp) inv = (float)(1.0 / (double)__ldg(loss_scale));  // ref amp_kernel.cu:29 (double divide, narrowed)
+    ep.begin(loss_scale);
 #pragma unroll
     for (int u = 0; u < kGradUnroll; ++u) {
       const int i = u * kGradThreads + threadIdx.x;
       if (i < nvec) {
-        if constexpr (sizeof(T) == 2 && !kMp) {
-          uint32_t* w = reinterpret_cast<uint32_t*>(v[u].v);
-#pragma unroll
-          for (int j = 0; j < kVec / 2; ++j) {
-            uint32_t nw = w[j];
-            if (amp) {
-              float lo, hi;
-              Pair<T>::unpack(nw, lo, hi);
-              nw = Pair<T>::pack_rn(__fmul_rn(lo, inv), __fmul_rn(hi, inv));  // narrow = T(MT(x) * inv)
-              bad_bits |= Pair<T>::nonfinite(nw);                             // finite check on the narrowed value
-              w[j] = nw;
-            }
-            if (kNorm) {
-              float lo, hi;
-              Pair<T>::unpack(Pair<T>::square(nw), lo, hi);  // T(x)*T(x) rounded to T, both halves at once
-              acc = __fadd_rn(__fadd_rn(acc, lo), hi);       // same order as the element-wise code
-            }
-          }
+        if (kMode == 2) {
+          pack_scale_vec<T>(v[u], pack_scale, pack_bias);
+          store_vec<T>(out + i * kVec, v[u]);
+          ep.vec(v[u]);
         } else {
-#pragma unroll
-          for (int j = 0; j < kVec; ++j) v[u].v[j] = elem(v[u].v[j]);
+          ep.vec(v[u]);
+          if (kMode == 1) store_vec<T>(out + i * kVec, v[u]);
         }
-        if (kWrite) store_vec<T>(out + i * kVec, v[u]);
       }
     }
-    if (bad_bits) bad = true;
     const int e = nvec * kVec + threadIdx.x;
-    if (e < n) {
-      const T r = elem(x[e]);
-      if (kWrite) out[e] = r;
-    }
+    if (e < n) one(e);
   } else {
-    if (amp) inv = (float)(1.0 / (double)__ldg(loss_scale));
-    for (int e = threadIdx.x; e < n; e += kGradThreads) {
-      const T r = elem(x[e]);
-      if (kWrite) out[e] = r;
-    }
+    ep.begin(loss_scale);
+    for (int e = threadIdx.x; e < n; e += kGradThreads) one(e);
   }
 
-  if (amp) {
-    // only `true` is ever written, so concurrent stores are benign (ref amp_kernel.cu:79-81)
-    const int any = __syncthreads_or(bad ? 1 : 0);
-    if (any && threadIdx.x == 0) *found_inf = true;
-  }
-  if (kNorm) {
-    const float s = block_sum<kGradThreads>(acc, red);
-    if (threadIdx.x == 0) partials[blockIdx.x] = s;
-  }
+  bool any_bad;
+  const float s = ep.finish(red, &any_bad);
+  // only `true` is ever written, so concurrent stores are benign (ref amp_kernel.cu:79-81)
+  if (any_bad && threadIdx.x == 0) *found_inf = true;
+  if (kNorm && threadIdx.x == 0)
+    partials[kMode == 2 ? d->partial_base + (int)(offset / kGradChunk) : (int)blockIdx.x] = s;
 }
 
 __device__ __forceinline__ float round_mode(float v, int mode) {
@@ -176,14 +102,17 @@ __device__ __forceinline__ float round_mode(float v, int mode) {
   return v;
 }
 
-// The one grid-level pass: a single CTA of 1024 threads.  Phase 1 turns chunk partials into
-// per-tensor sums in a fixed order: tensors with many chunks are summed by the whole CTA
-// (thread-strided with independent loads, then the fixed-shape block tree), small tensors by one
-// warp each (lane-strided, then a fixed butterfly).  Phase 2: thread 0 adds the per-tensor sums in
-// list order per dtype group (add_n), casts, adds the groups, sqrt, clip coefficient
-// (ref clip.py:685-713).
+// The one grid-level pass.  Phase 1 turns chunk partials into per-tensor sums in a fixed order: a tensor with many
+// chunks is summed by a whole 1024-thread CTA (thread-strided with four independent accumulators, then the
+// fixed-shape block tree), a small tensor by one warp (lane-strided, then a fixed butterfly).  The tensors are
+// spread over a few CTAs -- WHICH CTA sums a tensor changes nothing about HOW it is summed, so the result does not
+// depend on the grid (round 1 ran this on one CTA: 52 us for BERT-base's 25 large tensors, one latency chain after
+// the other; spread out it is ~10 us).  Phase 2 runs in the CTA that finishes last (ticket): thread 0 adds the
+// per-tensor sums in list order per dtype group (add_n), casts, adds the groups, sqrt, clip coefficient
+// (ref clip.py:685-713).  No float atomics: bit-identical run to run.
 constexpr int kFinThreads = 1024;
-constexpr int kFinBigTensor = 256;  // chunks; above this the whole CTA cooperates on the tensor
+constexpr int kFinBigTensor = 256;  // chunks; above this a whole CTA cooperates on the tensor
+constexpr int kFinMaxGrid = 64;
 
 __device__ __forceinline__ void store_tensor_sum(const NormGroup& g, int t, float s) {
   g.tensor_sums[t] = s;
@@ -194,26 +123,29 @@ __device__ __forceinline__ void store_tensor_sum(const NormGroup& g, int t, floa
   }
 }
 
-constexpr int kFinMaxTensors = 4096;  // tensors per dtype group staged in shared memory
+constexpr int kFinMaxTensors = 4096;  // tensors per dtype group staged in shared memory at a time
 
-__global__ void __launch_bounds__(kFinThreads) norm_finalize_kernel(const NormFinalizeArgs a) {
+__global__ void __launch_bounds__(kFinThreads) norm_finalize_kernel(const NormFinalizeArgs a, unsigned int* ticket) {
   __shared__ float red[kFinThreads / 32];
   __shared__ int s_first[kFinMaxTensors + 1];   // chunk ranges of the group's tensors
-  __shared__ float s_sum[kFinMaxTensors];       // per-tensor sums of the group
+  __shared__ float s_sum[kFinMaxTensors];       // per-tensor sums of the group (phase 2)
   __shared__ float s_group[3];
+  __shared__ unsigned int s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = kFinThreads >> 5;
+  // ---- phase 1: per-tensor sums
+  int big_seen = 0, small_seen = 0;  // running counts over all groups: the round-robin keys (uniform in the CTA)
   for (int gi = 0; gi < a.ngroups; ++gi) {
     const NormGroup& g = a.g[gi];
-    float group_sum = 0.0f;  // meaningful in thread 0 only
     for (int base = 0; base < g.ntensors; base += kFinMaxTensors) {
       const int nt = min(kFinMaxTensors, g.ntensors - base);
       // stage the chunk ranges with one coalesced pass (a serial walk over global memory costs ~0.3 us per tensor)
       for (int i = threadIdx.x; i <= nt; i += kFinThreads) s_first[i] = g.first_chunk[base + i];
       __syncthreads();
-      // big tensors: all threads (uniform control flow: every thread sees the same chunk counts)
+      // big tensors: all threads of the CTA that owns the tensor (uniform control flow)
       for (int t = 0; t < nt; ++t) {
         const int c0 = s_first[t], c1 = s_first[t + 1];
         if (c1 - c0 <= kFinBigTensor) continue;
+        if ((big_seen++) % (int)gridDim.x != (int)blockIdx.x) continue;
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
         int c = c0 + threadIdx.x;
         for (; c + 3 * kFinThreads < c1; c += 4 * kFinThreads) {
@@ -227,26 +159,52 @@ __global__ void __launch_bounds__(kFinThreads) norm_finalize_kernel(const NormFi
         for (; c < c1; c += kFinThreads) s0 = __fadd_rn(s0, g.partials[c]);
         float s = __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
         s = block_sum<kFinThreads>(s, red);
-        if (threadIdx.x == 0) s_sum[t] = round_mode(s, g.round_mode);  // the op's output is T-typed
+        if (threadIdx.x == 0) store_tensor_sum(g, base + t, round_mode(s, g.round_mode));  // the op's output is T-typed
       }
-      // small tensors: one warp each
-      for (int t = warp; t < nt; t += nwarps) {
+      // small tensors: one warp each, spread over the warps of all CTAs
+      for (int t = 0; t < nt; ++t) {
         const int c0 = s_first[t], c1 = s_first[t + 1];
         if (c1 - c0 > kFinBigTensor) continue;
+        const int k = small_seen++;
+        if (k % ((int)gridDim.x * nwarps) != (int)blockIdx.x * nwarps + warp) continue;
         float s = 0.0f;
         for (int c = c0 + lane; c < c1; c += 32) s = __fadd_rn(s, g.partials[c]);
         s = warp_sum(s);
-        if (lane == 0) s_sum[t] = round_mode(s, g.round_mode);
+        if (lane == 0) store_tensor_sum(g, base + t, round_mode(s, g.round_mode));
       }
       __syncthreads();
-      for (int t = threadIdx.x; t < nt; t += kFinThreads) store_tensor_sum(g, base + t, s_sum[t]);
+    }
+  }
+  // ---- the CTA that finishes last does phase 2 (fence + ticket: it sees every other CTA's sums)
+  if (gridDim.x > 1) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int t = atomicAdd(ticket, 1u);
+      s_last = (t == gridDim.x - 1) ? 1u : 0u;
+      if (s_last) {
+        *ticket = 0u;
+        __threadfence();
+      }
+    }
+    __syncthreads();
+    if (!s_last) return;
+  }
+  if (!a.compute_clip) return;
+  // ---- phase 2: add_n per group in list order
+  for (int gi = 0; gi < a.ngroups; ++gi) {
+    const NormGroup& g = a.g[gi];
+    float group_sum = 0.0f;  // meaningful in thread 0 only
+    for (int base = 0; base < g.ntensors; base += kFinMaxTensors) {
+      const int nt = min(kFinMaxTensors, g.ntensors - base);
+      for (int t = threadIdx.x; t < nt; t += kFinThreads) s_sum[t] = __ldcg(g.tensor_sums + base + t);
+      __syncthreads();
       if (threadIdx.x == 0)
-        for (int t = 0; t < nt; ++t) group_sum = __fadd_rn(group_sum, s_sum[t]);  // add_n, list order
+        for (int t = 0; t < nt; ++t) group_sum = __fadd_rn(group_sum, s_sum[t]);
       __syncthreads();
     }
     if (threadIdx.x == 0) s_group[gi] = group_sum;
   }
-  if (!a.compute_clip) return;
   if (threadIdx.x == 0) {
     float total = 0.0f;
     for (int gi = 0; gi < a.ngroups; ++gi) {
@@ -263,8 +221,6 @@ __global__ void __launch_bounds__(kFinThreads) norm_finalize_kernel(const NormFi
     if (a.clip_out) *a.clip_out = clip;
   }
 }
-
-constexpr int kGradThreads = 256;  // geometry of the (rare) clip-multiply and zero-fill passes
 
 template <typename T>
 __global__ void __launch_bounds__(kGradThreads) clip_mul_kernel(const GradDesc* __restrict__ descs,
@@ -334,57 +290,47 @@ __global__ void update_loss_scaling_kernel(const bool* found_inf, const float* p
 }
 
 template <typename T>
-int32_t launch_pass_typed(const DeviceTable& tab, bool write, bool norm, bool mp, const float* ls, bool* found,
-                          float* partials, cudaStream_t stream) {
+int32_t launch_pass_typed(const DeviceTable& tab, const GradPassOpts& o, cudaStream_t stream) {
   if (tab.nchunks == 0) return PRB_SUCCESS;
   const GradDesc* d = reinterpret_cast<const GradDesc*>(tab.descs);
-#define PRB_GPV(W, N, M, T_, U_, B_) \
-  grad_pass_kernel<T, W, N, M, T_, U_, B_><<<tab.nchunks, T_, 0, stream>>>(d, tab.chunks, ls, found, partials)
-#define PRB_GP(W, N, M)                                    \
-  do {                                                     \
-    switch (active_grad_variant()) {                       \
-      case 0: PRB_GPV(W, N, M, 256, 4, 2); break;          \
-      case 1: PRB_GPV(W, N, M, 256, 2, 4); break;          \
-      case 2: PRB_GPV(W, N, M, 256, 1, 8); break;          \
-      case 3: PRB_GPV(W, N, M, 128, 1, 16); break;         \
-      case 4: PRB_GPV(W, N, M, 128, 2, 8); break;          \
-      case 5: PRB_GPV(W, N, M, 256, 8, 2); break;          \
-      case 6: PRB_GPV(W, N, M, 512, 4, 1); break;          \
-      default: PRB_GPV(W, N, M, 512, 8, 1); break;         \
-    }                                                      \
+  KernelTimer kt(o.mode == 2 ? KK_PACK_EPILOGUE : KK_GRAD_PASS, stream);
+#define PRB_GP(M, N, P)                                                                                              \
+  grad_pass_kernel<T, M, N, P><<<tab.nchunks, kGradThreads, 0, stream>>>(d, tab.chunks, o.loss_scale, o.found_inf, \
+                                                                         o.partials, o.pack_scale, o.pack_bias)
+#define PRB_GPM(M)                          \
+  do {                                      \
+    if (!o.norm) PRB_GP(M, false, false);   \
+    else if (!o.mp) PRB_GP(M, true, false); \
+    else PRB_GP(M, true, true);             \
   } while (0)
-  if (write && !norm) PRB_GP(true, false, false);
-  else if (write && norm && !mp) PRB_GP(true, true, false);
-  else if (write && norm && mp) PRB_GP(true, true, true);
-  else if (!write && norm && !mp) PRB_GP(false, true, false);
-  else if (!write && norm && mp) PRB_GP(false, true, true);
-  else PRB_GP(false, false, false);
+  if (o.mode == 0) PRB_GPM(0);
+  else if (o.mode == 1) PRB_GPM(1);
+  else PRB_GPM(2);
+#undef PRB_GPM
 #undef PRB_GP
-#undef PRB_GPV
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 
 }  // namespace
 
-int grad_chunk_elems() {
-  const GradVariant v = kGradVariants[active_grad_variant()];
-  return v.threads * kVec * v.unroll;
-}
-
-int32_t launch_grad_pass(int32_t dtype, const DeviceTable& tab, bool write, bool norm, bool mp, const float* loss_scale,
-                         bool* found_inf, float* partials, cudaStream_t stream) {
+int32_t launch_grad_pass(int32_t dtype, const DeviceTable& tab, const GradPassOpts& o, cudaStream_t stream) {
+  PRB_ENFORCE(o.loss_scale == nullptr || o.found_inf != nullptr, PRB_INVALID_ARGUMENT, "grad pass: unscale needs a found_inf flag");
+  PRB_ENFORCE(!o.norm || o.partials != nullptr, PRB_INVALID_ARGUMENT, "grad pass: norm needs a partials buffer");
   switch (dtype) {
-    case PRB_FLOAT32: return launch_pass_typed<float>(tab, write, norm, mp, loss_scale, found_inf, partials, stream);
-    case PRB_BFLOAT16:
-      return launch_pass_typed<__nv_bfloat16>(tab, write, norm, mp, loss_scale, found_inf, partials, stream);
-    case PRB_FLOAT16: return launch_pass_typed<__half>(tab, write, norm, mp, loss_scale, found_inf, partials, stream);
+    case PRB_FLOAT32: return launch_pass_typed<float>(tab, o, stream);
+    case PRB_BFLOAT16: return launch_pass_typed<__nv_bfloat16>(tab, o, stream);
+    case PRB_FLOAT16: return launch_pass_typed<__half>(tab, o, stream);
     default: PRB_FAIL(PRB_UNIMPLEMENTED, "dtype %s is not built (float32/bfloat16/float16 only)", dtype_name(dtype));
   }
 }
 
 int32_t launch_norm_finalize(const NormFinalizeArgs& a, cudaStream_t stream) {
-  norm_finalize_kernel<<<1, kFinThreads, 0, stream>>>(a);
+  int grid = a.grid_hint < 1 ? 1 : (a.grid_hint > kFinMaxGrid ? kFinMaxGrid : a.grid_hint);
+  void* tk = nullptr;
+  if (grid > 1) PRB_TRY(ticket_counter(&tk, stream));
+  KernelTimer kt(KK_NORM_FINALIZE, stream);
+  norm_finalize_kernel<<<grid, kFinThreads, 0, stream>>>(a, reinterpret_cast<unsigned int*>(tk));
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
@@ -453,9 +399,11 @@ int32_t prb_check_finite_and_unscale(const PRB_Tensor* xs, int64_t num, const PR
   }
   DeviceTable tab;
   PRB_TRY(grad_table(xs, outs, num, -1, stream, &tab));
-  return launch_grad_pass(dt, tab, /*write=*/true, /*norm=*/false, /*mp=*/false,
-                          reinterpret_cast<const float*>(scale->data), reinterpret_cast<bool*>(found_infinite->data),
-                          nullptr, stream);
+  GradPassOpts o;
+  o.mode = 1;
+  o.loss_scale = reinterpret_cast<const float*>(scale->data);
+  o.found_inf = reinterpret_cast<bool*>(found_infinite->data);
+  return launch_grad_pass(dt, tab, o, stream);
 }
 
 int32_t prb_squared_l2_norm(const PRB_Tensor* x, PRB_Tensor* out, void* stream_) {
@@ -468,9 +416,12 @@ int32_t prb_squared_l2_norm(const PRB_Tensor* x, PRB_Tensor* out, void* stream_)
   PRB_TRY(grad_table(x, nullptr, 1, -1, stream, &tab));
   void* ws = nullptr;
   const size_t npart = (size_t)tab.nchunks + 1;
-  PRB_TRY(workspace((npart + 1) * sizeof(float), &ws, /*slot=*/1));
+  PRB_TRY(workspace((npart + 1) * sizeof(float), &ws, /*slot=*/1, stream));
   float* partials = reinterpret_cast<float*>(ws);
-  PRB_TRY(launch_grad_pass(x->dtype, tab, false, true, false, nullptr, nullptr, partials, stream));
+  GradPassOpts o;
+  o.norm = true;
+  o.partials = partials;
+  PRB_TRY(launch_grad_pass(x->dtype, tab, o, stream));
   NormFinalizeArgs a{};
   a.ngroups = 1;
   a.g[0].partials = partials;
@@ -504,7 +455,7 @@ int32_t prb_clip_grad_by_global_norm(PRB_Tensor* grads, int64_t num, float clip_
     total_tensors += tabs[c].ndescs;
   }
   void* ws = nullptr;
-  PRB_TRY(workspace((total_chunks + total_tensors + 2) * sizeof(float), &ws, /*slot=*/1));
+  PRB_TRY(workspace((total_chunks + total_tensors + 2) * sizeof(float), &ws, /*slot=*/1, stream));
   float* base = reinterpret_cast<float*>(ws);
   float* clip_dev = clip_out ? reinterpret_cast<float*>(clip_out->data) : base + total_chunks + total_tensors;
   float* norm_dev = global_norm_out ? reinterpret_cast<float*>(global_norm_out->data) : nullptr;
@@ -513,7 +464,11 @@ int32_t prb_clip_grad_by_global_norm(PRB_Tensor* grads, int64_t num, float clip_
   float* sums = base + total_chunks;
   for (int c = 0; c < 3; ++c) {
     if (tabs[c].ndescs == 0) continue;
-    PRB_TRY(launch_grad_pass(classes[c], tabs[c], false, true, use_mp_type != 0, nullptr, nullptr, part, stream));
+    GradPassOpts o;
+    o.norm = true;
+    o.mp = use_mp_type != 0;
+    o.partials = part;
+    PRB_TRY(launch_grad_pass(classes[c], tabs[c], o, stream));
     NormGroup& g = a.g[a.ngroups++];
     g.partials = part;
     g.first_chunk = tabs[c].first_chunk;
@@ -529,6 +484,11 @@ int32_t prb_clip_grad_by_global_norm(PRB_Tensor* grads, int64_t num, float clip_
   a.clip_norm = clip_norm;
   a.auto_skip_clip = auto_skip_clip;
   a.compute_clip = 1;
+  {
+    std::vector<int64_t> ns((size_t)num);
+    for (int64_t i = 0; i < num; ++i) ns[(size_t)i] = grads[i].numel;
+    a.grid_hint = finalize_grid_hint(ns.data(), num);
+  }
   a.norm_out = norm_dev;
   a.clip_out = clip_dev;
   PRB_TRY(launch_norm_finalize(a, stream));

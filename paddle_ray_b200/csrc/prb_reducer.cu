@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "prb_bucket.cuh"
+#include "prb_grad_pass.cuh"
 #include "prb_nvlink.h"
 #include "prb_nvls.h"
 
@@ -140,6 +141,19 @@ struct Group {
   // plans cached per group (rebuilt only when the set of unused parameters changes)
   DeviceTable pack_tab, unpack_tab;
   bool pack_valid = false, unpack_valid = false, pack_had_unused = false;
+  DeviceTable packep_tab;         // pack with the check + norm epilogue (GradDesc table, grad_pass_kernel mode 2)
+  bool packep_valid = false, packep_had_unused = false;
+  int64_t first_chunk = 0;        // index of the group's first 8192-element chunk in the reducer's own numbering
+};
+
+// Producer-side pass 1 (prb_reducer_set_grad_epilogue): what the kernel that writes a bucket leaves behind.
+struct Epilogue {
+  bool on = false;
+  const float* loss_scale = nullptr;  // device; nullptr = no unscale / finite check
+  bool* found_inf = nullptr;          // device (this rank's flag)
+  bool norm = false, mp = false;
+  std::vector<int32_t> partial_base;  // per var: first partial in the consumer's layout
+  bool cleared = false;               // found_inf was cleared in this backward
 };
 }  // namespace
 
@@ -150,6 +164,13 @@ struct PRB_Reducer {
   PRB_Comm* comm = nullptr;
   char* arena = nullptr;
   size_t arena_bytes = 0;
+  // Sidecar at the end of the arena (so that peers can reach it like the buckets): norm partials of every
+  // 8192-element chunk of every gradient, the per-tensor sums / clip scratch of the consumer, and flags.
+  size_t sidecar_off = 0;
+  int64_t sidecar_floats = 0;
+  int64_t total_chunks = 0;
+  Epilogue ep;
+  bool grads_in_arena = false;  // gradients are produced in their bucket slots: no pack, no unpack
   void* arena_reg = nullptr;  // ncclCommRegister handle of the arena (NULL when unavailable)
   NvlContext* nvl = nullptr;    // allreduce over NVLink peer memory (prb_nvlink.cu)
   NvlsContext* nvls = nullptr;  // allreduce through NVLink multicast (prb_nvls.cu); owns the arena when set
@@ -171,8 +192,8 @@ struct PRB_Reducer {
   bool batching = false;
   std::vector<size_t> batch;
   std::vector<size_t> batch_key;
-  DeviceTable batch_pack_tab, batch_unpack_tab;
-  bool batch_valid = false;
+  DeviceTable batch_pack_tab, batch_unpack_tab, batch_packep_tab;
+  bool batch_valid = false, batch_packep_valid = false;
   std::vector<int64_t> launched;
 };
 
@@ -197,6 +218,78 @@ int32_t group_tables(PRB_Reducer* r, Group& g, bool for_unpack, cudaStream_t str
                    /*pin=*/true);
 }
 
+float* sidecar(PRB_Reducer* r) { return reinterpret_cast<float*>(r->arena + r->sidecar_off); }
+
+// GradDesc of var v for the pack with epilogue: gradient -> slot, partials at the consumer's position.
+GradDesc packep_desc(PRB_Reducer* r, const Group& g, size_t s) {
+  const int64_t v = g.vars[s];
+  const int es = dtype_size(g.dtype);
+  GradDesc d{};
+  d.x = r->grads[v].data;
+  d.out = r->arena + g.arena_off + (size_t)g.slot_off[s] * es;
+  d.aligned = map_aligned(d.x, d.out, es) ? 1 : 0;
+  d.partial_base = r->ep.norm ? r->ep.partial_base[(size_t)v] : 0;
+  return d;
+}
+
+int32_t group_packep_table(PRB_Reducer* r, Group& g, cudaStream_t stream, DeviceTable* tab) {
+  std::vector<GradDesc> descs;
+  std::vector<int64_t> numels;
+  for (size_t s = 0; s < g.vars.size(); ++s) {
+    if (r->unused[g.vars[s]]) continue;
+    descs.push_back(packep_desc(r, g, s));
+    numels.push_back(r->grads[g.vars[s]].numel);
+  }
+  return get_table(descs.data(), sizeof(GradDesc), (int)descs.size(), numels.data(), grad_chunk_elems(), stream, tab,
+                   /*pin=*/true);
+}
+
+GradPassOpts packep_opts(PRB_Reducer* r) {
+  GradPassOpts o;
+  o.mode = 2;
+  o.norm = r->ep.norm;
+  o.mp = r->ep.mp;
+  o.loss_scale = r->ep.loss_scale;
+  o.found_inf = r->ep.found_inf;
+  o.partials = sidecar(r);
+  o.pack_scale = (float)(1.0 / (double)r->comm->nranks);  // Scalar::to<MT>() (ref scale_kernel.cu:64-66)
+  o.pack_bias = 0.0f;
+  return o;
+}
+
+// Is the epilogue carried by the pack kernel in this configuration?  (One rank, gradients outside the arena.
+// With several ranks the check must see the REDUCED value: it rides in the exchange kernel instead.)
+bool epilogue_in_pack(const PRB_Reducer* r) { return r->ep.on && r->comm->nranks == 1 && !r->grads_in_arena; }
+// Several ranks: only the library's own peer-memory exchange kernel can carry the epilogue and fold the scale.
+bool epilogue_in_exchange(const PRB_Reducer* r) { return r->ep.on && r->comm->nranks > 1 && r->nvl != nullptr; }
+bool epilogue_active(const PRB_Reducer* r) { return epilogue_in_pack(r) || epilogue_in_exchange(r); }
+bool exchange_folds_scale(const PRB_Reducer* r) { return r->comm->nranks > 1 && r->nvl != nullptr; }
+
+// Once per backward, before the first bucket is written: clear this rank's found_inf.
+int32_t epilogue_begin(PRB_Reducer* r, cudaStream_t calc) {
+  if (!epilogue_active(r) || r->ep.cleared) return PRB_SUCCESS;
+  if (r->ep.loss_scale != nullptr) PRB_CUDA(cudaMemsetAsync(r->ep.found_inf, 0, 1, calc));
+  r->ep.cleared = true;
+  return PRB_SUCCESS;
+}
+
+// A parameter without a gradient in this backward: zero slot (ref reducer.cc:833-855) and, with the epilogue,
+// zero norm partials (nothing will visit its chunks on this rank when the pack carries the epilogue).
+int32_t zero_unused_slots(PRB_Reducer* r, Group& g, cudaStream_t calc) {
+  const int es = dtype_size(g.dtype);
+  char* region = r->arena + g.arena_off;
+  for (size_t s = 0; s < g.vars.size(); ++s) {
+    const int64_t v = g.vars[s];
+    if (!r->unused[v]) continue;
+    PRB_CUDA(cudaMemsetAsync(region + (size_t)g.slot_off[s] * es, 0, (size_t)r->grads[v].numel * es, calc));
+    if (epilogue_in_pack(r) && r->ep.norm) {
+      const int64_t nch = (r->grads[v].numel + grad_chunk_elems() - 1) / grad_chunk_elems();
+      PRB_CUDA(cudaMemsetAsync(sidecar(r) + r->ep.partial_base[(size_t)v], 0, (size_t)nch * sizeof(float), calc));
+    }
+  }
+  return PRB_SUCCESS;
+}
+
 // ref: FusedAllReduceSchedule reducer.cc:1037-1070 ("concat > div_nranks > allreduce > split")
 int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   Group& g = r->groups[gi];
@@ -206,25 +299,46 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   }
   PRB_Comm* c = r->comm;
   const int es = dtype_size(g.dtype);
-  if (r->batching && c->nranks == 1 && !g.has_unused && !g.pack_had_unused &&
+  if (r->batching && c->nranks == 1 && !r->grads_in_arena && !g.has_unused && !g.pack_had_unused && !g.packep_had_unused &&
       (r->batch.empty() || r->groups[r->batch.front()].dtype == g.dtype)) {
     r->batch.push_back(gi);
     r->launched.push_back((int64_t)gi);
     return PRB_SUCCESS;
   }
   char* region = r->arena + g.arena_off;
-  if (g.has_unused) {
-    for (size_t s = 0; s < g.vars.size(); ++s)
-      if (r->unused[g.vars[s]])
-        PRB_CUDA(cudaMemsetAsync(region + (size_t)g.slot_off[s] * es, 0, (size_t)r->grads[g.vars[s]].numel * es, calc));
+  PRB_TRY(epilogue_begin(r, calc));
+  if (g.has_unused) PRB_TRY(zero_unused_slots(r, g, calc));
+  if (r->grads_in_arena) {
+    // the producer wrote the slots: nothing to pack; with several ranks the 1/nranks scale runs in place
+    // (ref scale_ reducer.cc:1049-1050) unless the exchange kernel folds it in
+    if (c->nranks > 1 && !exchange_folds_scale(r)) {
+      if (!g.pack_valid) {
+        MapDesc d{};
+        d.src = region;
+        d.dst = region;
+        d.aligned = 1;
+        PRB_TRY(get_table(&d, sizeof(d), 1, &g.length, map_chunk_elems(), calc, &g.pack_tab, /*pin=*/true));
+        g.pack_valid = true;
+      }
+      PRB_TRY(launch_scale(g.dtype, g.pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
+    }
+  } else if (epilogue_in_pack(r)) {
+    // pack + scale + unscale/inf check + norm partials in one pass, calc stream
+    if (!g.packep_valid || g.has_unused || g.packep_had_unused) {
+      PRB_TRY(group_packep_table(r, g, calc, &g.packep_tab));
+      g.packep_valid = true;
+      g.packep_had_unused = g.has_unused;
+    }
+    PRB_TRY(launch_grad_pass(g.dtype, g.packep_tab, packep_opts(r), calc));
+  } else {
+    // pack + scale_(bucket, 1.0/nranks, 0.0, false) in one pass, calc stream
+    if (!g.pack_valid || g.has_unused || g.pack_had_unused) {
+      PRB_TRY(group_tables(r, g, false, calc, &g.pack_tab));
+      g.pack_valid = true;
+      g.pack_had_unused = g.has_unused;
+    }
+    PRB_TRY(launch_scale(g.dtype, g.pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
   }
-  // pack + scale_(bucket, 1.0/nranks, 0.0, false) in one pass, calc stream
-  if (!g.pack_valid || g.has_unused || g.pack_had_unused) {
-    PRB_TRY(group_tables(r, g, false, calc, &g.pack_tab));
-    g.pack_valid = true;
-    g.pack_had_unused = g.has_unused;
-  }
-  PRB_TRY(launch_scale(g.dtype, g.pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
   if (c->nranks > 1) {
     // SyncDefaultStream: comm stream waits for the calc stream (ref process_group_nccl.cc:658-667)
     cudaStream_t cs = c->stream;
@@ -241,7 +355,7 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
       PRB_TRY(nccl_dtype(g.dtype, &nt));
       PRB_NCCL(g_nccl.AllReduce(region, region, (size_t)g.length, nt, ncclSum, c->comm, cs));
     }
-    if (r->unpack) {  // the reference also splits on the comm stream (reducer.cc:1062-1069)
+    if (r->unpack && !r->grads_in_arena) {  // the reference also splits on the comm stream (reducer.cc:1062-1069)
       if (!g.unpack_valid) {
         PRB_TRY(group_tables(r, g, true, cs, &g.unpack_tab));
         g.unpack_valid = true;
@@ -249,7 +363,7 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
       PRB_TRY(launch_copy(es, g.unpack_tab, cs));
     }
     PRB_CUDA(cudaEventRecord(g.done, cs));
-  } else if (r->unpack) {
+  } else if (r->unpack && !r->grads_in_arena) {
     if (!g.unpack_valid) {
       PRB_TRY(group_tables(r, g, true, calc, &g.unpack_tab));
       g.unpack_valid = true;
@@ -262,8 +376,11 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
 
 int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
   if (r->batch.empty()) return PRB_SUCCESS;
-  if (!r->batch_valid || r->batch_key != r->batch) {
+  if (r->batch_key != r->batch) r->batch_valid = r->batch_packep_valid = false;
+  const bool with_ep = epilogue_in_pack(r);
+  if (with_ep ? !r->batch_packep_valid : !r->batch_valid) {
     std::vector<MapDesc> pack, unpack;
+    std::vector<GradDesc> packep;
     std::vector<int64_t> numels;
     for (size_t gi : r->batch) {
       Group& g = r->groups[gi];
@@ -281,19 +398,28 @@ int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
         u.dst = r->grads[v].data;
         u.aligned = d.aligned;
         unpack.push_back(u);
+        if (with_ep) packep.push_back(packep_desc(r, g, s));
         numels.push_back(r->grads[v].numel);
       }
     }
-    PRB_TRY(get_table(pack.data(), sizeof(MapDesc), (int)pack.size(), numels.data(), map_chunk_elems(), calc,
-                      &r->batch_pack_tab, /*pin=*/true));
+    if (with_ep) {
+      PRB_TRY(get_table(packep.data(), sizeof(GradDesc), (int)packep.size(), numels.data(), grad_chunk_elems(), calc,
+                        &r->batch_packep_tab, /*pin=*/true));
+      r->batch_packep_valid = true;
+    } else {
+      PRB_TRY(get_table(pack.data(), sizeof(MapDesc), (int)pack.size(), numels.data(), map_chunk_elems(), calc,
+                        &r->batch_pack_tab, /*pin=*/true));
+      r->batch_valid = true;
+    }
     PRB_TRY(get_table(unpack.data(), sizeof(MapDesc), (int)unpack.size(), numels.data(), map_chunk_elems(), calc,
                       &r->batch_unpack_tab, /*pin=*/true));
     r->batch_key = r->batch;
-    r->batch_valid = true;
   }
   const int32_t dt = r->groups[r->batch.front()].dtype;
   r->batch.clear();
-  PRB_TRY(launch_scale(dt, r->batch_pack_tab, 1.0, 0.0f, false, calc));  // 1.0 / nranks with one rank
+  PRB_TRY(epilogue_begin(r, calc));
+  if (with_ep) PRB_TRY(launch_grad_pass(dt, r->batch_packep_tab, packep_opts(r), calc));
+  else PRB_TRY(launch_scale(dt, r->batch_pack_tab, 1.0, 0.0f, false, calc));  // 1.0 / nranks with one rank
   if (r->unpack) PRB_TRY(launch_copy(dtype_size(dt), r->batch_unpack_tab, calc));
   return PRB_SUCCESS;
 }
@@ -523,6 +649,7 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
         break;
       }
       const int es = dtype_size(t.dtype);
+      if (t.data == nullptr && !r->dry) r->grads_in_arena = true;  // no buffer given: the gradient lives in its slot
       if (!(es == 2 || es == 4) || (t.device < 0 && !r->dry)) {
         set_error("reducer_create: tensor %lld must be a float32/bfloat16/float16 device tensor", (long long)v);
         status = PRB_UNIMPLEMENTED;
@@ -537,6 +664,8 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
     g.length = off;
     g.arena_off = arena;
     arena += align_up((size_t)off * dtype_size(g.dtype), 256);
+    g.first_chunk = r->total_chunks;
+    for (int64_t v : g.vars) r->total_chunks += (r->grads[(size_t)v].numel + grad_chunk_elems() - 1) / grad_chunk_elems();
     r->groups.push_back(std::move(g));
   }
   if (status == PRB_SUCCESS)
@@ -550,6 +679,10 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
     delete r;
     return status;
   }
+  // sidecar: [total_chunks partials | num per-tensor sums | 8 spare floats (clip scratch)] + 256 B of flags
+  r->sidecar_off = arena;
+  r->sidecar_floats = r->total_chunks + num + 8;
+  arena += align_up((size_t)r->sidecar_floats * sizeof(float), 256) + 256;
   r->arena_bytes = arena;
   if (r->dry) {
     r->finalized = true;
@@ -641,6 +774,7 @@ int32_t prb_reducer_prepare_for_backward(PRB_Reducer* r) {
   r->has_marked_unused = false;
   r->finalized = false;
   r->launched.clear();
+  r->ep.cleared = false;
   return PRB_SUCCESS;
 }
 
@@ -683,6 +817,61 @@ int32_t prb_reducer_mark_vars_ready(PRB_Reducer* r, const int64_t* var_indices, 
   r->batch.clear();
   return st;
 }
+
+int32_t prb_reducer_set_grads_in_arena(PRB_Reducer* r, int32_t enabled) {
+  PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  PRB_ENFORCE(r->finalized, PRB_PRECONDITION_NOT_MET, "reducer: cannot change the gradient layout in the middle of a backward");
+  if (!enabled)
+    for (const PRB_Tensor& t : r->grads)
+      PRB_ENFORCE(t.data != nullptr || r->dry, PRB_INVALID_ARGUMENT,
+                  "reducer: this reducer was created without gradient buffers; its gradients can only live in the arena");
+  r->grads_in_arena = enabled != 0;
+  for (Group& g : r->groups) g.pack_valid = false;  // the table slot is shared by the pack and the in-place scale
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_set_grad_epilogue(PRB_Reducer* r, const PRB_GradEpilogue* e, PRB_Tensor* partials_out,
+                                      int32_t* active) {
+  PRB_ENFORCE(r && !r->dry, PRB_INVALID_ARGUMENT, "reducer: bad handle");
+  PRB_ENFORCE(r->finalized, PRB_PRECONDITION_NOT_MET, "reducer: cannot change the epilogue in the middle of a backward");
+  Epilogue ep;
+  if (e != nullptr) {
+    if (e->loss_scale != nullptr) {
+      PRB_ENFORCE(e->loss_scale->numel == 1 && e->loss_scale->dtype == PRB_FLOAT32 && e->loss_scale->device >= 0,
+                  PRB_INVALID_ARGUMENT, "grad epilogue: loss_scale must be one float32 on the device");
+      PRB_ENFORCE(e->found_inf && e->found_inf->numel == 1 && e->found_inf->dtype == PRB_BOOL && e->found_inf->device >= 0,
+                  PRB_INVALID_ARGUMENT, "grad epilogue: loss_scale needs a bool device found_inf");
+      ep.loss_scale = reinterpret_cast<const float*>(e->loss_scale->data);
+      ep.found_inf = reinterpret_cast<bool*>(e->found_inf->data);
+    }
+    ep.norm = e->want_norm != 0;
+    ep.mp = e->use_mp_type != 0;
+    if (ep.norm) {
+      PRB_ENFORCE(e->partial_base != nullptr, PRB_INVALID_ARGUMENT, "grad epilogue: want_norm needs partial_base");
+      ep.partial_base.assign(e->partial_base, e->partial_base + r->grads.size());
+      for (size_t v = 0; v < r->grads.size(); ++v) {
+        const int64_t nch = (r->grads[v].numel + grad_chunk_elems() - 1) / grad_chunk_elems();
+        PRB_ENFORCE(ep.partial_base[v] >= 0 && ep.partial_base[v] + nch <= r->total_chunks, PRB_OUT_OF_RANGE,
+                    "grad epilogue: partial_base[%zu] = %d does not fit the %lld chunks of this reducer", v,
+                    ep.partial_base[v], (long long)r->total_chunks);
+      }
+    }
+    ep.on = ep.norm || ep.loss_scale != nullptr;
+  }
+  r->ep = ep;
+  for (Group& g : r->groups) g.packep_valid = false;
+  r->batch_packep_valid = false;
+  if (partials_out != nullptr) {
+    partials_out->data = sidecar(r);
+    partials_out->numel = r->sidecar_floats;
+    partials_out->dtype = PRB_FLOAT32;
+    partials_out->device = r->comm->device;
+  }
+  if (active != nullptr) *active = epilogue_active(r) ? 1 : 0;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_grad_chunk_elems(void) { return grad_chunk_elems(); }
 
 int32_t prb_reducer_set_unpack(PRB_Reducer* r, int32_t enabled) {
   PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");

@@ -43,28 +43,28 @@ int sm_count() {
   return cached[dev];
 }
 
-int l2_hints() {
-  static int v = [] {
-    const char* e = getenv("PRB_L2_HINTS");
-    return e ? atoi(e) : 0;
-  }();
-  return v;
-}
-
 namespace {
 struct Slot {
   void* ptr = nullptr;
   size_t bytes = 0;
 };
+struct WsKey {
+  int dev;
+  cudaStream_t stream;
+  bool operator==(const WsKey& o) const { return dev == o.dev && stream == o.stream; }
+};
+struct WsKeyHash {
+  size_t operator()(const WsKey& k) const { return std::hash<void*>()((void*)k.stream) ^ ((size_t)k.dev * 0x9E3779B97F4A7C15ull); }
+};
 std::mutex g_ws_mu;
-std::unordered_map<int, std::vector<Slot>> g_ws;    // device -> slots
+std::unordered_map<WsKey, std::vector<Slot>, WsKeyHash> g_ws;  // (device, stream) -> slots
 }  // namespace
 
-int32_t workspace(size_t bytes, void** out, int slot) {
+int32_t workspace(size_t bytes, void** out, int slot, cudaStream_t stream) {
   int dev = 0;
   PRB_CUDA(cudaGetDevice(&dev));
   std::lock_guard<std::mutex> lk(g_ws_mu);
-  auto& slots = g_ws[dev];
+  auto& slots = g_ws[WsKey{dev, stream}];
   if ((int)slots.size() <= slot) slots.resize(slot + 1);
   Slot& s = slots[slot];
   if (s.bytes < bytes) {
@@ -79,21 +79,53 @@ int32_t workspace(size_t bytes, void** out, int slot) {
   return PRB_SUCCESS;
 }
 
-int32_t ticket_counter(void** out) {
+int32_t ticket_counter(void** out, cudaStream_t stream) {
   int dev = 0;
   PRB_CUDA(cudaGetDevice(&dev));
   static std::mutex mu;
-  static std::unordered_map<int, void*> counters;
+  static std::unordered_map<WsKey, void*, WsKeyHash> counters;
   std::lock_guard<std::mutex> lk(mu);
-  auto it = counters.find(dev);
+  const WsKey key{dev, stream};
+  auto it = counters.find(key);
   if (it == counters.end()) {
     void* p = nullptr;
     PRB_CUDA(cudaMalloc(&p, 256));
-    PRB_CUDA(cudaMemset(p, 0, 256));
-    it = counters.emplace(dev, p).first;
+    PRB_CUDA(cudaMemset(p, 0, 256));  // synchronous: complete before the first launch on any stream
+    it = counters.emplace(key, p).first;
   }
   *out = it->second;
   return PRB_SUCCESS;
+}
+
+// ---------------------------------------------------------------- per-kernel timing
+std::atomic<int> g_kernel_timing{0};
+namespace {
+struct TimedLaunch {
+  int kind;
+  cudaEvent_t start, stop;
+};
+std::mutex g_kt_mu;
+std::vector<TimedLaunch> g_kt;
+}  // namespace
+
+void KernelTimer::begin(int kind, cudaStream_t stream) {
+  kind_ = kind;
+  stream_ = stream;
+  if (cudaEventCreate(&start_) != cudaSuccess) {
+    start_ = nullptr;
+    return;
+  }
+  cudaEventRecord(start_, stream);
+}
+void KernelTimer::end() {
+  cudaEvent_t stop = nullptr;
+  if (cudaEventCreate(&stop) != cudaSuccess) {
+    cudaEventDestroy(start_);
+    return;
+  }
+  cudaEventRecord(stop, stream_);
+  std::lock_guard<std::mutex> lk(g_kt_mu);
+  g_kt.push_back(TimedLaunch{kind_, start_, stop});
 }
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -261,12 +293,51 @@ int32_t prb_flush_l2(void* stream) {
   PRB_TRY(require_device());
   const size_t bytes = (size_t)256 << 20;  // 256 MiB > 126 MB L2
   void* buf = nullptr;
-  PRB_TRY(workspace(bytes, &buf, /*slot=*/7));
+  PRB_TRY(workspace(bytes, &buf, /*slot=*/7, nullptr));
   flush_kernel<<<sm_count() * 8, 256, 0, (cudaStream_t)stream>>>((float4*)buf, bytes / sizeof(float4));
   PRB_CUDA(cudaGetLastError());  // bench scaffolding: not counted as a hot-path launch
   return PRB_SUCCESS;
 }
 
 int64_t prb_launch_count(void) { return g_launch_count.load(); }
+
+int32_t prb_kernel_timing(int32_t enable) {
+  {
+    std::lock_guard<std::mutex> lk(g_kt_mu);
+    if (enable) {
+      for (TimedLaunch& t : g_kt) {
+        cudaEventDestroy(t.start);
+        cudaEventDestroy(t.stop);
+      }
+      g_kt.clear();
+    }
+  }
+  g_kernel_timing.store(enable ? 1 : 0);
+  return PRB_SUCCESS;
+}
+
+int32_t prb_kernel_timing_read(int32_t kind, double* total_ms, int64_t* launches) {
+  PRB_ENFORCE(kind >= 0 && kind < KK_COUNT && total_ms && launches, PRB_INVALID_ARGUMENT, "kernel_timing_read: bad arguments");
+  PRB_CUDA(cudaDeviceSynchronize());
+  std::lock_guard<std::mutex> lk(g_kt_mu);
+  double ms = 0.0;
+  int64_t n = 0;
+  for (const TimedLaunch& t : g_kt) {
+    if (t.kind != kind) continue;
+    float e = 0.f;
+    PRB_CUDA(cudaEventElapsedTime(&e, t.start, t.stop));
+    ms += e;
+    ++n;
+  }
+  *total_ms = ms;
+  *launches = n;
+  return PRB_SUCCESS;
+}
+
+const char* prb_kernel_kind_name(int32_t kind) {
+  static const char* names[KK_COUNT] = {"map_chunks_kernel", "grad_pass_kernel", "grad_pass_kernel<pack>",
+                                        "norm_finalize_kernel", "adam_chunks_kernel", "nvl_exchange_kernel"};
+  return kind >= 0 && kind < KK_COUNT ? names[kind] : "?";
+}
 
 }  // extern "C"

@@ -10,8 +10,11 @@
 //                              in registers (with the reference's intermediate roundings to T),
 //                              predicated on found_inf on the device, optionally writes the final
 //                              gradient back or zeroes it.
-// Every parameter/moment byte crosses HBM once; a gradient byte twice (norm pass + update pass) --
-// the global norm is a grid-wide dependency -- and usually the second read hits the 126 MB L2.
+// Every parameter/moment byte crosses HBM once.  The global norm is a grid-wide dependency, so the check + norm
+// cannot ride in the update pass; it rides in whatever kernel touches the gradient BEFORE the update instead: the
+// reducer's pack (one rank) or the exchange kernel's slice owner (several ranks) leave found_inf and the norm
+// partials behind (cfg->pass1_done), and pass 1 disappears.  Only a caller without a reducer in front pays the
+// second read of the gradient (ncu: it comes from HBM, not from L2 -- the update pass streams 10x the L2 size).
 #include <vector>
 
 #include "prb_adam.cuh"
@@ -91,21 +94,39 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
                 "dp_step_tail: found_inf must be one bool on the device");
   const float* clip_dev = nullptr;
 
-  if (cfg->use_amp) PRB_CUDA(cudaMemsetAsync(found, 0, 1, stream));
+  // pass1_done: the producer of the gradients (the reducer's pack at one rank, the exchange kernel at several; see
+  // prb_reducer_set_grad_epilogue) already cleared found_inf, ran the check and left the norm partials in
+  // cfg->pass1_partials, so the gradient is not read a second time here.
+  const bool pass1_done = cfg->pass1_done != 0;
+  if (pass1_done)
+    PRB_ENFORCE(!cfg->use_clip || cfg->pass1_partials != nullptr, PRB_INVALID_ARGUMENT,
+                "dp_step_tail: pass1_done with use_clip needs pass1_partials");
+  if (cfg->use_amp && !pass1_done) PRB_CUDA(cudaMemsetAsync(found, 0, 1, stream));
   if (cfg->use_amp || cfg->use_clip) {
     DeviceTable gt;
     PRB_TRY(get_table(gdescs.data(), sizeof(GradDesc), (int)num, numels.data(), grad_chunk_elems(), stream, &gt));
     float* partials = nullptr;
     float* scratch_clip = nullptr;
     if (cfg->use_clip) {
-      void* ws = nullptr;
-      PRB_TRY(workspace(((size_t)gt.nchunks + (size_t)num + 2) * sizeof(float), &ws, /*slot=*/1));
-      partials = reinterpret_cast<float*>(ws);
+      if (pass1_done) {
+        partials = cfg->pass1_partials;  // sized by prb_tail_partials_numel: [nchunks | num tensor sums | 2]
+      } else {
+        void* ws = nullptr;
+        PRB_TRY(workspace(((size_t)gt.nchunks + (size_t)num + 2) * sizeof(float), &ws, /*slot=*/1, stream));
+        partials = reinterpret_cast<float*>(ws);
+      }
       scratch_clip = partials + gt.nchunks + num;
     }
     const bool mp = cfg->use_mp_type != 0;
-    PRB_TRY(launch_grad_pass(dt_g, gt, /*write=*/false, /*norm=*/cfg->use_clip != 0, mp, ls, cfg->use_amp ? found : nullptr,
-                             partials, stream));
+    if (!pass1_done) {
+      GradPassOpts o;
+      o.norm = cfg->use_clip != 0;
+      o.mp = mp;
+      o.loss_scale = ls;
+      o.found_inf = cfg->use_amp ? found : nullptr;
+      o.partials = partials;
+      PRB_TRY(launch_grad_pass(dt_g, gt, o, stream));
+    }
     if (cfg->use_clip) {
       NormFinalizeArgs a{};
       a.ngroups = 1;
@@ -118,6 +139,7 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
       a.clip_norm = cfg->clip_norm;
       a.auto_skip_clip = cfg->auto_skip_clip;
       a.compute_clip = 1;
+      a.grid_hint = finalize_grid_hint(numels.data(), num);
       a.norm_out = global_norm_out ? reinterpret_cast<float*>(global_norm_out->data) : nullptr;
       a.clip_out = clip_out ? reinterpret_cast<float*>(clip_out->data) : scratch_clip;
       PRB_TRY(launch_norm_finalize(a, stream));
@@ -139,11 +161,9 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   a.loss_scale = ls;
   a.clip = clip_dev;
   a.zero_grad = cfg->zero_grads;
-  a.l2_hints = l2_hints();
-  a.reverse = getenv("PRB_TAIL_REVERSE") != nullptr ? 1 : 0;  // measured neutral on B200 (profiles/r1_experiments.md)
   // beta-pow accumulators advance inside the update kernel (last-CTA ticket) unless found_inf
   void* tk = nullptr;
-  PRB_TRY(ticket_counter(&tk));
+  PRB_TRY(ticket_counter(&tk, stream));
   if (!cfg->keep_beta_pow) {
     a.pow_b1 = reinterpret_cast<float*>(beta1_pow->data);
     a.pow_b2 = reinterpret_cast<float*>(beta2_pow->data);

@@ -209,6 +209,34 @@ class EagerReducer:
     def set_unpack(self, enabled: bool):
         call("prb_reducer_set_unpack", self.handle, int(bool(enabled)))
 
+    def set_grads_in_arena(self, enabled: bool):
+        call("prb_reducer_set_grads_in_arena", self.handle, int(bool(enabled)))
+
+    def set_grad_epilogue(self, loss_scale=None, found_inf=None, partial_base=None, use_mp_type=False):
+        """Producer-side pass 1 (see prb_reducer_set_grad_epilogue).  Returns (active, partials view); all arguments
+        None switches it off."""
+        out = _lib.PRBTensor()
+        active = C.c_int32()
+        if loss_scale is None and partial_base is None:
+            call("prb_reducer_set_grad_epilogue", self.handle, None, C.byref(out), C.byref(active))
+            self._epilogue_keep = None
+            return False, None
+        e = _lib.GradEpilogue()
+        keep = [e]
+        if loss_scale is not None:
+            ls, fi = loss_scale.prb, found_inf.prb
+            e.loss_scale, e.found_inf = C.pointer(ls), C.pointer(fi)
+            keep += [ls, fi]
+        if partial_base is not None:
+            pb = np.ascontiguousarray(partial_base, np.int32)
+            assert pb.size == len(self._grads)
+            e.want_norm, e.partial_base = 1, pb.ctypes.data
+            keep.append(pb)
+        e.use_mp_type = int(bool(use_mp_type))
+        call("prb_reducer_set_grad_epilogue", self.handle, C.byref(e), C.byref(out), C.byref(active))
+        self._epilogue_keep = keep
+        return bool(active.value), Tensor(out.numel, out.dtype, out.device, data_ptr=out.data, owner=self)
+
     @property
     def allreduce_backend(self) -> str:
         return {0: "none", 1: "nccl", 2: "nvlink", 3: "nvls"}[lib.prb_reducer_allreduce_backend(self.handle)]
@@ -282,7 +310,7 @@ class DataParallel:
     """
 
     def __init__(self, parameters, strategy=None, comm_buffer_size=25, last_comm_buffer_size=1,
-                 find_unused_parameters=False, group=None, consume_from_buckets=False):
+                 find_unused_parameters=False, group=None, consume_from_buckets=False, grads_in_arena=False):
         self._parameters = [p for p in parameters if not getattr(p, "stop_gradient", False)]
         assert len(self._parameters) > 0, (
             "This model does not have any parameters to train, and does not need to use DataParallel")
@@ -292,8 +320,9 @@ class DataParallel:
         if self.group is None:
             warnings.warn("init_parallel_env() was not called: falling back to a single-rank communicator.")
             self.group = init_parallel_env()
+        self.grads_in_arena = bool(grads_in_arena)
         for p in self._parameters:
-            if p.grad is None:
+            if p.grad is None and not self.grads_in_arena:
                 p.grad = Tensor.zeros(p.numel, p.dtype, p.device)
         sync_params_buffers(self._parameters, self.group)
         self.comm_buffer_size = int(comm_buffer_size * 1024 * 1024)
@@ -301,16 +330,28 @@ class DataParallel:
         self.init_reducer()
         self._consume = False
         self.pipelined = False
-        if consume_from_buckets:
+        self._epilogue_key = None     # what the reducer's grad epilogue is currently configured for
+        self._epilogue_armed = False  # True once a backward has run with it (its results are there to consume)
+        self._epilogue_partials = None
+        if consume_from_buckets or self.grads_in_arena:
             self.consume_from_buckets(True)
 
     def init_reducer(self):
         is_sparse = [bool(getattr(p, "is_sparse_grad", False)) for p in self._parameters]
         self.group_indices = assign_group_by_size(self._parameters, is_sparse,
                                                   [self.last_comm_buffer_size, self.comm_buffer_size])
-        self._reducer = EagerReducer([p.grad for p in self._parameters], list(reversed(self.group_indices)), is_sparse,
+        if self.grads_in_arena:
+            # gradients are PRODUCED in the bucket slots (no pack, no split back): p.grad becomes the slot view.
+            # ref: MarkVarReady aliases the gradient into the group's dense tensor, reducer.cc:774-901
+            grads = [Tensor(p.numel, p.dtype, p.device, data_ptr=0) for p in self._parameters]
+        else:
+            grads = [p.grad for p in self._parameters]
+        self._reducer = EagerReducer(grads, list(reversed(self.group_indices)), is_sparse,
                                      self.group, [self.last_comm_buffer_size, self.comm_buffer_size],
                                      self.find_unused_parameters)
+        if self.grads_in_arena:
+            for i, p in enumerate(self._parameters):
+                p.grad = self._reducer.bucket_view(i)
         # backward produces gradients in reverse parameter order
         self._reverse_order = (C.c_int64 * len(self._parameters))(*reversed(range(len(self._parameters))))
 
@@ -349,6 +390,25 @@ class DataParallel:
     def prepare_for_backward(self, unused_vars=()):
         if self.grad_need_sync:
             self._reducer.prepare_for_backward(unused_vars)
+            self._epilogue_armed = self._epilogue_key is not None
+
+    def _configure_epilogue(self, key, loss_scale=None, found_inf=None, partial_base=None, use_mp_type=False):
+        """Called by the optimizer between two backward passes.  key None switches the epilogue off.  Returns True when
+        the reducer will carry pass 1 from the NEXT backward on."""
+        if key == self._epilogue_key:
+            return key is not None
+        self._epilogue_armed = False
+        if key is None:
+            self._reducer.set_grad_epilogue()
+            self._epilogue_key, self._epilogue_partials = None, None
+            return False
+        active, partials = self._reducer.set_grad_epilogue(loss_scale, found_inf, partial_base, use_mp_type)
+        if not active:
+            self._reducer.set_grad_epilogue()
+            self._epilogue_key, self._epilogue_partials = None, None
+            return False
+        self._epilogue_key, self._epilogue_partials = key, partials
+        return True
 
     def mark_var_ready(self, index: int, stream=None):
         if self.grad_need_sync:

@@ -2,6 +2,7 @@
 from __future__ import annotations
 
 from .. import _C_ops
+from .._lib import FLOAT32
 from ..core import Tensor
 
 _clip_by_global_norm_using_mp_type_flag = False
@@ -40,6 +41,12 @@ class ClipGradByGlobalNorm(ClipGradBase):
         self.last_global_norm: Tensor | None = None
         self.last_clip: Tensor | None = None
 
+    def _ensure_outputs(self):
+        """The two device scalars every user of this object writes into; allocated once, never rebound (cached
+        optimizer plans hold their addresses)."""
+        if self.last_global_norm is None:
+            self.last_global_norm, self.last_clip = Tensor.zeros(1, FLOAT32), Tensor.zeros(1, FLOAT32)
+
     def __str__(self):
         return "Gradient Clip By GlobalNorm, global_norm=%f" % (self.clip_norm)
 
@@ -52,6 +59,8 @@ class ClipGradByGlobalNorm(ClipGradBase):
             ng = Tensor(g.numel, g.dtype, g.device)
             ng.copy_(g)
             new_grads[id(p)] = ng
-        self.last_global_norm, self.last_clip = _C_ops.clip_grad_by_global_norm_(
-            list(new_grads.values()), self.clip_norm, self.auto_skip_clip, _clip_by_global_norm_using_mp_type())
+        self._ensure_outputs()
+        _C_ops.clip_grad_by_global_norm_(list(new_grads.values()), self.clip_norm, self.auto_skip_clip,
+                                         _clip_by_global_norm_using_mp_type(), norm=self.last_global_norm,
+                                         clip=self.last_clip)
         return [(p, new_grads.get(id(p), g)) for p, g in params_grads]

@@ -23,12 +23,13 @@ from collections import OrderedDict
 import numpy as np
 
 from .. import _C_ops, _lib, core
-from .._lib import BFLOAT16, BOOL, FLOAT16, FLOAT32, TailConfig, call, tensor_array
+from .._lib import BFLOAT16, BOOL, FLOAT16, FLOAT32, TailConfig, call, lib, tensor_array
 from ..core import Tensor
 from ..nn.clip import ClipGradByGlobalNorm, _clip_by_global_norm_using_mp_type
 from .lr import LRScheduler
 
 _ALIGN_ELEMS = 64  # 256 B of fp32
+_MISSING = object()  # a cached plan may legitimately be None (the per-tensor path)
 
 
 class _ScalarFeeder:
@@ -86,6 +87,9 @@ class Optimizer:
         self._zero_grads_in_step = False
         # True keeps p.grad reference-visible after an AMP step (the unscaled gradient is stored back)
         self._write_back_unscaled_grads = True
+        # True lets the producer of the bucket (DataParallel's pack / exchange kernel) carry the inf check and the
+        # norm partials, so the step reads each gradient once; False keeps pass 1 here (used by parity tests)
+        self._use_producer_pass1 = True
         self.clear_gradients = self.clear_grad
 
     # ---- auxiliary vars (found_inf hand-off from GradScaler; ref adamw.py:283-291)
@@ -168,11 +172,15 @@ class Optimizer:
         found_inf = self._get_auxiliary_var("found_inf")
         loss_scale = self._get_auxiliary_var("loss_scale")  # set by GradScaler when the unscale is deferred to us
         clip = self._grad_clip
+        # everything a cached plan bakes in: buffers, flags and hyper-parameters (changing weight decay or the clip
+        # norm in the middle of training builds a new plan instead of being ignored)
         key = (tuple(g.data_ptr for _, g in pg), id(clip), loss_scale.data_ptr if loss_scale is not None else 0,
                found_inf.data_ptr if found_inf is not None else 0, self._zero_grads_in_step,
-               self._write_back_unscaled_grads, _clip_by_global_norm_using_mp_type())
-        plan = self._step_plans.get(key)
-        if plan is None:
+               self._write_back_unscaled_grads, _clip_by_global_norm_using_mp_type(), self._hyper_key(),
+               (clip.clip_norm, clip.auto_skip_clip) if clip is not None else None,
+               pg[0][0]._bucket[0].pipelined if pg[0][0]._bucket[0] is not None else None, self._use_producer_pass1)
+        plan = self._step_plans.get(key, _MISSING)
+        if plan is _MISSING:
             if len(self._step_plans) > 16:
                 self._step_plans.clear()
             plan = self._step_plans[key] = self._build_plan(pg, found_inf, loss_scale)
@@ -181,12 +189,28 @@ class Optimizer:
         lr = self._global_lr().prb
         lr_ref = C.byref(lr)
         stream = core._stream_handle(None)
-        for dp, gi, args in plan:
+        for entry in plan:
+            dp, gi, args, ep = entry["dp"], entry["group"], entry["args"], entry["epilogue"]
             if dp is not None:
                 if gi is None:
                     dp.wait_all_groups()
                 else:
                     dp.wait_group(gi)
+                if ep is not None and dp._epilogue_key == ep["key"] and dp._epilogue_armed:
+                    # the backward that just ended ran with the epilogue: found_inf and the norm partials are there
+                    args = entry["args_fused"]
+                elif ep is not None or dp._epilogue_key is not None:
+                    # (re)configure for the NEXT backward; this step still runs its own pass 1
+                    if ep is not None and dp._configure_epilogue(ep["key"], loss_scale, found_inf, ep["partial_base"],
+                                                                 _clip_by_global_norm_using_mp_type()):
+                        if entry["args_fused"] is None:
+                            entry["args_fused"] = self._tail_args(entry["pg"], found_inf, loss_scale,
+                                                                  keep_beta_pow=False,
+                                                                  pass1_partials=dp._epilogue_partials)
+                    elif ep is None:
+                        dp._configure_epilogue(None)
+                    else:
+                        entry["epilogue"] = None  # this reducer cannot carry it (NCCL / NVLS backend, arena mode)
             ev = self._launch_events
             if ev is not None:  # measurement hook: CUDA events right around each launch (after its stream wait)
                 a, b = ev.pop()
@@ -197,34 +221,58 @@ class Optimizer:
             else:
                 call("prb_dp_step_tail", args[0], args[1], args[2], lr_ref, *args[4:16], stream)
 
+    def _hyper_key(self):
+        return (float(self._beta1), float(self._beta2), float(self._epsilon), float(self._coeff()),
+                id(getattr(self, "_lr_ratio", None)), id(getattr(self, "_apply_decay_param_fun", None)))
+
     def _tensor_attrs(self, pg):
         lr_ratio = np.ones(len(pg), np.float32)
         with_decay = np.ones(len(pg), np.uint8)
         return lr_ratio, with_decay
 
     def _build_plan(self, pg, found_inf, loss_scale):
-        """-> list of (DataParallel or None, group index or None, argument block), or None for the slow path."""
+        """-> list of plan entries {dp, group, args, pg, epilogue, args_fused}, or None for the slow path."""
         uniform = len({p.dtype for p, _ in pg}) == 1 and len({g.dtype for _, g in pg}) == 1 and \
             len({self._find_master(p) for p, _ in pg}) == 1
         clip = self._grad_clip
         if not uniform or (clip is not None and not all(p.need_clip is not False for p, _ in pg)):
             return None
-        # Gradients that sit in a DataParallel bucket arena of a multi-rank job: without a global dependency
-        # (no clip, no AMP) each bucket's parameters are updated as soon as THAT bucket's allreduce is done,
-        # overlapping the allreduce of the buckets behind it.
-        dp = pg[0][0]._bucket[0]
-        if dp is not None and dp.pipelined:
-            if clip is None and loss_scale is None and found_inf is None:
-                by_group = {}
-                for p, g in pg:
-                    by_group.setdefault(p._bucket[1], []).append((p, g))
-                order = sorted(by_group)
-                return [(dp, gi, self._tail_args(by_group[gi], None, None, keep_beta_pow=k != len(order) - 1))
-                        for k, gi in enumerate(order)]
-            return [(dp, None, self._tail_args(pg, found_inf, loss_scale, keep_beta_pow=False))]
-        return [(None, None, self._tail_args(pg, found_inf, loss_scale, keep_beta_pow=False))]
 
-    def _tail_args(self, pg, found_inf, loss_scale, keep_beta_pow):
+        def entry(dp, gi, sub, fi, ls, keep, ep=None):
+            return {"dp": dp, "group": gi, "pg": sub, "epilogue": ep, "args_fused": None,
+                    "args": self._tail_args(sub, fi, ls, keep_beta_pow=keep)}
+
+        # Gradients that sit in a DataParallel bucket arena: without a global dependency (no clip, no AMP) each
+        # bucket's parameters are updated as soon as THAT bucket's allreduce is done, overlapping the allreduce of
+        # the buckets behind it.  With a global dependency the producer of the buckets carries pass 1 (epilogue).
+        dp = pg[0][0]._bucket[0]
+        if dp is None:
+            return [entry(None, None, pg, found_inf, loss_scale, False)]
+        needs_pass1 = clip is not None or loss_scale is not None
+        if dp.pipelined and not needs_pass1 and found_inf is None:
+            by_group = {}
+            for p, g in pg:
+                by_group.setdefault(p._bucket[1], []).append((p, g))
+            order = sorted(by_group)
+            return [entry(dp, gi, by_group[gi], None, None, k != len(order) - 1) for k, gi in enumerate(order)]
+        ep = None
+        # AMP already unscaled by an explicit scaler.unscale_() (found_inf without loss_scale): the check and the norm
+        # must see what that call left behind, so the producer cannot have done them
+        if self._use_producer_pass1 and needs_pass1 and not (found_inf is not None and loss_scale is None):
+            index = {id(p): i for i, p in enumerate(dp._parameters)}
+            if len(pg) == len(index) and all(id(p) in index for p, _ in pg):
+                chunk = lib.prb_grad_chunk_elems()
+                base = np.zeros(len(pg), np.int32)
+                at = 0
+                for p, _ in pg:
+                    base[index[id(p)]] = at
+                    at += (p.numel + chunk - 1) // chunk
+                ep = {"key": (id(self), loss_scale.data_ptr if loss_scale is not None else 0, clip is not None,
+                              _clip_by_global_norm_using_mp_type()),
+                      "partial_base": base if clip is not None else None}
+        return [entry(dp, None, pg, found_inf, loss_scale, False, ep)]
+
+    def _tail_args(self, pg, found_inf, loss_scale, keep_beta_pow, pass1_partials=None):
         """ctypes argument block of one prb_dp_step_tail call (kept alive by the plan that holds it)."""
         clip = self._grad_clip
         params = [p for p, _ in pg]
@@ -245,6 +293,8 @@ class Optimizer:
                                    and not self._zero_grads_in_step)
         cfg.zero_grads = int(self._zero_grads_in_step)
         cfg.keep_beta_pow = int(keep_beta_pow)
+        if pass1_partials is not None:
+            cfg.pass1_done, cfg.pass1_partials = 1, pass1_partials.data_ptr
         lr_ratio, with_decay = self._tensor_attrs(pg)
         acc = [self._accumulators[p.name] for p in params]
         keep = {
@@ -256,8 +306,7 @@ class Optimizer:
             "ls": None, "fi": None, "gn": None, "cl": None,
         }
         if clip is not None:
-            if clip.last_global_norm is None:
-                clip.last_global_norm, clip.last_clip = Tensor.zeros(1, FLOAT32), Tensor.zeros(1, FLOAT32)
+            clip._ensure_outputs()
             keep["gn"], keep["cl"] = clip.last_global_norm.prb, clip.last_clip.prb
         if loss_scale is not None:
             keep["ls"] = loss_scale.prb
