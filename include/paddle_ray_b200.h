@@ -296,13 +296,18 @@ int32_t prb_reducer_group_of(const PRB_Reducer* r, int64_t var_index, int64_t* o
  * over NVLink peer memory (CUDA IPC; the default), 3 = the library's kernel over NVLink multicast (NVLS: the switch
  * adds and replicates).  PRB_ALLREDUCE = nvls | nvlink | nccl picks the first level to try; each level falls back
  * to the next, collectively, when it cannot be set up (single node, one GPU per process required for 2 and 3).
- * prb_reducer_comm_error reports (synchronously) whether a wait inside those kernels ever ran into its time limit,
- * i.e. a peer never arrived. */
+ * A wait inside those kernels that runs into its time limit (PRB_NVL_TIMEOUT_MS, default 600 000: a peer is gone)
+ * does not fall through to the reduction: the rank leaves the data untouched, tells its peers (they fail at once),
+ * and marks the exchange dead.  prb_reducer_comm_error reports that state without synchronising (a mapped host
+ * word); prb_reducer_prepare_for_backward and prb_reducer_wait_group check it and fail with PRB_EXTERNAL. */
 int32_t prb_reducer_allreduce_backend(const PRB_Reducer* r);
 /* Only the allreduce of one group's bucket region, in place, on `stream` (measurement aid: lets a benchmark time
  * the exchange step of ref reducer.cc:1058 by itself with either backend). */
 int32_t prb_reducer_allreduce_group(PRB_Reducer* r, int64_t group_index, void* stream);
 int32_t prb_reducer_comm_error(PRB_Reducer* r, int32_t* out);
+/* Cap on the grid of the library's exchange kernel (0 = one CTA per SM, the default).  A job whose backward pass
+ * needs every SM can trade exchange bandwidth for room (NCCL runs 16-32 CTAs). */
+int32_t prb_reducer_set_exchange_ctas(PRB_Reducer* r, int32_t max_ctas);
 /* 1 when every group of the current backward has been launched and finalised. */
 int32_t prb_reducer_is_finalized(const PRB_Reducer* r);
 /* Device address / element offset of parameter i's slot inside the bucket arena. */

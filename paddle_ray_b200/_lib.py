@@ -100,6 +100,7 @@ SIGNATURES = {
     "prb_reducer_allreduce_backend": [_vp],
     "prb_reducer_allreduce_group": [_vp, _i64, _vp],
     "prb_reducer_comm_error": [_vp, C.POINTER(_i32)],
+    "prb_reducer_set_exchange_ctas": [_vp, _i32],
     "prb_reducer_is_finalized": [_vp],
     "prb_reducer_bucket_view": [_vp, _i64, _T],
     "prb_reducer_launched_groups": [_vp, _vp, _i64, _vp],

@@ -7,27 +7,6 @@
 namespace prb {
 namespace {
 
-// Scale of the pack (mode 2): out = T(scale * (MT(x) + bias))   (ref scale_kernel.cu:35-40, bias_after_scale = false)
-template <typename T>
-__device__ __forceinline__ T pack_scale_elem(T raw, float scale, float bias) {
-  return Conv<T>::from_f32(__fmul_rn(scale, __fadd_rn(Conv<T>::to_f32(raw), bias)));
-}
-template <typename T>
-__device__ __forceinline__ void pack_scale_vec(Pack<T>& v, float scale, float bias) {
-  if constexpr (sizeof(T) == 2) {
-    uint32_t* w = reinterpret_cast<uint32_t*>(v.v);
-#pragma unroll
-    for (int j = 0; j < kVec / 2; ++j) {
-      float lo, hi;
-      Pair<T>::unpack(w[j], lo, hi);
-      w[j] = Pair<T>::pack_rn(__fmul_rn(scale, __fadd_rn(lo, bias)), __fmul_rn(scale, __fadd_rn(hi, bias)));
-    }
-  } else {
-#pragma unroll
-    for (int j = 0; j < kVec; ++j) v.v[j] = pack_scale_elem<T>(v.v[j], scale, bias);
-  }
-}
-
 // kMode 0: read only.  1: store the unscaled value (check_finite_and_unscale_).  2: the reducer's pack -- store
 // T(scale * (x + bias)) into the bucket slot and run the check + norm on the value just stored.
 template <typename T, int kMode, bool kNorm, bool kMp>

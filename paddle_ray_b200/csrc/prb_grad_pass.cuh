@@ -126,6 +126,27 @@ struct Pair<__half> {
   }
 };
 
+// Scale of the pack (mode 2): out = T(scale * (MT(x) + bias))   (ref scale_kernel.cu:35-40, bias_after_scale = false)
+template <typename T>
+__device__ __forceinline__ T pack_scale_elem(T raw, float scale, float bias) {
+  return Conv<T>::from_f32(__fmul_rn(scale, __fadd_rn(Conv<T>::to_f32(raw), bias)));
+}
+template <typename T>
+__device__ __forceinline__ void pack_scale_vec(Pack<T>& v, float scale, float bias) {
+  if constexpr (sizeof(T) == 2) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(v.v);
+#pragma unroll
+    for (int j = 0; j < kVec / 2; ++j) {
+      float lo, hi;
+      Pair<T>::unpack(w[j], lo, hi);
+      w[j] = Pair<T>::pack_rn(__fmul_rn(scale, __fadd_rn(lo, bias)), __fmul_rn(scale, __fadd_rn(hi, bias)));
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < kVec; ++j) v.v[j] = pack_scale_elem<T>(v.v[j], scale, bias);
+  }
+}
+
 // Per-thread state of the check + norm of one chunk.  A thread feeds it its lane vectors in the order
 // u = 0 .. kGradUnroll-1 (vector index u * kGradThreads + threadIdx.x), then (one thread in eight) the ragged
 // tail element; finish() does the CTA-wide part.  Whoever follows this protocol produces the same bits.

@@ -1,4 +1,4 @@
-// In-place bucket allreduce over NVLink peer memory (single node, one process per GPU).
+// In-place bucket exchange (allreduce) over NVLink peer memory (single node, one process per GPU).
 //
 // The reference hands every bucket to ncclAllReduce (ref: process_group_nccl.cc:841-865).  On an
 // NVSwitch box every GPU can load and store every peer's memory at NVLink speed, so the reducer's
@@ -6,204 +6,276 @@
 // written as one kernel per rank:
 //
 //   ready barrier   every rank tells its peers "my packed bucket is complete" (the kernel runs after the
-//                   pack in stream order) and waits for theirs;
-//   reduce-scatter  rank r owns slice r of the bucket: it loads that slice from ALL ranks' arenas
-//                   (256-/128-bit peer loads), adds the values in rank order 0..n-1 in fp32 -- a fixed
-//                   order, so the result does not depend on who computes it -- rounds once to T ...
+//                   pack in stream order) and waits for theirs (one warp does the talking, prb_nvl_common.cuh);
+//   reduce-scatter  rank r owns a slice of the bucket: it loads that slice from ALL ranks' arenas
+//                   (256-/128-bit loads, ~8-16 of them in flight per thread), adds the values in rank order
+//                   0..n-1 in fp32 -- a fixed order, so the result does not depend on who computes it --
+//                   rounds once to T ...
 //   all-gather      ... and stores the reduced vector straight into every rank's arena (peer stores);
 //   done barrier    the last CTA of each rank publishes "all my stores are out"; a rank's kernel ends
 //                   only after every peer has published, so the next kernel in the stream (the optimizer)
 //                   sees the complete reduced bucket.
 //
+// Two things ride on the reduced value while the slice owner holds it in registers:
+//   * the 1/nranks scale of gradients that were produced in the arena (each rank's value goes through
+//     T(scale * (x + 0)) before the add: ScaleFunctor's rounding, ref scale_kernel.cu:24-41), so that mode needs
+//     no pass of its own for the scale;
+//   * producer-side pass 1 (chunk mode): check_finite_and_unscale's inf/nan test and the squared-norm partial of
+//     every 8192-element chunk (ChunkEpilogue, prb_grad_pass.cuh), stored into EVERY rank's sidecar with the same
+//     peer stores -- the gradient is not read again before the update pass, and the bits equal those of a
+//     separate pass over the reduced bucket.
+//
 // Per rank and bucket of S bytes: (n-1)/n * S over NVLink in each direction, no staging copies, no
-// extra HBM pass.  Barriers are 64-bit sequence numbers written with st.release.sys into the peer's
-// signal block and polled with ld.acquire.sys; every wait has a time limit (a missing peer turns into
-// an error flag, never into a hung GPU).  Results are bit-equal across ranks by construction and equal
-// to NCCL's for two ranks (one addition); for more ranks the fp32 accumulation with one final rounding
-// is at least as accurate as pairwise sums in T.
+// extra HBM pass.  Results are bit-equal across ranks by construction and equal to NCCL's for two ranks (one
+// addition); for more ranks the fp32 accumulation with one final rounding is at least as accurate as pairwise
+// sums in T.
 //
 // The default for multi-rank reducers (PRB_ALLREDUCE=nccl forces NCCL).  Needs CUDA IPC between the ranks;
 // falls back to NCCL if any rank cannot set it up -- the decision is taken collectively.
+#include "prb_grad_pass.cuh"
 #include "prb_nvl_common.cuh"
 
 namespace prb {
 namespace {
 
+static_assert(kNvlThreads == kGradThreads, "the exchange kernel produces norm partials with the grad-pass CTA shape");
+
 struct NvlArgs {
-  char* arena[kMaxRanks];              // every rank's bucket arena as mapped into this process
-  Signals* sig[kMaxRanks];             // every rank's signal block
-  int nranks, rank;
-  int parallel_release;        // see done_barrier
-  size_t region_off;                   // byte offset of the bucket inside the arena
-  long long nvec;                      // 8-element vectors in the bucket
-  unsigned long long seq;
+  Bar bar;
+  char* arena[kMaxRanks];  // every rank's bucket arena as mapped into this process
+  // flat mode
+  size_t region_off;       // byte offset of the bucket inside the arena
+  long long nvec;          // 8-element vectors in the bucket
+  // chunk mode
+  const GradDesc* descs;
+  const Chunk* chunks;
+  int nchunks;
+  // scale fold
+  float scale, bias;
+  // epilogue
+  const float* loss_scale;
+  bool* found_local;
+  size_t partials_off, flags_off;
 };
 
-// Peer loads/stores: plain (coherent at system scope after the barriers), 8 elements per access.
+// Loads in flight per thread.  NVLink latency is ~2 us: a thread that waits for ONE remote vector at a time
+// moves ~230 GB/s per GPU at two ranks (round-2 measurement), so the number of lane vectors a thread handles per
+// round grows as the rank count shrinks: ~8 loads of 32 bytes (fp32) or ~16 loads of 16 bytes (16-bit types).
+template <typename T, int kRanks>
+struct Flight {
+  static constexpr int kTarget = sizeof(T) == 4 ? 8 : 16;
+  static constexpr int kVecs = (kTarget / kRanks) < 1 ? 1 : ((kTarget / kRanks) > kGradUnroll ? kGradUnroll : (kTarget / kRanks));
+};
+
+// Loads of the vector at byte offset `off` from every rank's arena (issued, not yet used).
+// kRanks is the communicator size rounded up to 2, 4 or 8; surplus slots are skipped at run time.
+template <typename T, int kRanks>
+__device__ __forceinline__ void load_all(const NvlArgs& a, size_t off, Pack<T> (&in)[kRanks]) {
+#pragma unroll
+  for (int q = 0; q < kRanks; ++q)
+    if (q < a.bar.nranks) load_vec<T>(reinterpret_cast<const T*>(a.arena[q] + off), in[q]);
+}
+
+// Sum over ranks in rank order (a fixed order: the same on every rank), rounded once to T.
+template <typename T, int kRanks, bool kFold>
+__device__ __forceinline__ void combine(const NvlArgs& a, Pack<T> (&in)[kRanks], Pack<T>& out) {
+  float acc[kVec];
+#pragma unroll
+  for (int q = 0; q < kRanks; ++q) {
+    if (q < a.bar.nranks) {
+      if (kFold) pack_scale_vec<T>(in[q], a.scale, a.bias);
+#pragma unroll
+      for (int j = 0; j < kVec; ++j) {
+        const float x = Conv<T>::to_f32(in[q].v[j]);
+        acc[j] = (q == 0) ? x : __fadd_rn(acc[j], x);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kVec; ++j) out.v[j] = Conv<T>::from_f32(acc[j]);
+}
+
+// One element straight from memory (never from a stale L1 line): the ragged tail path.
 template <typename T>
-__device__ __forceinline__ void peer_load(const T* p, Pack<T>& o) {
-  uint32_t* w = reinterpret_cast<uint32_t*>(o.v);
+__device__ __forceinline__ T load_elem_cv(const char* p) {
   if constexpr (sizeof(T) == 4) {
-    asm volatile("ld.global.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-                 : "l"(p));
+    uint32_t w = *reinterpret_cast<const volatile uint32_t*>(p);
+    return *reinterpret_cast<T*>(&w);
   } else {
-    asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p));
+    uint16_t w = *reinterpret_cast<const volatile uint16_t*>(p);
+    return *reinterpret_cast<T*>(&w);
   }
 }
 
 template <typename T, int kRanks>
-__global__ void __launch_bounds__(kNvlThreads, kNvlMinCtasPerSm) nvl_allreduce_kernel(const NvlArgs a) {
-  Signals* mine = a.sig[a.rank];
-  const int slot = (int)(a.seq & (kSlots - 1));
-  // ---- ready barrier
-  if (blockIdx.x == 0 && threadIdx.x < a.nranks) st_release_sys(&a.sig[threadIdx.x]->ready[slot][a.rank], a.seq);
-  if (threadIdx.x < a.nranks && !wait_at_least(&mine->ready[slot][threadIdx.x], a.seq)) mine->error = 1;
-  __syncthreads();
+__device__ __forceinline__ void store_all(const NvlArgs& a, size_t off, const Pack<T>& v) {
+#pragma unroll
+  for (int q = 0; q < kRanks; ++q)
+    if (q < a.bar.nranks) store_vec<T>(reinterpret_cast<T*>(a.arena[q] + off), v);
+}
 
-  // ---- reduce-scatter + all-gather of my slice
-  const long long v0 = a.nvec * a.rank / a.nranks, v1 = a.nvec * (a.rank + 1) / a.nranks;
+// ---- flat mode: rank r owns the r-th n-th of the region
+template <typename T, int kRanks, bool kFold>
+__global__ void __launch_bounds__(kNvlThreads, 2) nvl_exchange_kernel(const NvlArgs a) {
+  const int slot = (int)(a.bar.seq & (kSlots - 1));
+  if (!ready_barrier(a.bar, slot)) return;
+  const long long v0 = a.nvec * a.bar.rank / a.bar.nranks, v1 = a.nvec * (a.bar.rank + 1) / a.bar.nranks;
   const long long stride = (long long)gridDim.x * kNvlThreads;
-  for (long long v = v0 + (long long)blockIdx.x * kNvlThreads + threadIdx.x; v < v1; v += stride) {
-    const size_t off = a.region_off + (size_t)v * kVec * sizeof(T);
-    // kRanks is the communicator size rounded up to 2, 4 or 8; surplus slots are skipped at run time.
-    // Peers are loaded four at a time (all four loads in flight together) and added in rank order.
-    constexpr int kBatch = kRanks > 4 ? 4 : kRanks;
-    float acc[kVec];
+  constexpr int kV = Flight<T, kRanks>::kVecs;
+  for (long long v = v0 + (long long)blockIdx.x * kNvlThreads + threadIdx.x; v < v1; v += stride * kV) {
+    Pack<T> in[kV][kRanks];
 #pragma unroll
-    for (int b = 0; b < kRanks; b += kBatch) {
-      Pack<T> in[kBatch];
+    for (int u = 0; u < kV; ++u)
+      if (v + u * stride < v1) load_all<T, kRanks>(a, a.region_off + (size_t)(v + u * stride) * kVec * sizeof(T), in[u]);
 #pragma unroll
-      for (int q = 0; q < kBatch; ++q)
-        if (b + q < a.nranks) peer_load<T>(reinterpret_cast<const T*>(a.arena[b + q] + off), in[q]);
+    for (int u = 0; u < kV; ++u) {
+      if (v + u * stride < v1) {
+        Pack<T> out;
+        combine<T, kRanks, kFold>(a, in[u], out);
+        store_all<T, kRanks>(a, a.region_off + (size_t)(v + u * stride) * kVec * sizeof(T), out);
+      }
+    }
+  }
+  done_barrier(a.bar, slot);
+}
+
+// ---- chunk mode: rank r owns the r-th n-th of the (tensor, 8192-element chunk) list; one CTA per chunk at a
+// time, with exactly the thread -> element assignment of grad_pass_kernel, so the partials are the same bits
+template <typename T, int kRanks, bool kFold, bool kNorm, bool kMp>
+__global__ void __launch_bounds__(kNvlThreads, 2) nvl_exchange_chunks_kernel(const NvlArgs a) {
+  __shared__ float red[kNvlThreads / 32];
+  const int slot = (int)(a.bar.seq & (kSlots - 1));
+  if (!ready_barrier(a.bar, slot)) return;
+  const int n = a.bar.nranks, r = a.bar.rank;
+  const int c0 = (int)((long long)a.nchunks * r / n), c1 = (int)((long long)a.nchunks * (r + 1) / n);
+  const char* my_arena = a.arena[r];
+  for (int c = c0 + (int)blockIdx.x; c < c1; c += (int)gridDim.x) {
+    const int4 craw = __ldg(reinterpret_cast<const int4*>(a.chunks) + c);
+    const int cn = craw.y;
+    const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
+    const GradDesc* __restrict__ d = a.descs + craw.x;
+    const size_t off = (size_t)(reinterpret_cast<const char*>(d->x) - my_arena) + (size_t)offset * sizeof(T);
+    ChunkEpilogue<T, kNorm, kMp> ep;
+    ep.begin(a.loss_scale);
+    const int nvec = cn / kVec;
+    constexpr int kV = Flight<T, kRanks>::kVecs;
+#pragma unroll 1
+    for (int u0 = 0; u0 < kGradUnroll; u0 += kV) {
+      Pack<T> in[kV][kRanks];
 #pragma unroll
-      for (int q = 0; q < kBatch; ++q) {
-        if (b + q < a.nranks) {
+      for (int u = 0; u < kV; ++u) {
+        const int i = (u0 + u) * kNvlThreads + threadIdx.x;
+        if (i < nvec) load_all<T, kRanks>(a, off + (size_t)i * kVec * sizeof(T), in[u]);
+      }
 #pragma unroll
-          for (int j = 0; j < kVec; ++j) {
-            const float x = Conv<T>::to_f32(in[q].v[j]);
-            acc[j] = (b + q == 0) ? x : __fadd_rn(acc[j], x);  // rank order: the same on every rank
-          }
+      for (int u = 0; u < kV; ++u) {  // reduce, store and feed the epilogue in the order u = 0, 1, 2, 3
+        const int i = (u0 + u) * kNvlThreads + threadIdx.x;
+        if (i < nvec) {
+          Pack<T> v;
+          combine<T, kRanks, kFold>(a, in[u], v);
+          store_all<T, kRanks>(a, off + (size_t)i * kVec * sizeof(T), v);
+          ep.vec(v);
         }
       }
     }
-    Pack<T> out;
-#pragma unroll
-    for (int j = 0; j < kVec; ++j) out.v[j] = Conv<T>::from_f32(acc[j]);
-#pragma unroll
-    for (int q = 0; q < kRanks; ++q)
-      if (q < a.nranks) store_vec<T>(reinterpret_cast<T*>(a.arena[q] + off), out);
+    const int e = nvec * kVec + threadIdx.x;
+    if (e < cn) {  // ragged tail of the tensor's last chunk (the slot's zero padding is never touched)
+      const size_t o = off + (size_t)e * sizeof(T);
+      float acc = 0.0f;
+      for (int q = 0; q < n; ++q) {
+        T x = load_elem_cv<T>(a.arena[q] + o);
+        if (kFold) x = pack_scale_elem<T>(x, a.scale, a.bias);
+        acc = (q == 0) ? Conv<T>::to_f32(x) : __fadd_rn(acc, Conv<T>::to_f32(x));
+      }
+      const T out = Conv<T>::from_f32(acc);
+      for (int q = 0; q < n; ++q) *reinterpret_cast<T*>(a.arena[q] + o) = out;
+      ep.elem(out);
+    }
+    bool any_bad;
+    const float s = ep.finish(red, &any_bad);
+    if (threadIdx.x == 0) {
+      if (kNorm) {
+        const size_t po = a.partials_off + ((size_t)d->partial_base + (size_t)(offset / kGradChunk)) * sizeof(float);
+        for (int q = 0; q < n; ++q) *reinterpret_cast<float*>(a.arena[q] + po) = s;
+      }
+      if (any_bad)  // only "set" is ever written, so concurrent stores are benign (ref amp_kernel.cu:79-81)
+        for (int q = 0; q < n; ++q) *reinterpret_cast<unsigned int*>(a.arena[q] + a.flags_off) = 1u;
+    }
   }
-
-  // ---- done barrier: my stores are out (last CTA publishes), then wait for every peer's
-  done_barrier(a, mine, slot);
+  const bool last = done_barrier(a.bar, slot);
+  // every peer's stores are out: the flag in MY sidecar is the OR over all slices of all ranks so far in this step
+  if (last && threadIdx.x == 0 && a.found_local != nullptr &&
+      *reinterpret_cast<const volatile unsigned int*>(my_arena + a.flags_off) != 0u)
+    *a.found_local = true;
 }
 
 }  // namespace
 
 struct NvlContext {
   NvlArgs args;
-  void* opened[2 * kMaxRanks];
+  SignalSet sigs;
+  void* opened[kMaxRanks];
   int nopened = 0;
-  Signals* my_signals = nullptr;
   unsigned long long seq = 0;
   int ctas = 0;
 };
 
-int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, size_t arena_bytes, cudaStream_t stream,
-                  NvlContext** out) {
-  *out = nullptr;
-  if (nranks < 2 || nranks > kMaxRanks) return PRB_SUCCESS;  // nothing to set up: caller keeps NCCL
-  (void)arena_bytes;
-  NvlContext* c = new NvlContext();
-  memset(&c->args, 0, sizeof(c->args));
-  int ok = 1;
-  cudaIpcMemHandle_t mine[2];
-  if (cudaMalloc((void**)&c->my_signals, sizeof(Signals)) != cudaSuccess) ok = 0;
-  if (ok && cudaMemset(c->my_signals, 0, sizeof(Signals)) != cudaSuccess) ok = 0;
-  if (ok && cudaIpcGetMemHandle(&mine[0], arena) != cudaSuccess) ok = 0;
-  if (ok && cudaIpcGetMemHandle(&mine[1], c->my_signals) != cudaSuccess) ok = 0;
-  cudaGetLastError();
-  // exchange {ok, handles} through the communicator (collective: every rank takes part even when it failed)
-  struct Packet {
-    int ok, pad;
-    cudaIpcMemHandle_t h[2];
-  } pk, all[kMaxRanks];
-  memset(&pk, 0, sizeof(pk));
-  pk.ok = ok;
-  if (ok) {
-    pk.h[0] = mine[0];
-    pk.h[1] = mine[1];
-  }
-  void *dsend = nullptr, *drecv = nullptr;
-  PRB_CUDA(cudaMalloc(&dsend, sizeof(Packet)));
-  PRB_CUDA(cudaMalloc(&drecv, sizeof(Packet) * nranks));
-  PRB_CUDA(cudaMemcpyAsync(dsend, &pk, sizeof(Packet), cudaMemcpyHostToDevice, stream));
-  PRB_TRY(nc.all_gather_bytes(nc.comm, dsend, drecv, sizeof(Packet), stream));
-  PRB_CUDA(cudaMemcpyAsync(all, drecv, sizeof(Packet) * nranks, cudaMemcpyDeviceToHost, stream));
-  PRB_CUDA(cudaStreamSynchronize(stream));
-  cudaFree(dsend);
-  cudaFree(drecv);
-  for (int q = 0; q < nranks; ++q) ok = ok && all[q].ok;
-  if (ok) {
-    for (int q = 0; q < nranks && ok; ++q) {
-      if (q == rank) {
-        c->args.arena[q] = reinterpret_cast<char*>(arena);
-        c->args.sig[q] = c->my_signals;
-        continue;
-      }
-      void *pa = nullptr, *ps = nullptr;
-      if (cudaIpcOpenMemHandle(&pa, all[q].h[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
-      if (ok) c->opened[c->nopened++] = pa;
-      if (ok && cudaIpcOpenMemHandle(&ps, all[q].h[1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
-      if (ok) c->opened[c->nopened++] = ps;
-      c->args.arena[q] = reinterpret_cast<char*>(pa);
-      c->args.sig[q] = reinterpret_cast<Signals*>(ps);
-    }
-    cudaGetLastError();
-  }
-  // second agreement round: did everybody manage to map everybody?
-  int agreed = 0;
-  PRB_TRY(nc.all_min_int(nc.comm, ok, &agreed, stream));
-  if (!agreed) {
-    nvl_destroy(c);
-    return PRB_SUCCESS;  // *out stays NULL: the caller keeps using NCCL
-  }
-  c->args.nranks = nranks;
-  c->args.rank = rank;
-  c->args.parallel_release = 1;
-  if (const char* e = getenv("PRB_NVL_PARALLEL_RELEASE")) c->args.parallel_release = atoi(e) != 0;
-  int per_sm = kNvlCtasPerSm;
-  if (const char* e = getenv("PRB_NVL_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
-  c->ctas = sm_count() * per_sm;
-  *out = c;
-  return PRB_SUCCESS;
+bool nvl_remote_domain() {
+  static const bool v = [] {
+    const char* e = getenv("PRB_NVL_DOMAIN");
+    return !(e != nullptr && strcmp(e, "default") == 0);
+  }();
+  return v;
 }
 
-int32_t signals_setup(const NvlCollectives& nc, int nranks, int rank, cudaStream_t stream, SignalSet* out, int* ok_out) {
+unsigned long long nvl_timeout_ns() {
+  static const unsigned long long v = [] {
+    const char* e = getenv("PRB_NVL_TIMEOUT_MS");
+    const long long ms = e ? atoll(e) : 600000ll;
+    return (unsigned long long)(ms > 0 ? ms : 600000ll) * 1000000ull;
+  }();
+  return v;
+}
+
+// Exchange one fixed-size packet per rank through the communicator.  Takes part in the collective whatever the
+// local state; returns false if anything local or the collective itself failed.
+static bool gather_packets(const NvlCollectives& nc, const void* mine, void* all, size_t bytes, int nranks, cudaStream_t stream) {
+  void *dsend = nullptr, *drecv = nullptr;
+  bool ok = cudaMalloc(&dsend, bytes) == cudaSuccess && cudaMalloc(&drecv, bytes * nranks) == cudaSuccess;
+  if (ok) ok = cudaMemcpyAsync(dsend, mine, bytes, cudaMemcpyHostToDevice, stream) == cudaSuccess;
+  // a rank that could not even allocate still has to enter the collective: it sends from a spare buffer
+  static char* spare = nullptr;
+  if (!ok && spare == nullptr) cudaMalloc((void**)&spare, 4096 * (size_t)(kMaxRanks + 1));
+  const bool coll_ok = nc.all_gather_bytes(nc.comm, ok ? dsend : spare, ok ? drecv : spare + 4096, bytes, stream) == PRB_SUCCESS;
+  if (ok && coll_ok) ok = cudaMemcpyAsync(all, drecv, bytes * nranks, cudaMemcpyDeviceToHost, stream) == cudaSuccess;
+  if (cudaStreamSynchronize(stream) != cudaSuccess) ok = false;
+  if (dsend) cudaFree(dsend);
+  if (drecv) cudaFree(drecv);
+  cudaGetLastError();
+  return ok && coll_ok;
+}
+
+void signals_setup(const NvlCollectives& nc, int nranks, int rank, cudaStream_t stream, SignalSet* out, int* ok_out) {
   int ok = 1;
   cudaIpcMemHandle_t mine;
   memset(&mine, 0, sizeof(mine));
   if (cudaMalloc((void**)&out->mine, sizeof(Signals)) != cudaSuccess) ok = 0;
   if (ok && cudaMemset(out->mine, 0, sizeof(Signals)) != cudaSuccess) ok = 0;
   if (ok && cudaIpcGetMemHandle(&mine, out->mine) != cudaSuccess) ok = 0;
+  if (ok && cudaHostAlloc((void**)&out->host_error, sizeof(unsigned int), cudaHostAllocMapped) == cudaSuccess) {
+    *out->host_error = 0u;
+    if (cudaHostGetDevicePointer((void**)&out->host_error_dev, out->host_error, 0) != cudaSuccess) out->host_error_dev = nullptr;
+  }
   cudaGetLastError();
   struct Packet {
     int ok, pad;
     cudaIpcMemHandle_t h;
   } pk, all[kMaxRanks];
   memset(&pk, 0, sizeof(pk));
+  memset(all, 0, sizeof(all));
   pk.ok = ok;
   pk.h = mine;
-  void *dsend = nullptr, *drecv = nullptr;
-  PRB_CUDA(cudaMalloc(&dsend, sizeof(Packet)));
-  PRB_CUDA(cudaMalloc(&drecv, sizeof(Packet) * nranks));
-  PRB_CUDA(cudaMemcpyAsync(dsend, &pk, sizeof(Packet), cudaMemcpyHostToDevice, stream));
-  PRB_TRY(nc.all_gather_bytes(nc.comm, dsend, drecv, sizeof(Packet), stream));
-  PRB_CUDA(cudaMemcpyAsync(all, drecv, sizeof(Packet) * nranks, cudaMemcpyDeviceToHost, stream));
-  PRB_CUDA(cudaStreamSynchronize(stream));
-  cudaFree(dsend);
-  cudaFree(drecv);
+  if (!gather_packets(nc, &pk, all, sizeof(Packet), nranks, stream)) ok = 0;
   for (int q = 0; q < nranks; ++q) ok = ok && all[q].ok;
   for (int q = 0; q < nranks && ok; ++q) {
     if (q == rank) {
@@ -217,7 +289,6 @@ int32_t signals_setup(const NvlCollectives& nc, int nranks, int rank, cudaStream
   }
   cudaGetLastError();
   *ok_out = ok;
-  return PRB_SUCCESS;
 }
 
 void signals_destroy(SignalSet* s) {
@@ -225,50 +296,154 @@ void signals_destroy(SignalSet* s) {
   s->nopened = 0;
   if (s->mine) cudaFree(s->mine);
   s->mine = nullptr;
+  if (s->host_error) cudaFreeHost(s->host_error);
+  s->host_error = nullptr;
+}
+
+void fill_bar(const SignalSet& s, int nranks, int rank, Bar* b) {
+  for (int q = 0; q < kMaxRanks; ++q) b->sig[q] = s.sig[q];
+  b->nranks = nranks;
+  b->rank = rank;
+  b->seq = 0;
+  b->timeout_ns = nvl_timeout_ns();
+  b->host_error = s.host_error_dev;
+}
+
+int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, size_t arena_bytes, cudaStream_t stream,
+                  NvlContext** out) {
+  *out = nullptr;
+  if (nranks < 2 || nranks > kMaxRanks) return PRB_SUCCESS;  // nothing to set up: caller keeps NCCL
+  (void)arena_bytes;
+  NvlContext* c = new NvlContext();
+  memset(&c->args, 0, sizeof(c->args));
+  // Every step below is collective: a local failure is folded into `ok` and the rank keeps taking part in every
+  // exchange and in the final vote, so that no peer is left waiting in a collective this rank has abandoned.
+  int ok = 1;
+  signals_setup(nc, nranks, rank, stream, &c->sigs, &ok);
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  if (ok && cudaIpcGetMemHandle(&mine, arena) != cudaSuccess) ok = 0;
+  cudaGetLastError();
+  struct Packet {
+    int ok, pad;
+    cudaIpcMemHandle_t h;
+  } pk, all[kMaxRanks];
+  memset(&pk, 0, sizeof(pk));
+  memset(all, 0, sizeof(all));
+  pk.ok = ok;
+  pk.h = mine;
+  if (!gather_packets(nc, &pk, all, sizeof(Packet), nranks, stream)) ok = 0;
+  for (int q = 0; q < nranks; ++q) ok = ok && all[q].ok;
+  for (int q = 0; q < nranks && ok; ++q) {
+    if (q == rank) {
+      c->args.arena[q] = reinterpret_cast<char*>(arena);
+      continue;
+    }
+    void* pa = nullptr;
+    if (cudaIpcOpenMemHandle(&pa, all[q].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
+    if (ok) c->opened[c->nopened++] = pa;
+    c->args.arena[q] = reinterpret_cast<char*>(pa);
+  }
+  cudaGetLastError();
+  // final agreement: did everybody manage to map everybody?
+  int agreed = 0;
+  const int32_t vote = nc.all_min_int(nc.comm, ok, &agreed, stream);
+  if (vote != PRB_SUCCESS || !agreed) {
+    nvl_destroy(c);
+    return vote;  // *out stays NULL: the caller keeps using NCCL (or reports the broken communicator)
+  }
+  fill_bar(c->sigs, nranks, rank, &c->args.bar);
+  int per_sm = 1;  // the kernel is NVLink-bound and mostly waits: more CTAs only take registers from the optimizer
+  if (const char* e = getenv("PRB_NVL_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
+  c->ctas = sm_count() * per_sm;
+  if (const char* e = getenv("PRB_NVL_CTAS")) c->ctas = atoi(e) > 0 ? atoi(e) : c->ctas;
+  *out = c;
+  return PRB_SUCCESS;
 }
 
 int nvl_next_slot(const NvlContext* c) { return c ? (int)((c->seq + 1) & (kSlots - 1)) : 0; }
 
-int32_t nvl_allreduce(NvlContext* c, size_t region_off_bytes, int64_t numel, int32_t dtype, cudaStream_t stream) {
-  PRB_ENFORCE(c != nullptr, PRB_INVALID_ARGUMENT, "nvlink allreduce: no context");
-  PRB_ENFORCE(numel % kVec == 0 && region_off_bytes % 32 == 0, PRB_INVALID_ARGUMENT,
-              "nvlink allreduce: the bucket must be a whole number of 8-element vectors at a 32-byte offset");
-  NvlArgs a = c->args;
-  a.region_off = region_off_bytes;
-  a.nvec = numel / kVec;
-  a.seq = ++c->seq;
-  const long long per_rank = (a.nvec + a.nranks - 1) / a.nranks;
-  int ctas = (int)((per_rank + kNvlThreads - 1) / kNvlThreads);
-  if (ctas > c->ctas) ctas = c->ctas;  // a few CTAs per SM, each looping over its share of the slice
-  if (ctas < 1) ctas = 1;
-#define PRB_NVL(T_)                                                                              \
-  do {                                                                                           \
-    if (a.nranks <= 2) nvl_allreduce_kernel<T_, 2><<<ctas, kNvlThreads, 0, stream>>>(a);         \
-    else if (a.nranks <= 4) nvl_allreduce_kernel<T_, 4><<<ctas, kNvlThreads, 0, stream>>>(a);    \
-    else nvl_allreduce_kernel<T_, 8><<<ctas, kNvlThreads, 0, stream>>>(a);                       \
-  } while (0)
-  switch (dtype) {
-    case PRB_FLOAT32: PRB_NVL(float); break;
-    case PRB_BFLOAT16: PRB_NVL(__nv_bfloat16); break;
-    case PRB_FLOAT16: PRB_NVL(__half); break;
-    default: PRB_FAIL(PRB_UNIMPLEMENTED, "nvlink allreduce: dtype %s is not built", dtype_name(dtype));
+void nvl_set_max_ctas(NvlContext* c, int max_ctas) {
+  if (c) c->ctas = max_ctas > 0 ? max_ctas : sm_count();
+}
+
+namespace {
+
+template <typename T, int kRanks>
+cudaError_t launch_exchange(const NvlArgs& a, const NvlWork& w, int ctas, cudaStream_t stream) {
+  if (w.table == nullptr) {
+    if (w.fold_scale) return nvl_launch(nvl_exchange_kernel<T, kRanks, true>, ctas, kNvlThreads, stream, a);
+    return nvl_launch(nvl_exchange_kernel<T, kRanks, false>, ctas, kNvlThreads, stream, a);
   }
-#undef PRB_NVL
+#define PRB_NVC(F)                                                                                                 \
+  do {                                                                                                             \
+    if (!w.norm) return nvl_launch(nvl_exchange_chunks_kernel<T, kRanks, F, false, false>, ctas, kNvlThreads, stream, a); \
+    if (!w.mp) return nvl_launch(nvl_exchange_chunks_kernel<T, kRanks, F, true, false>, ctas, kNvlThreads, stream, a);    \
+    return nvl_launch(nvl_exchange_chunks_kernel<T, kRanks, F, true, true>, ctas, kNvlThreads, stream, a);         \
+  } while (0)
+  if (w.fold_scale) PRB_NVC(true);
+  PRB_NVC(false);
+#undef PRB_NVC
+}
+
+template <typename T>
+cudaError_t launch_exchange_ranks(const NvlArgs& a, const NvlWork& w, int ctas, cudaStream_t stream) {
+  if (a.bar.nranks <= 2) return launch_exchange<T, 2>(a, w, ctas, stream);
+  if (a.bar.nranks <= 4) return launch_exchange<T, 4>(a, w, ctas, stream);
+  return launch_exchange<T, 8>(a, w, ctas, stream);
+}
+
+}  // namespace
+
+int32_t nvl_exchange(NvlContext* c, const NvlWork& w, cudaStream_t stream) {
+  PRB_ENFORCE(c != nullptr, PRB_INVALID_ARGUMENT, "nvlink exchange: no context");
+  PRB_ENFORCE(w.numel % kVec == 0 && w.region_off % 32 == 0, PRB_INVALID_ARGUMENT,
+              "nvlink exchange: the bucket must be a whole number of 8-element vectors at a 32-byte offset");
+  NvlArgs a = c->args;
+  a.region_off = w.region_off;
+  a.nvec = w.numel / kVec;
+  a.bar.seq = ++c->seq;
+  a.scale = w.scale;
+  a.bias = 0.0f;
+  int ctas;
+  if (w.table != nullptr) {
+    PRB_ENFORCE(w.loss_scale == nullptr || w.found_local != nullptr, PRB_INVALID_ARGUMENT,
+                "nvlink exchange: the finite check needs a found_inf flag");
+    a.descs = reinterpret_cast<const GradDesc*>(w.table->descs);
+    a.chunks = w.table->chunks;
+    a.nchunks = w.table->nchunks;
+    a.loss_scale = w.loss_scale;
+    a.found_local = w.found_local;
+    a.partials_off = w.partials_off;
+    a.flags_off = w.flags_off;
+    ctas = (a.nchunks + a.bar.nranks - 1) / a.bar.nranks;  // one CTA per chunk of my share, capped below
+  } else {
+    const long long per_rank = (a.nvec + a.bar.nranks - 1) / a.bar.nranks;
+    ctas = (int)((per_rank + kNvlThreads - 1) / kNvlThreads);
+  }
+  if (ctas > c->ctas) ctas = c->ctas;  // at most one CTA per SM, each looping over its share of the slice
+  if (ctas < 1) ctas = 1;
+  KernelTimer kt(KK_EXCHANGE, stream);
+  cudaError_t e;
+  switch (w.dtype) {
+    case PRB_FLOAT32: e = launch_exchange_ranks<float>(a, w, ctas, stream); break;
+    case PRB_BFLOAT16: e = launch_exchange_ranks<__nv_bfloat16>(a, w, ctas, stream); break;
+    case PRB_FLOAT16: e = launch_exchange_ranks<__half>(a, w, ctas, stream); break;
+    default: PRB_FAIL(PRB_UNIMPLEMENTED, "nvlink exchange: dtype %s is not built", dtype_name(w.dtype));
+  }
+  PRB_CUDA(e);
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 
-int32_t nvl_error_flag(NvlContext* c, int* out) {
-  unsigned int e = 0;
-  PRB_CUDA(cudaMemcpy(&e, &c->my_signals->error, sizeof(e), cudaMemcpyDeviceToHost));
-  *out = (int)e;
-  return PRB_SUCCESS;
+int nvl_error_flag(const NvlContext* c) {
+  return (c != nullptr && c->sigs.host_error != nullptr) ? (int)*reinterpret_cast<volatile unsigned int*>(c->sigs.host_error) : 0;
 }
 
 void nvl_destroy(NvlContext* c) {
   if (!c) return;
   for (int i = 0; i < c->nopened; ++i) cudaIpcCloseMemHandle(c->opened[i]);
-  if (c->my_signals) cudaFree(c->my_signals);
+  signals_destroy(&c->sigs);
   delete c;
 }
 

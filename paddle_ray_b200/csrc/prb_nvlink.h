@@ -1,6 +1,6 @@
-// Two-shot allreduce over NVLink peer memory for the reducer's bucket arena (see prb_nvlink.cu).
+// Two-shot bucket exchange over NVLink peer memory for the reducer's bucket arena (see prb_nvlink.cu).
 #pragma once
-#include "prb_common.cuh"
+#include "prb_plan.h"
 
 namespace prb {
 
@@ -13,17 +13,37 @@ struct NvlCollectives {
   int32_t (*all_min_int)(void* comm, int value, int* out, cudaStream_t s);
 };
 
+// One exchange: the in-place sum over ranks of arena[region_off .. region_off + numel * sizeof(T)) on every rank.
+struct NvlWork {
+  size_t region_off = 0;
+  int64_t numel = 0;
+  int32_t dtype = 0;
+  // gradients were produced in the arena unscaled: every rank's value goes through T(scale * (x + 0)) before it is
+  // added (the reducer's scale_(1/nranks), ref reducer.cc:1049-1050, same rounding as ScaleFunctor)
+  bool fold_scale = false;
+  float scale = 1.0f;
+  // Chunk mode: walk a GradDesc chunk table of the region's tensors (x = the tensor's slot in THIS rank's arena)
+  // instead of the flat region, so that the slice owner can leave the inf/nan flag and the squared-norm partial
+  // of every 8192-element chunk of the REDUCED gradient in every rank's sidecar (producer-side pass 1).
+  const DeviceTable* table = nullptr;
+  const float* loss_scale = nullptr;  // device; nullptr = no unscale / finite check
+  bool* found_local = nullptr;        // this rank's found_inf (set from the sidecar flag when the exchange ends)
+  bool norm = false, mp = false;
+  size_t partials_off = 0, flags_off = 0;  // byte offsets of the sidecar inside the arena
+};
+
 // Collective over all ranks.  On success *out is a context, or NULL when the ranks agreed that peer
-// mapping is not available (the caller then keeps NCCL).
+// mapping is not available (the caller then keeps NCCL).  A local failure never makes a rank leave early.
 int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, size_t arena_bytes, cudaStream_t stream,
                   NvlContext** out);
 // Up to two calls may be in flight at once, PROVIDED call number k runs on stream (k & 1) of a fixed pair of
 // streams: nvl_next_slot tells which of the two the next call must use.
 int nvl_next_slot(const NvlContext* c);
-// In-place sum over ranks of arena[region_off .. region_off + numel * sizeof(T)) on every rank.
-int32_t nvl_allreduce(NvlContext* c, size_t region_off_bytes, int64_t numel, int32_t dtype, cudaStream_t stream);
-// 1 if any wait inside a kernel of this context hit its time limit (a peer never arrived).
-int32_t nvl_error_flag(NvlContext* c, int* out);
+int32_t nvl_exchange(NvlContext* c, const NvlWork& w, cudaStream_t stream);
+// Cap on the grid of the exchange kernels (0 = one CTA per SM).
+void nvl_set_max_ctas(NvlContext* c, int max_ctas);
+// 1 if an exchange of this context ran into its time limit or a peer aborted (read from a mapped host word: no sync).
+int nvl_error_flag(const NvlContext* c);
 void nvl_destroy(NvlContext* c);
 
 }  // namespace prb

@@ -162,13 +162,10 @@ size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // ---------------------------------------------------------------- kernel
 struct NvlsArgs {
+  Bar bar;                   // barriers (prb_nvl_common.cuh)
   char* mc;                  // multicast address of the arena
-  Signals* sig[kMaxRanks];
-  int nranks, rank;
-  int parallel_release;        // see done_barrier
   size_t region_off;
   long long nvec;            // 16-byte vectors in the bucket
-  unsigned long long seq;
 };
 
 struct V16 {
@@ -198,14 +195,11 @@ constexpr int kNvlsUnroll = 8;  // 16-byte vectors in flight per thread: the rou
 
 template <typename T>
 __global__ void __launch_bounds__(kNvlThreads, 2) nvls_allreduce_kernel(const NvlsArgs a) {
-  Signals* mine = a.sig[a.rank];
-  const int slot = (int)(a.seq & (kSlots - 1));
+  const int slot = (int)(a.bar.seq & (kSlots - 1));
   // ---- ready barrier: every rank's packed bucket is complete
-  if (blockIdx.x == 0 && threadIdx.x < a.nranks) st_release_sys(&a.sig[threadIdx.x]->ready[slot][a.rank], a.seq);
-  if (threadIdx.x < a.nranks && !wait_at_least(&mine->ready[slot][threadIdx.x], a.seq)) mine->error = 1;
-  __syncthreads();
+  if (!ready_barrier(a.bar, slot)) return;
   // ---- my slice: the switch reduces on the way in and replicates on the way out
-  const long long v0 = a.nvec * a.rank / a.nranks, v1 = a.nvec * (a.rank + 1) / a.nranks;
+  const long long v0 = a.nvec * a.bar.rank / a.bar.nranks, v1 = a.nvec * (a.bar.rank + 1) / a.bar.nranks;
   const long long stride = (long long)gridDim.x * kNvlThreads;
   char* base = a.mc + a.region_off;
   for (long long v = v0 + (long long)blockIdx.x * kNvlThreads + threadIdx.x; v < v1; v += stride * kNvlsUnroll) {
@@ -218,7 +212,7 @@ __global__ void __launch_bounds__(kNvlThreads, 2) nvls_allreduce_kernel(const Nv
       if (v + u * stride < v1) mc_store(base + (size_t)(v + u * stride) * 16, r[u]);
   }
   // ---- done barrier
-  done_barrier(a, mine, slot);
+  done_barrier(a.bar, slot);
 }
 
 }  // namespace
@@ -368,7 +362,7 @@ int32_t nvls_setup(const NvlCollectives& nc, int nranks, int rank, int device, s
   // ---- 7: signal blocks for the barriers
   if (agreed) {
     int sok = 0;
-    PRB_TRY(signals_setup(nc, nranks, rank, stream, &c->sigs, &sok));
+    signals_setup(nc, nranks, rank, stream, &c->sigs, &sok);
     ok = ok && sok;
     PRB_TRY(vote(nc, ok, stream, &agreed));
   }
@@ -377,12 +371,8 @@ int32_t nvls_setup(const NvlCollectives& nc, int nranks, int rank, int device, s
     return PRB_SUCCESS;  // the caller falls back to peer memory / NCCL
   }
   c->args.mc = reinterpret_cast<char*>(c->mc);
-  for (int q = 0; q < nranks; ++q) c->args.sig[q] = c->sigs.sig[q];
-  c->args.nranks = nranks;
-  c->args.rank = rank;
-  c->args.parallel_release = 1;
-  if (const char* e = getenv("PRB_NVL_PARALLEL_RELEASE")) c->args.parallel_release = atoi(e) != 0;
-  int per_sm = kNvlCtasPerSm;
+  fill_bar(c->sigs, nranks, rank, &c->args.bar);
+  int per_sm = 1;
   if (const char* e = getenv("PRB_NVL_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
   c->ctas = sm_count() * per_sm;
   *out = c;
@@ -400,26 +390,24 @@ int32_t nvls_allreduce(NvlsContext* c, size_t region_off_bytes, int64_t numel, i
   NvlsArgs a = c->args;
   a.region_off = region_off_bytes;
   a.nvec = (long long)(bytes / 16);
-  a.seq = ++c->seq;
-  const long long per_rank = (a.nvec + a.nranks - 1) / a.nranks;
+  a.bar.seq = ++c->seq;
+  const long long per_rank = (a.nvec + a.bar.nranks - 1) / a.bar.nranks;
   int ctas = (int)((per_rank + kNvlThreads - 1) / kNvlThreads);
   if (ctas > c->ctas) ctas = c->ctas;
   if (ctas < 1) ctas = 1;
+  KernelTimer kt(KK_EXCHANGE, stream);
   switch (dtype) {
-    case PRB_FLOAT32: nvls_allreduce_kernel<float><<<ctas, kNvlThreads, 0, stream>>>(a); break;
-    case PRB_BFLOAT16: nvls_allreduce_kernel<__nv_bfloat16><<<ctas, kNvlThreads, 0, stream>>>(a); break;
-    case PRB_FLOAT16: nvls_allreduce_kernel<__half><<<ctas, kNvlThreads, 0, stream>>>(a); break;
+    case PRB_FLOAT32: PRB_CUDA(nvl_launch(nvls_allreduce_kernel<float>, ctas, kNvlThreads, stream, a)); break;
+    case PRB_BFLOAT16: PRB_CUDA(nvl_launch(nvls_allreduce_kernel<__nv_bfloat16>, ctas, kNvlThreads, stream, a)); break;
+    case PRB_FLOAT16: PRB_CUDA(nvl_launch(nvls_allreduce_kernel<__half>, ctas, kNvlThreads, stream, a)); break;
     default: PRB_FAIL(PRB_UNIMPLEMENTED, "nvls allreduce: dtype %s is not built", dtype_name(dtype));
   }
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }
 
-int32_t nvls_error_flag(NvlsContext* c, int* out) {
-  unsigned int e = 0;
-  PRB_CUDA(cudaMemcpy(&e, &c->sigs.mine->error, sizeof(e), cudaMemcpyDeviceToHost));
-  *out = (int)e;
-  return PRB_SUCCESS;
+int nvls_error_flag(const NvlsContext* c) {
+  return (c != nullptr && c->sigs.host_error != nullptr) ? (int)*reinterpret_cast<volatile unsigned int*>(c->sigs.host_error) : 0;
 }
 
 }  // namespace prb

@@ -16,7 +16,7 @@ int32_t nvls_setup(const NvlCollectives& nc, int nranks, int rank, int device, s
 // Same two-stream / two-slot rule as nvl_allreduce.
 int nvls_next_slot(const NvlsContext* c);
 int32_t nvls_allreduce(NvlsContext* c, size_t region_off_bytes, int64_t numel, int32_t dtype, cudaStream_t stream);
-int32_t nvls_error_flag(NvlsContext* c, int* out);
+int nvls_error_flag(const NvlsContext* c);
 void nvls_destroy(NvlsContext* c);
 
 }  // namespace prb

@@ -143,6 +143,8 @@ struct Group {
   bool pack_valid = false, unpack_valid = false, pack_had_unused = false;
   DeviceTable packep_tab;         // pack with the check + norm epilogue (GradDesc table, grad_pass_kernel mode 2)
   bool packep_valid = false, packep_had_unused = false;
+  DeviceTable exch_tab;           // chunk table of the group's slots for the exchange kernel's epilogue
+  bool exch_valid = false;
   int64_t first_chunk = 0;        // index of the group's first 8192-element chunk in the reducer's own numbering
 };
 
@@ -154,6 +156,7 @@ struct Epilogue {
   bool norm = false, mp = false;
   std::vector<int32_t> partial_base;  // per var: first partial in the consumer's layout
   bool cleared = false;               // found_inf was cleared in this backward
+  bool sidecar_cleared = false;       // ... and so was the flag the peers write (several ranks)
 };
 }  // namespace
 
@@ -192,8 +195,8 @@ struct PRB_Reducer {
   bool batching = false;
   std::vector<size_t> batch;
   std::vector<size_t> batch_key;
-  DeviceTable batch_pack_tab, batch_unpack_tab, batch_packep_tab;
-  bool batch_valid = false, batch_packep_valid = false;
+  DeviceTable batch_pack_tab, batch_unpack_tab, batch_packep_tab, batch_exch_tab;
+  bool batch_valid = false, batch_packep_valid = false, batch_exch_valid = false;
   std::vector<int64_t> launched;
 };
 
@@ -290,6 +293,81 @@ int32_t zero_unused_slots(PRB_Reducer* r, Group& g, cudaStream_t calc) {
   return PRB_SUCCESS;
 }
 
+// GradDesc of var v for the exchange kernel: x = the slot in THIS rank's arena (peers are reached by offset).
+GradDesc exch_desc(PRB_Reducer* r, const Group& g, size_t s) {
+  GradDesc d{};
+  d.x = r->arena + g.arena_off + (size_t)g.slot_off[s] * dtype_size(g.dtype);
+  d.out = nullptr;
+  d.aligned = 1;
+  d.partial_base = r->ep.norm ? r->ep.partial_base[(size_t)g.vars[s]] : 0;
+  return d;
+}
+
+int32_t exchange_table(PRB_Reducer* r, const std::vector<size_t>& gis, cudaStream_t stream, DeviceTable* tab) {
+  std::vector<GradDesc> descs;
+  std::vector<int64_t> numels;
+  for (size_t gi : gis) {
+    const Group& g = r->groups[gi];
+    for (size_t s = 0; s < g.vars.size(); ++s) {
+      descs.push_back(exch_desc(r, g, s));
+      numels.push_back(r->grads[(size_t)g.vars[s]].numel);
+    }
+  }
+  return get_table(descs.data(), sizeof(GradDesc), (int)descs.size(), numels.data(), grad_chunk_elems(), stream, tab,
+                   /*pin=*/true);
+}
+
+bool batch_exchange_enabled() {
+  static const bool v = [] {
+    const char* e = getenv("PRB_BATCH_EXCHANGE");
+    return !(e != nullptr && atoi(e) == 0);
+  }();
+  return v;
+}
+
+size_t sidecar_flags_off(const PRB_Reducer* r) {
+  return r->sidecar_off + align_up((size_t)r->sidecar_floats * sizeof(float), 256);
+}
+
+// The library's own exchange of the contiguous arena region of groups [first, last] on comm stream `cs`.
+int32_t nvl_exchange_groups(PRB_Reducer* r, size_t first, size_t last, const DeviceTable* table, cudaStream_t cs) {
+  const Group &g0 = r->groups[first], &g1 = r->groups[last];
+  const int es = dtype_size(g0.dtype);
+  NvlWork w;
+  w.region_off = g0.arena_off;
+  w.numel = (int64_t)((g1.arena_off + (size_t)g1.length * es - g0.arena_off) / es);
+  w.dtype = g0.dtype;
+  w.fold_scale = r->grads_in_arena;
+  w.scale = (float)(1.0 / (double)r->comm->nranks);
+  if (table != nullptr && epilogue_in_exchange(r)) {
+    w.table = table;
+    w.loss_scale = r->ep.loss_scale;
+    w.found_local = r->ep.found_inf;
+    w.norm = r->ep.norm;
+    w.mp = r->ep.mp;
+    w.partials_off = r->sidecar_off;
+    w.flags_off = sidecar_flags_off(r);
+  }
+  return nvl_exchange(r->nvl, w, cs);
+}
+
+// Once per backward with the epilogue in the exchange: clear the sidecar flag the peers write into.
+int32_t epilogue_begin_exchange(PRB_Reducer* r, cudaStream_t calc) {
+  if (!epilogue_in_exchange(r) || r->ep.loss_scale == nullptr || r->ep.sidecar_cleared) return PRB_SUCCESS;
+  PRB_CUDA(cudaMemsetAsync(r->arena + sidecar_flags_off(r), 0, 256, calc));
+  r->ep.sidecar_cleared = true;
+  return PRB_SUCCESS;
+}
+
+// A dead exchange context (a peer never arrived): raise on the host instead of carrying on with unreduced gradients.
+int32_t check_comm_alive(const PRB_Reducer* r) {
+  const int dead = r->nvls != nullptr ? nvls_error_flag(r->nvls) : (r->nvl != nullptr ? nvl_error_flag(r->nvl) : 0);
+  PRB_ENFORCE(!dead, PRB_EXTERNAL,
+              "bucket exchange failed: a peer rank did not arrive within PRB_NVL_TIMEOUT_MS or aborted; the gradients of "
+              "that step were NOT reduced and this communicator is dead (restart the job)");
+  return PRB_SUCCESS;
+}
+
 // ref: FusedAllReduceSchedule reducer.cc:1037-1070 ("concat > div_nranks > allreduce > split")
 int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   Group& g = r->groups[gi];
@@ -299,7 +377,15 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   }
   PRB_Comm* c = r->comm;
   const int es = dtype_size(g.dtype);
-  if (r->batching && c->nranks == 1 && !r->grads_in_arena && !g.has_unused && !g.pack_had_unused && !g.packep_had_unused &&
+  // Batch mode: groups that complete inside ONE mark_vars_ready call.  One rank: a single pack launch for all of
+  // them.  Several ranks: only when the consumer has a global dependency anyway (epilogue set: it cannot start
+  // before the last bucket is reduced) -- then one pack and ONE exchange (one barrier pair) serve all of them;
+  // without such a dependency buckets stay separate so that the optimizer can consume them one by one.
+  // (With find_unused_parameters the ranks may disagree about which groups hold unused parameters, and every rank
+  // must issue the same sequence of exchanges: no batching then.)
+  const bool batch_here = (c->nranks == 1 && !r->grads_in_arena) ||
+                          (c->nranks > 1 && epilogue_in_exchange(r) && batch_exchange_enabled() && !r->find_unused);
+  if (r->batching && batch_here && !g.has_unused && !g.pack_had_unused && !g.packep_had_unused &&
       (r->batch.empty() || r->groups[r->batch.front()].dtype == g.dtype)) {
     r->batch.push_back(gi);
     r->launched.push_back((int64_t)gi);
@@ -307,6 +393,7 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   }
   char* region = r->arena + g.arena_off;
   PRB_TRY(epilogue_begin(r, calc));
+  PRB_TRY(epilogue_begin_exchange(r, calc));
   if (g.has_unused) PRB_TRY(zero_unused_slots(r, g, calc));
   if (r->grads_in_arena) {
     // the producer wrote the slots: nothing to pack; with several ranks the 1/nranks scale runs in place
@@ -349,7 +436,11 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
     if (r->nvls != nullptr) {
       PRB_TRY(nvls_allreduce(r->nvls, g.arena_off, g.length, g.dtype, cs));
     } else if (r->nvl != nullptr) {
-      PRB_TRY(nvl_allreduce(r->nvl, g.arena_off, g.length, g.dtype, cs));
+      if (epilogue_in_exchange(r) && !g.exch_valid) {
+        PRB_TRY(exchange_table(r, {gi}, cs, &g.exch_tab));
+        g.exch_valid = true;
+      }
+      PRB_TRY(nvl_exchange_groups(r, gi, gi, epilogue_in_exchange(r) ? &g.exch_tab : nullptr, cs));
     } else {
       ncclDataType_t nt;
       PRB_TRY(nccl_dtype(g.dtype, &nt));
@@ -376,9 +467,12 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
 
 int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
   if (r->batch.empty()) return PRB_SUCCESS;
-  if (r->batch_key != r->batch) r->batch_valid = r->batch_packep_valid = false;
+  if (r->batch_key != r->batch) r->batch_valid = r->batch_packep_valid = r->batch_exch_valid = false;
+  PRB_Comm* c = r->comm;
+  const bool multi = c->nranks > 1;
   const bool with_ep = epilogue_in_pack(r);
-  if (with_ep ? !r->batch_packep_valid : !r->batch_valid) {
+  const bool need_pack = !r->grads_in_arena;
+  if (need_pack && (with_ep ? !r->batch_packep_valid : !r->batch_valid)) {
     std::vector<MapDesc> pack, unpack;
     std::vector<GradDesc> packep;
     std::vector<int64_t> numels;
@@ -413,14 +507,34 @@ int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
     }
     PRB_TRY(get_table(unpack.data(), sizeof(MapDesc), (int)unpack.size(), numels.data(), map_chunk_elems(), calc,
                       &r->batch_unpack_tab, /*pin=*/true));
-    r->batch_key = r->batch;
   }
-  const int32_t dt = r->groups[r->batch.front()].dtype;
+  if (multi && epilogue_in_exchange(r) && !r->batch_exch_valid) {
+    PRB_TRY(exchange_table(r, r->batch, calc, &r->batch_exch_tab));
+    r->batch_exch_valid = true;
+  }
+  r->batch_key = r->batch;
+  const size_t first = r->batch.front(), last = r->batch.back();
+  const std::vector<size_t> members = r->batch;
+  const int32_t dt = r->groups[first].dtype;
   r->batch.clear();
   PRB_TRY(epilogue_begin(r, calc));
-  if (with_ep) PRB_TRY(launch_grad_pass(dt, r->batch_packep_tab, packep_opts(r), calc));
-  else PRB_TRY(launch_scale(dt, r->batch_pack_tab, 1.0, 0.0f, false, calc));  // 1.0 / nranks with one rank
-  if (r->unpack) PRB_TRY(launch_copy(dtype_size(dt), r->batch_unpack_tab, calc));
+  PRB_TRY(epilogue_begin_exchange(r, calc));
+  if (need_pack) {
+    if (with_ep) PRB_TRY(launch_grad_pass(dt, r->batch_packep_tab, packep_opts(r), calc));
+    else PRB_TRY(launch_scale(dt, r->batch_pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
+  }
+  if (!multi) {
+    if (r->unpack && need_pack) PRB_TRY(launch_copy(dtype_size(dt), r->batch_unpack_tab, calc));
+    return PRB_SUCCESS;
+  }
+  // several ranks: ONE exchange for the whole batch (the groups' regions are adjacent in the arena)
+  cudaStream_t cs = nvl_next_slot(r->nvl) == 1 ? c->stream2 : c->stream;
+  Group& g0 = r->groups[first];
+  PRB_CUDA(cudaEventRecord(g0.ready, calc));
+  PRB_CUDA(cudaStreamWaitEvent(cs, g0.ready, 0));
+  PRB_TRY(nvl_exchange_groups(r, first, last, &r->batch_exch_tab, cs));
+  if (r->unpack && need_pack) PRB_TRY(launch_copy(dtype_size(dt), r->batch_unpack_tab, cs));
+  for (size_t gi : members) PRB_CUDA(cudaEventRecord(r->groups[gi].done, cs));
   return PRB_SUCCESS;
 }
 
@@ -758,6 +872,7 @@ int32_t prb_reducer_destroy(PRB_Reducer* r) {
 
 int32_t prb_reducer_prepare_for_backward(PRB_Reducer* r) {
   PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  if (!r->dry) PRB_TRY(check_comm_alive(r));
   // ref: PrepareForBackward reducer.cc:669-728
   PRB_ENFORCE(!r->need_finalize, PRB_PRECONDITION_NOT_MET,
               "A serious error has occurred here. Please set find_unused_parameters=True to traverse backward graph "
@@ -775,6 +890,7 @@ int32_t prb_reducer_prepare_for_backward(PRB_Reducer* r) {
   r->finalized = false;
   r->launched.clear();
   r->ep.cleared = false;
+  r->ep.sidecar_cleared = false;
   return PRB_SUCCESS;
 }
 
@@ -859,8 +975,8 @@ int32_t prb_reducer_set_grad_epilogue(PRB_Reducer* r, const PRB_GradEpilogue* e,
     ep.on = ep.norm || ep.loss_scale != nullptr;
   }
   r->ep = ep;
-  for (Group& g : r->groups) g.packep_valid = false;
-  r->batch_packep_valid = false;
+  for (Group& g : r->groups) g.packep_valid = g.exch_valid = false;
+  r->batch_packep_valid = r->batch_exch_valid = false;
   if (partials_out != nullptr) {
     partials_out->data = sidecar(r);
     partials_out->numel = r->sidecar_floats;
@@ -895,7 +1011,11 @@ int32_t prb_reducer_allreduce_group(PRB_Reducer* r, int64_t gi, void* stream) {
   if (r->nvls != nullptr) return nvls_allreduce(r->nvls, g.arena_off, g.length, g.dtype, (cudaStream_t)stream);
   if (r->nvl != nullptr) {
     // stand-alone calls all go to the caller's one stream, which orders them whatever slot they use
-    return nvl_allreduce(r->nvl, g.arena_off, g.length, g.dtype, (cudaStream_t)stream);
+    NvlWork w;
+    w.region_off = g.arena_off;
+    w.numel = g.length;
+    w.dtype = g.dtype;
+    return nvl_exchange(r->nvl, w, (cudaStream_t)stream);
   }
   ncclDataType_t nt;
   PRB_TRY(nccl_dtype(g.dtype, &nt));
@@ -906,16 +1026,13 @@ int32_t prb_reducer_allreduce_group(PRB_Reducer* r, int64_t gi, void* stream) {
 
 int32_t prb_reducer_comm_error(PRB_Reducer* r, int32_t* out) {
   PRB_ENFORCE(r && out, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
-  *out = 0;
-  if (r->nvls != nullptr) {
-    int e = 0;
-    PRB_TRY(nvls_error_flag(r->nvls, &e));
-    *out = e;
-  } else if (r->nvl != nullptr) {
-    int e = 0;
-    PRB_TRY(nvl_error_flag(r->nvl, &e));
-    *out = e;
-  }
+  *out = r->nvls != nullptr ? nvls_error_flag(r->nvls) : (r->nvl != nullptr ? nvl_error_flag(r->nvl) : 0);
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_set_exchange_ctas(PRB_Reducer* r, int32_t max_ctas) {
+  PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  if (r->nvl != nullptr) nvl_set_max_ctas(r->nvl, max_ctas);
   return PRB_SUCCESS;
 }
 
@@ -930,6 +1047,7 @@ int32_t prb_reducer_wait_group(PRB_Reducer* r, int64_t gi, void* stream) {
   PRB_ENFORCE(gi >= 0 && gi < (int64_t)r->groups.size(), PRB_OUT_OF_RANGE, "Out of bounds group index %lld", (long long)gi);
   PRB_ENFORCE((size_t)gi < r->next_group, PRB_PRECONDITION_NOT_MET,
               "group %lld has not been launched in this backward yet", (long long)gi);
+  if (!r->dry) PRB_TRY(check_comm_alive(r));
   if (!r->dry && r->comm->nranks > 1) PRB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, r->groups[(size_t)gi].done, 0));
   return PRB_SUCCESS;
 }
