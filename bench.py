@@ -497,9 +497,10 @@ def run_reference_arm(args):
 # --------------------------------------------------------------------------------------------
 # N > 1 parity preamble (untimed, < 1 s): the GPU-test box has one GPU, so the multi-rank path proves itself here
 # --------------------------------------------------------------------------------------------
-def parity_preamble(prb, group):
+def parity_preamble(prb, group, arena=False, save_dir=None):
     """A tiny AMP bf16 + master + clip job through the same API on all ranks: one clean step, one step with an Inf
-    injected on ONE rank (every rank must skip and halve its loss scale), one more clean step.  After each step
+    injected on ONE rank (every rank must skip and halve its loss scale), two more clean steps (even steps mark all
+    gradients ready in one call, odd steps hook by hook).  After each step
     parameters, masters, moments and the scaler state must be bit-equal across ranks (checksums compared through
     the communicator); with two ranks (one addition, so the order cannot matter) they must also equal the oracle's
     composition of the reference's stages bit for bit.  Returns "ok" or "fail: <what>"."""
@@ -511,7 +512,8 @@ def parity_preamble(prb, group):
         for i, sz in enumerate(sizes):
             p0 = orc.from_f32(np.random.default_rng(100 + i).normal(0, 0.02, sz).astype(np.float32), orc.BF16)
             p = prb.Tensor.from_numpy(p0, orc.BF16, name="pp_%d" % i)
-            p.grad = prb.Tensor.zeros(sz, orc.BF16)
+            if not arena:
+                p.grad = prb.Tensor.zeros(sz, orc.BF16)
             params.append(p)
             host.append({"param": p0.copy(), "mom1": np.zeros(sz, np.float32), "mom2": np.zeros(sz, np.float32),
                          "master": orc.to_f32(p0, orc.BF16)})
@@ -519,7 +521,8 @@ def parity_preamble(prb, group):
         opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, weight_decay=0.01, grad_clip=clip,
                                   multi_precision=True)
         scaler = prb.amp.GradScaler(init_loss_scaling=2.0 ** 15, decr_every_n_nan_or_inf=1)
-        dp = prb.DataParallel(params, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True)
+        dp = prb.DataParallel(params, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True,
+                              grads_in_arena=arena)
         scale, b1p, b2p = 2.0 ** 15, np.float32(0.9), np.float32(0.999)
         for step in range(4):
             per_rank = [[orc.from_f32((np.random.default_rng(1000 * r + 10 * step + i).normal(0, 1e-2, sz) * 2.0 ** 15 * 30)
@@ -529,10 +532,19 @@ def parity_preamble(prb, group):
             for p, g in zip(params, per_rank[rank]):
                 p.grad.copy_from_numpy(g)
             dp.prepare_for_backward()
-            dp.mark_all_ready()
+            if step % 2 == 0:
+                dp.mark_all_ready()                       # one call: one pack + one exchange for all buckets
+            else:
+                for i in reversed(range(len(params))):    # hooks one by one: one pack + one exchange per bucket
+                    dp.mark_var_ready(i)
             scaler.step(opt)
             scaler.update()
             prb.current_stream().synchronize()
+            if save_dir is not None:
+                for i, p in enumerate(params):
+                    np.save(os.path.join(save_dir, "amp%d_param_%d_%d_r%d.npy" % (int(arena), step, i, rank)), p.numpy())
+                    np.save(os.path.join(save_dir, "amp%d_m2_%d_%d_r%d.npy" % (int(arena), step, i, rank)),
+                            opt._accumulators[p.name]["moment2"].numpy())
             found = bool(scaler._found_inf.numpy()[0])
             if found != (step == 1):
                 return "fail: step %d found_inf=%s on rank %d" % (step, found, rank)
@@ -550,7 +562,7 @@ def parity_preamble(prb, group):
             mx, mn = t.numpy()
             if mx != -mn:
                 return "fail: step %d state differs across ranks" % step
-            if n == 2:
+            if n == 2 and dp._reducer.allreduce_backend != "nvls":   # (the NVSwitch's own adder is not bit-pinned)
                 red = []
                 for i in range(len(sizes)):
                     s = sum(orc.to_f32(orc.scale(per_rank[r][i], orc.BF16, 1.0 / n), orc.BF16).astype(np.float64) for r in range(n))
@@ -744,7 +756,18 @@ def run_gpu_arm(args):
 
     if prb.device_count() == 0:
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
-    group = prb.distributed.init_parallel_env()
+    # NCCL prints its version banner on stdout; the driver wants ONE JSON line there
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        group = prb.distributed.init_parallel_env()
+        if group.nranks > 1:
+            group.barrier()   # the first collective is where the banner appears
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
     rank, nranks = group.rank, group.nranks
     if nranks != args.gpus:
         raise SystemExit("bench.py: --gpus %d but WORLD_SIZE=%d (launch N>1 through torch.distributed.run)" % (args.gpus, nranks))

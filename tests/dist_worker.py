@@ -102,6 +102,38 @@ def main(out_dir):
         else:
             np.testing.assert_allclose(p.grad.numpy(), want, rtol=1e-6, atol=1e-8)
         np.save(os.path.join(out_dir, "fleet_grad_%d_r%d.npy" % (i, rank)), p.grad.numpy())
+    # AMP bf16 + fp32 master + global-norm clip across ranks, an Inf on ONE rank only (every rank must skip, the loss
+    # scale must move identically), batch and per-bucket exchange, gradients packed and produced in the arena;
+    # state bit-equal across ranks, N = 2 bit-exact vs the oracle  (the same routine bench.py runs before timing)
+    import bench
+    for arena in (False, True):
+        verdict = bench.parity_preamble(prb, group, arena=arena, save_dir=out_dir)
+        assert verdict == "ok", "AMP + clip parity (arena=%s): %s" % (arena, verdict)
+    # a parameter unused on rank 0 only (ref ProcessUnusedDenseVars reducer.cc:941-1011): its reduced gradient is the
+    # scaled sum of the OTHER ranks' gradients on every rank
+    up, ug = [], []
+    for i, sz in enumerate(sizes[:7]):
+        p = prb.Tensor.zeros(sz, "float32", name="u_%d" % i)
+        per_rank = [np.random.default_rng(7000 * r + i).normal(0, 1e-2, sz).astype(np.float32) for r in range(n)]
+        p.grad = prb.Tensor.from_numpy(per_rank[rank])
+        up.append(p)
+        ug.append(per_rank)
+    dpu = prb.DataParallel(up, comm_buffer_size=0.4, last_comm_buffer_size=0.01, find_unused_parameters=True)
+    lone = 3
+    dpu.prepare_for_backward(unused_vars=[lone] if rank == 0 else [])
+    for i in reversed(range(len(up))):
+        if not (rank == 0 and i == lone):
+            dpu.mark_var_ready(i)
+    assert dpu.finalized
+    prb.current_stream().synchronize()
+    for i, p in enumerate(up):
+        ranks = [r for r in range(n) if not (r == 0 and i == lone)]
+        want = np.sum([orc.scale(ug[i][r], orc.F32, 1.0 / n).astype(np.float64) for r in ranks], axis=0)
+        if n == 2:
+            np.testing.assert_array_equal(p.grad.numpy(), (want + 0.0).astype(np.float32))
+        else:
+            np.testing.assert_allclose(p.grad.numpy(), want, rtol=1e-6, atol=1e-8)
+        np.save(os.path.join(out_dir, "unused_grad_%d_r%d.npy" % (i, rank)), p.grad.numpy())
     # timing helper used by bench.py: max over ranks through the communicator
     t = prb.Tensor.from_numpy(np.array([float(rank + 1)], np.float32))
     group.all_reduce(t, "max")
@@ -110,5 +142,47 @@ def main(out_dir):
     print("rank %d ok" % rank, flush=True)
 
 
+def timeout_main():
+    """A rank that arrives later than PRB_NVL_TIMEOUT_MS: no rank may apply a half-reduced gradient silently.  The
+    waiting rank gives up, tells its peer, both exchanges leave the data alone and both hosts get an error."""
+    import time
+    group = prb.distributed.init_parallel_env()
+    rank = group.rank
+    p = prb.Tensor.from_numpy(np.full(100000, 1.0, np.float32), name="t_0")
+    p.grad = prb.Tensor.from_numpy(np.full(100000, float(rank + 1), np.float32))
+    dp = prb.DataParallel([p], consume_from_buckets=True)
+    if dp._reducer.allreduce_backend != "nvlink":
+        print("rank %d timeout skipped (backend %s)" % (rank, dp._reducer.allreduce_backend), flush=True)
+        return
+    dp.prepare_for_backward()
+    dp.mark_all_ready()
+    dp.wait_all_groups()
+    prb.current_stream().synchronize()
+    np.testing.assert_array_equal(dp.bucket_grads()[0].numpy(), np.full(100000, 1.5, np.float32))
+    group.barrier()
+    late = float(os.environ.get("PRB_TEST_LATE_S", "4"))
+    if rank == 1:
+        time.sleep(late)
+    dp.prepare_for_backward()
+    dp.mark_all_ready()
+    prb.synchronize()
+    time.sleep(late + 1 if rank == 0 else 0.5)  # let the peer run into it too
+    raised = False
+    try:
+        dp.wait_all_groups()
+    except prb._lib.PRBError as e:
+        raised = "bucket exchange failed" in str(e)
+    assert raised, "rank %d: the dead exchange was not reported" % rank
+    assert dp._reducer.comm_error()
+    # the bucket still holds this rank's own packed gradient: nothing half-reduced was stored
+    np.testing.assert_array_equal(dp.bucket_grads()[0].numpy(), np.full(100000, (rank + 1) * 0.5, np.float32))
+    print("rank %d timeout ok" % rank, flush=True)
+    sys.stdout.flush()
+    os._exit(0)  # the communicator is dead by design: skip the collective teardown
+
+
 if __name__ == "__main__":
-    main(sys.argv[1])
+    if len(sys.argv) > 2 and sys.argv[2] == "timeout":
+        timeout_main()
+    else:
+        main(sys.argv[1])

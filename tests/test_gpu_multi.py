@@ -43,3 +43,22 @@ def test_dataparallel_grads_equal_across_ranks(tmp_path, nranks, backend):
         for r in range(1, nranks):
             b = np.load(f0.replace("_r0.npy", "_r%d.npy" % r))
             assert a.tobytes() == b.tobytes(), os.path.basename(f0)
+
+
+def test_late_rank_makes_the_exchange_fail_loudly(tmp_path):
+    """a rank that is later than the exchange's time limit must not make its peers reduce garbage."""
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    procs = []
+    for r in range(2):
+        env = {**os.environ, "RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": "2", "MASTER_ADDR": "127.0.0.1",
+               "MASTER_PORT": str(port), "PRB_ALLREDUCE": "nvlink", "PRB_NVL_TIMEOUT_MS": "1500", "PRB_TEST_LATE_S": "4"}
+        procs.append(subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "dist_worker.py"), str(tmp_path), "timeout"],
+                                      env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+    outs = [p.communicate(timeout=120)[0].decode() for p in procs]
+    for r, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0 and ("timeout ok" in o or "timeout skipped" in o), "rank %d:\n%s" % (r, o[-3000:])
