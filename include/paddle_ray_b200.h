@@ -181,6 +181,10 @@ int32_t prb_scale(const PRB_Tensor* x, double scale, float bias, int32_t bias_af
 int32_t prb_concat(const PRB_Tensor* ins, int64_t num, PRB_Tensor* out, void* stream);
 int32_t prb_split(const PRB_Tensor* in, PRB_Tensor* outs, int64_t num, void* stream);
 
+/* out = x * y with y one float32 element on the device: the broadcast multiply of AmpScaler.scale(var)
+ * (ref: python/paddle/amp/grad_scaler.py:152-200, `var * self._scale`), without reading the loss scale back. */
+int32_t prb_multiply_by_scalar_tensor(const PRB_Tensor* x, const PRB_Tensor* y, PRB_Tensor* out, void* stream);
+
 /* cast between float32 / bfloat16 / float16 (init-time helper: master weights are the fp32 cast of
  * 16-bit parameters, ref: python/paddle/optimizer/optimizer.py:640-666). */
 int32_t prb_cast(const PRB_Tensor* x, PRB_Tensor* out, void* stream);

@@ -73,6 +73,7 @@ SIGNATURES = {
     "prb_concat": [_T, _i64, _T, _vp],
     "prb_split": [_T, _T, _i64, _vp],
     "prb_cast": [_T, _T, _vp],
+    "prb_multiply_by_scalar_tensor": [_T, _T, _T, _vp],
     "prb_assign_group_by_size": [_vp, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp],
     "prb_comm_get_unique_id": [_vp],
     "prb_comm_init_rank": [_vp, _i32, _i32, _i32, C.POINTER(_vp)],

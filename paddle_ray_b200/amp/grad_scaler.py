@@ -16,8 +16,10 @@ from enum import Enum
 
 import numpy as np
 
-from .. import _C_ops
-from .._lib import BOOL, FLOAT32, INT32
+import ctypes as C
+
+from .. import _C_ops, core
+from .._lib import BOOL, FLOAT32, INT32, call
 from ..core import Tensor
 
 
@@ -55,8 +57,10 @@ class AmpScaler:
         """``var * loss_scale`` (ref :170-200); a new tensor."""
         if not self._enable:
             return var
-        raise NotImplementedError("scaling the loss belongs to the forward pass, which is outside this path; "
-                                  "read scaler.get_loss_scaling() and scale the loss where it is produced")
+        out = Tensor(var.numel, var.dtype, var.device)
+        a, s, o = var.prb, self._scale.prb, out.prb
+        call("prb_multiply_by_scalar_tensor", C.byref(a), C.byref(s), C.byref(o), core._stream_handle(None))
+        return out
 
     def get_loss_scaling(self) -> Tensor:
         return self._scale

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "prb_adam.cuh"
+#include "prb_fp64.h"
 
 namespace prb {
 
@@ -285,6 +286,9 @@ struct ListArgs {
   int64_t num;
   const PRB_Tensor* skip;      // optional
   float beta1, beta2, epsilon;
+  double beta1_d, beta2_d, epsilon_d;  // the attributes as given (float64 kernels use them unrounded)
+  const double* lr_ratio_d;    // float64 path: per tensor or nullptr
+  const double* coeff_d;
   const float* lr_ratio;       // per tensor or nullptr (1.0)
   const float* coeff;          // per tensor or nullptr (0)
   int use_decay;               // decay line present
@@ -311,6 +315,89 @@ int32_t copy_if_different(const PRB_Tensor& src, const PRB_Tensor* dst, cudaStre
   return PRB_SUCCESS;
 }
 
+// float64 parameters (T = MT = double): moments, learning rate and beta-pows are double tensors too
+// (ref adamw_kernel.cu:147-343 with MPDType = double).  One launch per tensor: not on the north-star path.
+int32_t run_adam_list_f64(const ListArgs& A, cudaStream_t stream) {
+  const int64_t n = A.num;
+  PRB_ENFORCE(!A.multi_precision, PRB_INVALID_ARGUMENT, "%s: multi_precision has no meaning for float64 parameters", A.op);
+  const bool pows_on_host = A.b1pow[0].device < 0;
+  const bool* skip_dev = nullptr;
+  if (A.skip != nullptr) {
+    PRB_ENFORCE(A.skip->numel == 1, PRB_INVALID_ARGUMENT, "Input(SkipUpdate) size must be 1, but get %lld",
+                (long long)A.skip->numel);
+    if (A.skip->device < 0) {
+      if (*reinterpret_cast<const bool*>(A.skip->data)) return PRB_SUCCESS;
+    } else if (pows_on_host && !A.use_global_beta_pow) {
+      bool h = false;  // host-resident accumulators must not advance on a skipped step (ref adamw_kernel.cu:177-187)
+      PRB_CUDA(cudaMemcpyAsync(&h, A.skip->data, 1, cudaMemcpyDeviceToHost, stream));
+      PRB_CUDA(cudaStreamSynchronize(stream));
+      if (h) return PRB_SUCCESS;
+    } else {
+      skip_dev = reinterpret_cast<const bool*>(A.skip->data);
+    }
+  }
+  for (int64_t i = 0; i < n; ++i) {
+    const PRB_Tensor &p = A.param[i], &g = A.grad[i], &m1 = A.mom1[i], &m2 = A.mom2[i];
+    const int64_t pi = A.pow_from_first ? 0 : i;
+    const PRB_Tensor &lr = A.lr[i * A.lr_stride], &b1 = A.b1pow[pi], &b2 = A.b2pow[pi];
+    PRB_ENFORCE(p.dtype == PRB_FLOAT64 && g.dtype == PRB_FLOAT64 && m1.dtype == PRB_FLOAT64 && m2.dtype == PRB_FLOAT64 &&
+                    lr.dtype == PRB_FLOAT64 && b1.dtype == PRB_FLOAT64 && b2.dtype == PRB_FLOAT64,
+                PRB_INVALID_ARGUMENT,
+                "%s: float64 parameters need float64 grad, moments, learning_rate and beta-pows (MPType = double)", A.op);
+    PRB_ENFORCE(g.numel == p.numel && m1.numel == p.numel && m2.numel == p.numel, PRB_INVALID_ARGUMENT,
+                "%s: tensor %lld: param/grad/moment sizes differ", A.op, (long long)i);
+    PRB_ENFORCE(p.device >= 0 && g.device >= 0 && m1.device >= 0 && m2.device >= 0, PRB_INVALID_ARGUMENT,
+                "%s: param/grad/moments must be device tensors (there is no CPU path)", A.op);
+    PRB_ENFORCE(lr.numel == 1 && b1.numel == 1 && b2.numel == 1, PRB_INVALID_ARGUMENT,
+                "%s: learning_rate and beta-pows must hold one element", A.op);
+    PRB_ENFORCE((b1.device < 0) == pows_on_host && (b2.device < 0) == pows_on_host, PRB_INVALID_ARGUMENT,
+                "All Beta1Pow/Beta2Pow must be in the same place.");
+    PRB_TRY(copy_if_different(p, A.param_out ? &A.param_out[i] : nullptr, stream, "param", A.op));
+    PRB_TRY(copy_if_different(m1, A.mom1_out ? &A.mom1_out[i] : nullptr, stream, "moment1", A.op));
+    PRB_TRY(copy_if_different(m2, A.mom2_out ? &A.mom2_out[i] : nullptr, stream, "moment2", A.op));
+    Adam64 a{};
+    a.param = reinterpret_cast<double*>((A.param_out ? A.param_out[i] : p).data);
+    a.grad = reinterpret_cast<const double*>(g.data);
+    a.mom1 = reinterpret_cast<double*>((A.mom1_out ? A.mom1_out[i] : m1).data);
+    a.mom2 = reinterpret_cast<double*>((A.mom2_out ? A.mom2_out[i] : m2).data);
+    a.n = p.numel;
+    if (lr.device < 0) a.lr_host = *reinterpret_cast<const double*>(lr.data);
+    else a.lr_dev = reinterpret_cast<const double*>(lr.data);
+    if (pows_on_host) {
+      a.b1pow_host = *reinterpret_cast<const double*>(b1.data);
+      a.b2pow_host = *reinterpret_cast<const double*>(b2.data);
+    } else {
+      a.b1pow_dev = reinterpret_cast<const double*>(b1.data);
+      a.b2pow_dev = reinterpret_cast<const double*>(b2.data);
+    }
+    a.lr_ratio = A.lr_ratio_d ? A.lr_ratio_d[i] : 1.0;
+    a.beta1 = A.beta1_d;
+    a.beta2 = A.beta2_d;
+    a.epsilon = A.epsilon_d;
+    a.coeff = A.coeff_d ? A.coeff_d[i] : 0.0;
+    a.use_decay = A.use_decay;
+    a.skip = skip_dev;
+    PRB_TRY(launch_adam_f64(a, stream));
+  }
+  if (A.use_global_beta_pow) return PRB_SUCCESS;
+  for (int64_t i = 0; i < n; ++i) {  // ref adamw_kernel.cu:283-289 (host) / :332-341 (device)
+    const PRB_Tensor* o1 = A.b1pow_out ? &A.b1pow_out[i] : &A.b1pow[i];
+    const PRB_Tensor* o2 = A.b2pow_out ? &A.b2pow_out[i] : &A.b2pow[i];
+    bool seen = false;  // an accumulator shared by several parameters advances once per step
+    for (int64_t j = 0; j < i && !seen; ++j) seen = (A.b1pow_out ? A.b1pow_out[j].data : A.b1pow[j].data) == o1->data;
+    if (seen) continue;
+    if (pows_on_host) {
+      *reinterpret_cast<double*>(o1->data) = A.beta1_d * *reinterpret_cast<const double*>(A.b1pow[i].data);
+      *reinterpret_cast<double*>(o2->data) = A.beta2_d * *reinterpret_cast<const double*>(A.b2pow[i].data);
+    } else {
+      PRB_TRY(launch_beta_pow_f64(reinterpret_cast<const double*>(A.b1pow[i].data), reinterpret_cast<double*>(o1->data),
+                                  reinterpret_cast<const double*>(A.b2pow[i].data), reinterpret_cast<double*>(o2->data),
+                                  A.beta1_d, A.beta2_d, skip_dev, stream));
+    }
+  }
+  return PRB_SUCCESS;
+}
+
 int32_t run_adam_list(const ListArgs& A, cudaStream_t stream) {
   PRB_TRY(require_device());
   const int64_t n = A.num;
@@ -320,6 +407,7 @@ int32_t run_adam_list(const ListArgs& A, cudaStream_t stream) {
               "%s: a required input is NULL", A.op);
   PRB_ENFORCE(!A.multi_precision || A.master != nullptr, PRB_INVALID_ARGUMENT,
               "%s: multi_precision requires master_param", A.op);
+  if (A.param[0].dtype == PRB_FLOAT64) return run_adam_list_f64(A, stream);
 
   // ---- skip_update (ref adamw_kernel.cu:177-201, fused_adam_kernel.cu:325-343)
   const bool* skip_dev = nullptr;
@@ -517,10 +605,13 @@ int32_t prb_adamw(const PRB_Tensor* param, const PRB_Tensor* grad, const PRB_Ten
   (void)lazy_mode;
   (void)min_row_size_to_use_multithread;
   const float coeff_eff = with_decay ? coeff : 0.0f;  // ref adamw_kernel.cu:203-206
+  const double coeff_d = coeff_eff, ratio_d = lr_ratio;
   ListArgs A{};
+  A.lr_ratio_d = &ratio_d; A.coeff_d = &coeff_d;
   A.param = param; A.grad = grad; A.lr = learning_rate; A.lr_stride = 0; A.mom1 = moment1; A.mom2 = moment2;
   A.b1pow = beta1_pow; A.b2pow = beta2_pow; A.pow_from_first = false; A.master = multi_precision ? master_param : nullptr;
   A.num = 1; A.skip = skip_update; A.beta1 = (float)beta1; A.beta2 = (float)beta2; A.epsilon = (float)epsilon;
+  A.beta1_d = beta1; A.beta2_d = beta2; A.epsilon_d = epsilon;
   A.lr_ratio = &lr_ratio; A.coeff = &coeff_eff; A.use_decay = 1; A.multi_precision = multi_precision != 0;
   A.use_global_beta_pow = use_global_beta_pow != 0; A.param_out = param_out; A.mom1_out = moment1_out;
   A.mom2_out = moment2_out; A.b1pow_out = beta1_pow_out; A.b2pow_out = beta2_pow_out;
@@ -541,6 +632,7 @@ int32_t prb_adam(const PRB_Tensor* param, const PRB_Tensor* grad, const PRB_Tens
   A.param = param; A.grad = grad; A.lr = learning_rate; A.lr_stride = 0; A.mom1 = moment1; A.mom2 = moment2;
   A.b1pow = beta1_pow; A.b2pow = beta2_pow; A.pow_from_first = false; A.master = multi_precision ? master_param : nullptr;
   A.num = 1; A.skip = skip_update; A.beta1 = (float)beta1; A.beta2 = (float)beta2; A.epsilon = (float)epsilon;
+  A.beta1_d = beta1; A.beta2_d = beta2; A.epsilon_d = epsilon;
   A.lr_ratio = nullptr; A.coeff = nullptr; A.use_decay = 0; A.multi_precision = multi_precision != 0;
   A.use_global_beta_pow = use_global_beta_pow != 0; A.param_out = param_out; A.mom1_out = moment1_out;
   A.mom2_out = moment2_out; A.b1pow_out = beta1_pow_out; A.b2pow_out = beta2_pow_out;
@@ -559,6 +651,7 @@ int32_t prb_merged_adam(const PRB_Tensor* param, const PRB_Tensor* grad, const P
   A.param = param; A.grad = grad; A.lr = learning_rate; A.lr_stride = 1; A.mom1 = moment1; A.mom2 = moment2;
   A.b1pow = beta1_pow; A.b2pow = beta2_pow; A.pow_from_first = false; A.master = multi_precision ? master_param : nullptr;
   A.num = num; A.skip = nullptr; A.beta1 = (float)beta1; A.beta2 = (float)beta2; A.epsilon = (float)epsilon;
+  A.beta1_d = beta1; A.beta2_d = beta2; A.epsilon_d = epsilon;
   A.lr_ratio = nullptr; A.coeff = nullptr; A.use_decay = 0; A.multi_precision = multi_precision != 0;
   A.use_global_beta_pow = use_global_beta_pow != 0; A.param_out = param_out; A.mom1_out = moment1_out;
   A.mom2_out = moment2_out; A.b1pow_out = beta1_pow_out; A.b2pow_out = beta2_pow_out;
@@ -581,6 +674,9 @@ int32_t prb_fused_adam(const PRB_Tensor* params, const PRB_Tensor* grads, const 
   A.b1pow = beta1_pows; A.b2pow = beta2_pows; A.pow_from_first = true;  // ref fused_adam_kernel.cu:292-293,368-369
   A.master = multi_precision ? master_params : nullptr; A.num = num; A.skip = skip_update; A.beta1 = (float)beta1;
   A.beta2 = (float)beta2; A.epsilon = (float)epsilon; A.lr_ratio = nullptr; A.coeff = coeffs.data();
+  A.beta1_d = beta1; A.beta2_d = beta2; A.epsilon_d = epsilon;
+  std::vector<double> coeffs_d(coeffs.begin(), coeffs.end());
+  A.coeff_d = coeffs_d.data();
   A.use_decay = use_adamw ? 1 : 0; A.multi_precision = multi_precision != 0;
   A.use_global_beta_pow = use_global_beta_pow != 0; A.param_out = params_out; A.mom1_out = moments1_out;
   A.mom2_out = moments2_out; A.b1pow_out = beta1_pows_out; A.b2pow_out = beta2_pows_out;

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "prb_bucket.cuh"
+#include "prb_fp64.h"
 
 namespace prb {
 namespace {
@@ -123,6 +124,9 @@ int32_t prb_scale(const PRB_Tensor* x, double scale, float bias, int32_t bias_af
   PRB_ENFORCE(x->numel == out->numel && x->dtype == out->dtype, PRB_INVALID_ARGUMENT, "scale: x/out mismatch");
   PRB_ENFORCE(x->device >= 0 && out->device >= 0, PRB_INVALID_ARGUMENT, "scale: device tensors required");
   if (x->numel <= 0) return PRB_SUCCESS;  // ref scale_kernel.cu:59-61
+  if (x->dtype == PRB_FLOAT64)              // MT = double (ref scale_kernel.cu:70-75)
+    return launch_scale_f64(reinterpret_cast<const double*>(x->data), reinterpret_cast<double*>(out->data), x->numel, scale,
+                            (double)bias, bias_after_scale != 0, (cudaStream_t)stream);
   MapDesc d{};
   d.src = x->data;
   d.dst = out->data;
@@ -205,6 +209,41 @@ int32_t cast_from(const void* in, void* out, int32_t dt_out, int64_t n, cudaStre
 }
 }  // namespace
 }  // namespace prb
+
+namespace prb {
+namespace {
+// out = T(MT(x) * *y): elementwise multiply by a one-element float32 device tensor (the broadcast multiply behind
+// AmpScaler.scale, ref python/paddle/amp/grad_scaler.py:152-200 `var * self._scale`)
+template <typename T>
+__global__ void mul_scalar_tensor_kernel(const T* __restrict__ x, const float* __restrict__ y, T* __restrict__ out, int64_t n) {
+  const float s = __ldg(y);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    out[i] = Conv<T>::from_f32(__fmul_rn(Conv<T>::to_f32(x[i]), s));
+}
+}  // namespace
+}  // namespace prb
+
+extern "C" int32_t prb_multiply_by_scalar_tensor(const PRB_Tensor* x, const PRB_Tensor* y, PRB_Tensor* out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  PRB_TRY(prb::require_device());
+  PRB_ENFORCE(x && y && out && x->numel == out->numel && x->dtype == out->dtype, PRB_INVALID_ARGUMENT,
+              "multiply: x/out mismatch");
+  PRB_ENFORCE(y->numel == 1 && y->dtype == PRB_FLOAT32 && y->device >= 0 && x->device >= 0 && out->device >= 0,
+              PRB_INVALID_ARGUMENT, "multiply: y must be one float32 on the device, x and out device tensors");
+  if (x->numel == 0) return PRB_SUCCESS;
+  const int64_t n = x->numel;
+  const int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
+  const float* yp = reinterpret_cast<const float*>(y->data);
+  switch (x->dtype) {
+    case PRB_FLOAT32: prb::mul_scalar_tensor_kernel<float><<<blocks, 256, 0, stream>>>((const float*)x->data, yp, (float*)out->data, n); break;
+    case PRB_BFLOAT16: prb::mul_scalar_tensor_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>((const __nv_bfloat16*)x->data, yp, (__nv_bfloat16*)out->data, n); break;
+    case PRB_FLOAT16: prb::mul_scalar_tensor_kernel<__half><<<blocks, 256, 0, stream>>>((const __half*)x->data, yp, (__half*)out->data, n); break;
+    default: PRB_FAIL(PRB_UNIMPLEMENTED, "multiply: dtype %s is not built", prb::dtype_name(x->dtype));
+  }
+  PRB_LAUNCH_CHECK();
+  return PRB_SUCCESS;
+}
 
 extern "C" int32_t prb_cast(const PRB_Tensor* x, PRB_Tensor* out, void* stream) {
   PRB_TRY(prb::require_device());

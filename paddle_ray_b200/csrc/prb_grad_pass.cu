@@ -2,6 +2,7 @@
 // See prb_grad_pass.cuh for the design and the reference citations.
 #include <vector>
 
+#include "prb_fp64.h"
 #include "prb_grad_pass.cuh"
 
 namespace prb {
@@ -361,8 +362,10 @@ int32_t prb_check_finite_and_unscale(const PRB_Tensor* xs, int64_t num, const PR
   PRB_TRY(require_device());
   PRB_ENFORCE(scale && found_infinite && num >= 0 && (xs || num == 0), PRB_INVALID_ARGUMENT,
               "check_finite_and_unscale: NULL argument");
-  PRB_ENFORCE(scale->numel == 1 && scale->dtype == PRB_FLOAT32 && scale->device >= 0, PRB_INVALID_ARGUMENT,
-              "check_finite_and_unscale: Scale must be one float32 on the device");
+  const bool f64 = num > 0 && xs[0].dtype == PRB_FLOAT64;  // T = MT = double: the scale is a double tensor too
+  PRB_ENFORCE(scale->numel == 1 && scale->dtype == (f64 ? PRB_FLOAT64 : PRB_FLOAT32) && scale->device >= 0,
+              PRB_INVALID_ARGUMENT, "check_finite_and_unscale: Scale must be one %s on the device",
+              f64 ? "float64 (float64 gradients)" : "float32");
   PRB_ENFORCE(found_infinite->numel == 1 && found_infinite->dtype == PRB_BOOL && found_infinite->device >= 0,
               PRB_INVALID_ARGUMENT, "check_finite_and_unscale: FoundInfinite must be one bool on the device");
   // InverseAndMemset: *found_inf = false (ref amp_kernel.cu:27-31); the inverse is taken in-kernel.
@@ -375,6 +378,14 @@ int32_t prb_check_finite_and_unscale(const PRB_Tensor* xs, int64_t num, const PR
                 "check_finite_and_unscale: device tensors required");
     if (outs) PRB_ENFORCE(outs[i].numel == xs[i].numel && outs[i].dtype == dt, PRB_INVALID_ARGUMENT,
                           "check_finite_and_unscale: outs[%lld] does not match xs[%lld]", (long long)i, (long long)i);
+  }
+  if (f64) {  // ref amp_kernel.cu:352-357: one launch per tensor, not on the north-star path
+    for (int64_t i = 0; i < num; ++i)
+      PRB_TRY(launch_unscale_f64(reinterpret_cast<const double*>(xs[i].data),
+                                 reinterpret_cast<double*>((outs ? outs[i] : xs[i]).data), xs[i].numel,
+                                 reinterpret_cast<const double*>(scale->data),
+                                 reinterpret_cast<bool*>(found_infinite->data), stream));
+    return PRB_SUCCESS;
   }
   DeviceTable tab;
   PRB_TRY(grad_table(xs, outs, num, -1, stream, &tab));
@@ -391,6 +402,9 @@ int32_t prb_squared_l2_norm(const PRB_Tensor* x, PRB_Tensor* out, void* stream_)
   PRB_ENFORCE(x && out, PRB_INVALID_ARGUMENT, "squared_l2_norm: NULL tensor");
   PRB_ENFORCE(out->numel == 1 && out->dtype == x->dtype && out->device >= 0 && x->device >= 0, PRB_INVALID_ARGUMENT,
               "squared_l2_norm: out must be one element of x's dtype on the device");
+  if (x->dtype == PRB_FLOAT64)  // ref squared_l2_norm_kernel.cu:38-43
+    return launch_squared_l2_norm_f64(reinterpret_cast<const double*>(x->data), x->numel,
+                                      reinterpret_cast<double*>(out->data), stream);
   DeviceTable tab;
   PRB_TRY(grad_table(x, nullptr, 1, -1, stream, &tab));
   void* ws = nullptr;

@@ -40,21 +40,22 @@ static_assert((int64_t)kNaMaxChunks * kNaChunk == PRB_NOALLOC_MAX_NUMEL, "header
 // a device pointer and must never be passed to a kernel as one.
 static __device__ __align__(256) float g_noalloc_scratch[kScratchFloats];
 
-// Per-device cache of the array's device address (filled on the first call on that device).
-float* g_scratch_addr[64] = {nullptr};
+// Per-device cache of the array's device address (filled on the first call on that device; two threads that race
+// on the first call store the same value).
+std::atomic<float*> g_scratch_addr[64];
 
 int32_t scratch_for_current_device(float** out) {
   int dev = -1;
   PRB_CUDA(cudaGetDevice(&dev));
   PRB_ENFORCE(dev >= 0 && dev < 64, PRB_OUT_OF_RANGE, "squared_l2_norm_noalloc: device ordinal %d not supported", dev);
-  if (g_scratch_addr[dev] == nullptr) {
+  if (g_scratch_addr[dev].load(std::memory_order_acquire) == nullptr) {
     float* p = nullptr;
     // With `dev` current this yields the address of dev's copy of the array.
     PRB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
     PRB_ENFORCE(p != nullptr, PRB_EXTERNAL, "squared_l2_norm_noalloc: the scratch array has no device address");
-    g_scratch_addr[dev] = p;
+    g_scratch_addr[dev].store(p, std::memory_order_release);
   }
-  *out = g_scratch_addr[dev];
+  *out = g_scratch_addr[dev].load(std::memory_order_acquire);
   return PRB_SUCCESS;
 }
 
@@ -161,6 +162,8 @@ extern "C" int32_t prb_squared_l2_norm_noalloc(const PRB_Tensor* x, PRB_Tensor* 
               "squared_l2_norm_noalloc: x has %lld elements but the fixed scratch covers at most %lld; use "
               "prb_squared_l2_norm (which allocates) or reduce the tensor in pieces",
               (long long)x->numel, (long long)PRB_NOALLOC_MAX_NUMEL);
+  PRB_ENFORCE(out->data != nullptr && (x->data != nullptr || x->numel == 0), PRB_INVALID_ARGUMENT,
+              "squared_l2_norm_noalloc: NULL data pointer");
   int dev = -1;
   PRB_CUDA(cudaGetDevice(&dev));
   PRB_ENFORCE(x->device == dev && out->device == dev, PRB_INVALID_ARGUMENT,

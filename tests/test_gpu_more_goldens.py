@@ -1,6 +1,5 @@
-"""PREPARED, NOT YET RUN ON A GPU (round 1 ended with the GPU budget spent): move to tests/ after a green run.
-
-GPU parity against the fixtures added at the end of round 1:
+"""GPU parity of the CUDA path against three more fixture families generated from the reference's own tests
+(tests/golden/make_golden.py):
   * fused_adam_optest.npz      -- test_fused_adam_op.py (inputs exactly as that OpTest builds them) + fused_adam_step
   * adamw_layerwise.npz        -- test_adamw_op.py:614-755, lr_ratio per layer, five steps, rtol 1e-6
   * update_loss_scaling_cases  -- test_update_loss_scaling_op.py:52-136, the two known-answer cases
