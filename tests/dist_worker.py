@@ -134,6 +134,33 @@ def main(out_dir):
         else:
             np.testing.assert_allclose(p.grad.numpy(), want, rtol=1e-6, atol=1e-8)
         np.save(os.path.join(out_dir, "unused_grad_%d_r%d.npy" % (i, rank)), p.grad.numpy())
+    # sharded optimizer state (ZeRO-1, ref dygraph_sharding_optimizer.py): each parameter is updated by its owner only
+    # and broadcast; every rank must end with exactly the bits of the replicated optimizer
+    def make(prefix):
+        ps = []
+        for i, sz in enumerate(sizes):
+            p = prb.Tensor.from_numpy(np.random.default_rng(100 + i).normal(0, 0.02, sz).astype(np.float32), name="%s_%d" % (prefix, i))
+            p.grad = prb.Tensor.from_numpy(grads_all[i][rank])
+            ps.append(p)
+        return ps
+    pa, pb = make("rep"), make("shd")
+    dpa = prb.DataParallel(pa, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True)
+    dpb = prb.DataParallel(pb, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True)
+    oa = prb.optimizer.AdamW(learning_rate=1e-3, parameters=pa, weight_decay=0.01)
+    ob = prb.distributed.DygraphShardingOptimizer(prb.distributed.ShardingGroup(group), None, pb, prb.optimizer.AdamW,
+                                                  learning_rate=1e-3, weight_decay=0.01)
+    owned = ob._rank2params[rank]
+    assert 0 < len(owned) < len(pb) and set(ob._param2rank.values()) == set(range(n))
+    for step in range(3):
+        for dp_, op_ in ((dpa, oa), (dpb, ob)):
+            dp_.prepare_for_backward()
+            dp_.mark_all_ready()
+            op_.step()
+        prb.current_stream().synchronize()
+        for i, (a, b) in enumerate(zip(pa, pb)):
+            assert a.numpy().tobytes() == b.numpy().tobytes(), "sharded step %d param %d" % (step, i)
+            np.save(os.path.join(out_dir, "shard_param_%d_%d_r%d.npy" % (step, i, rank)), b.numpy())
+    assert set(ob._accumulators) == {p.name for p in owned}   # moments exist for the local shard only
     # timing helper used by bench.py: max over ranks through the communicator
     t = prb.Tensor.from_numpy(np.array([float(rank + 1)], np.float32))
     group.all_reduce(t, "max")

@@ -238,3 +238,34 @@ def test_fleet_build_groups_matches_reference_rule(prb):
     groups = prb.distributed.build_groups(vs, 700)
     assert [[v.numel for v in g] for g in groups] == [[100, 100], [100], [50, 50], [10]]
     assert [[v.numel for v in g] for g in prb.distributed.build_groups(vs, 10 ** 9)] == [[100, 100, 100], [50, 50], [10]]
+
+
+def test_sharding_optimizer_partitions_parameters_greedily():
+    """ref dygraph_sharding_optimizer.py:101-126: each parameter goes to the rank holding the fewest elements so far."""
+    from paddle_ray_b200.core import Tensor
+    from paddle_ray_b200.distributed.sharding import DygraphShardingOptimizer
+
+    class HCG:
+        def get_sharding_parallel_world_size(self):
+            return 3
+
+        def get_sharding_parallel_rank(self):
+            return 1
+
+        def get_sharding_parallel_group(self):
+            return None
+
+    class Inner:
+        def __init__(self, parameters, **kw):
+            self.parameters, self.kw, self._grad_clip = parameters, kw, None
+
+    sizes = [100, 10, 50, 60, 5, 200, 1]
+    params = [Tensor(n, "float32", device=-1, name="p%d" % i) for i, n in enumerate(sizes)]
+    opt = DygraphShardingOptimizer(HCG(), None, params, Inner, learning_rate=0.1)
+    got = {r: [p.name for p in ps] for r, ps in opt._rank2params.items()}
+    # p0->0 (100,0,0) p1->1 (100,10,0) p2->2 (100,10,50) p3->1 (100,70,50) p4->2 (100,70,55) p5->2 (100,70,255) p6->1
+    assert got == {0: ["p0"], 1: ["p1", "p3", "p6"], 2: ["p2", "p4", "p5"]}
+    assert [p.name for p in opt._inner_optimizer.parameters] == ["p1", "p3", "p6"] and opt.kw == {"learning_rate": 0.1}
+    assert opt._param2rank["p5"] == 2
+    with pytest.raises(TypeError):
+        DygraphShardingOptimizer(HCG(), None, tuple(params), Inner)

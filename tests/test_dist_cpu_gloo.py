@@ -80,3 +80,27 @@ def test_world_size_2_gloo(tmp_path):
         a = np.load(os.path.join(str(tmp_path), "g%d_r0.npy" % i))
         b = np.load(os.path.join(str(tmp_path), "g%d_r1.npy" % i))
         assert a.tobytes() == b.tobytes()
+
+
+def test_bench_reference_arm_runs_gloo_allreduce_with_all_cores():
+    """`bench.py --impl reference --gpus 2`: two local CPU processes, gloo allreduce per bucket, an explicit thread
+    count (not the OMP_NUM_THREADS=1 a launcher exports), and the `config` keys of the GPU arm."""
+    import json
+    import subprocess
+
+    env = {**os.environ, "OMP_NUM_THREADS": "1", "RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0"}
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
+                          "--warmup", "1", "--workload", "resnet18"], env=env, capture_output=True, timeout=300)
+    assert out.returncode == 0, out.stderr.decode()[-2000:]
+    line = json.loads(out.stdout.decode().strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0
+    assert "gloo" in line["details"]["allreduce"]
+    assert line["cpu_baseline"]["cores"] >= 2 and line["cpu_baseline"]["kind"] == "port"
+    sys.path.insert(0, ROOT)
+    import bench
+    want = bench.config_block("x", 1, 1, 1, "float32", "float32", False, False, 36, 2)
+    assert set(line["config"]) == set(want)
+    # a rank other than 0 under the launcher prints nothing and exits 0
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
+                         env={**env, "RANK": "1"}, capture_output=True, timeout=60)
+    assert out.returncode == 0 and out.stdout.decode().strip() == ""
