@@ -502,7 +502,7 @@ def parity_preamble(prb, group, arena=False, save_dir=None):
     injected on ONE rank (every rank must skip and halve its loss scale), two more clean steps (even steps mark all
     gradients ready in one call, odd steps hook by hook).  After each step
     parameters, masters, moments and the scaler state must be bit-equal across ranks (checksums compared through
-    the communicator); with two ranks (one addition, so the order cannot matter) they must also equal the oracle's
+    the communicator); with one or two ranks (at most one addition, so the order cannot matter) they must also equal the oracle's
     composition of the reference's stages bit for bit.  Returns "ok" or "fail: <what>"."""
     from oracle import oracle as orc
     rank, n = group.rank, group.nranks
@@ -562,7 +562,7 @@ def parity_preamble(prb, group, arena=False, save_dir=None):
             mx, mn = t.numpy()
             if mx != -mn:
                 return "fail: step %d state differs across ranks" % step
-            if n == 2 and dp._reducer.allreduce_backend != "nvls":   # (the NVSwitch's own adder is not bit-pinned)
+            if n <= 2 and dp._reducer.allreduce_backend != "nvls":   # (the NVSwitch's own adder is not bit-pinned)
                 red = []
                 for i in range(len(sizes)):
                     s = sum(orc.to_f32(orc.scale(per_rank[r][i], orc.BF16, 1.0 / n), orc.BF16).astype(np.float64) for r in range(n))
