@@ -43,6 +43,7 @@ template <typename T, typename Op>
 __global__ void __launch_bounds__(kMapThreads, kMapMinBlocks) map_chunks_kernel(const MapDesc* __restrict__ descs,
                                                                                 const Chunk* __restrict__ chunks,
                                                                                 const Op op) {
+  pdl_trigger();  // a dependent launch behind this one may start filling SMs as the grid drains
   const int4 craw = __ldg(reinterpret_cast<const int4*>(chunks) + blockIdx.x);
   const int n = craw.y;
   const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);

@@ -114,7 +114,33 @@ int32_t workspace(size_t bytes, void** out, int slot, cudaStream_t stream);
 // Launches on one stream are ordered, so they may share it; launches on different streams get their own.
 int32_t ticket_counter(void** out, cudaStream_t stream);
 
+bool pdl_enabled();  // PRB_PDL=0 switches programmatic dependent launch off (A/B aid)
+
 #ifdef __CUDACC__
+// ---------------------------------------------------------------- programmatic dependent launch
+// The kernels of one step form a chain on one stream (pack -> norm finalize -> update).  Launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, a kernel's CTAs may be scheduled while the previous kernel is
+// still draining (as soon as every CTA of that kernel has executed pdl_trigger or exited); whatever depends on the
+// previous kernel's results comes after pdl_wait, which returns only when that kernel has completed and its
+// writes are visible.  Both instructions are no-ops in a normally launched kernel.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), int grid, int block, cudaStream_t stream, bool pdl,
+                                 Args&&... args) {
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.stream = stream;
+  cfg.attrs = attr;
+  cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---------------------------------------------------------------- element conversions
 // MT = float for every supported T (ref: paddle/phi/common/amp_type_traits.h:24-39).
 template <typename T>

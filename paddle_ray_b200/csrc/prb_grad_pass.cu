@@ -18,6 +18,7 @@ __global__ void __launch_bounds__(kGradThreads, 2) grad_pass_kernel(const GradDe
                                                                     float* __restrict__ partials,
                                                                     const float pack_scale, const float pack_bias) {
   __shared__ float red[kGradThreads / 32];
+  pdl_trigger();  // the finalize / update that follows may start filling SMs as this grid drains
   const int4 craw = __ldg(reinterpret_cast<const int4*>(chunks) + blockIdx.x);
   const int n = craw.y;
   const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
@@ -112,6 +113,8 @@ __global__ void __launch_bounds__(kFinThreads) norm_finalize_kernel(const NormFi
   __shared__ float s_group[3];
   __shared__ unsigned int s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = kFinThreads >> 5;
+  pdl_trigger();  // lets the update pass start its parameter / moment loads under this (latency-bound) kernel
+  pdl_wait();     // the partials come from the previous kernel
   // ---- phase 1: per-tensor sums
   int big_seen = 0, small_seen = 0;  // running counts over all groups: the round-robin keys (uniform in the CTA)
   for (int gi = 0; gi < a.ngroups; ++gi) {
@@ -310,7 +313,7 @@ int32_t launch_norm_finalize(const NormFinalizeArgs& a, cudaStream_t stream) {
   void* tk = nullptr;
   if (grid > 1) PRB_TRY(ticket_counter(&tk, stream));
   KernelTimer kt(KK_NORM_FINALIZE, stream);
-  norm_finalize_kernel<<<grid, kFinThreads, 0, stream>>>(a, reinterpret_cast<unsigned int*>(tk));
+  PRB_CUDA(launch_kernel(norm_finalize_kernel, grid, kFinThreads, stream, a.pdl != 0, a, reinterpret_cast<unsigned int*>(tk)));
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }

@@ -66,6 +66,7 @@ struct NormFinalizeArgs {
   float* norm_out;       // optional fp32 device scalar
   float* clip_out;       // fp32 device scalar (1.0f means "leave gradients untouched")
   int32_t grid_hint;     // CTAs worth launching (finalize_grid_hint); the result does not depend on it
+  int32_t pdl;           // 1: launch as a programmatic dependent of the kernel before it in the stream
 };
 
 // How many CTAs the finalize can keep busy: one per tensor of more than 256 chunks, one per 32 smaller ones.

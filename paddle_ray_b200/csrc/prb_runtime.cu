@@ -43,6 +43,14 @@ int sm_count() {
   return cached[dev];
 }
 
+bool pdl_enabled() {
+  static const bool v = [] {
+    const char* e = getenv("PRB_PDL");
+    return !(e != nullptr && atoi(e) == 0);
+  }();
+  return v;
+}
+
 namespace {
 struct Slot {
   void* ptr = nullptr;
