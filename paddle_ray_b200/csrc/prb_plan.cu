@@ -21,6 +21,8 @@ struct Entry {
 std::mutex g_mu;
 std::list<Entry> g_lru;  // front = most recent
 constexpr size_t kMaxPlans = 64;
+constexpr size_t kGrace = 16;
+std::list<void*> g_parked;  // evicted device tables awaiting their free
 
 uint64_t fnv1a(const uint8_t* p, size_t n, uint64_t h = 1469598103934665603ull) {
   for (size_t i = 0; i < n; ++i) {
@@ -88,8 +90,15 @@ int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const i
     for (auto it = g_lru.end(); it != g_lru.begin();) {  // least recently used entry that nobody holds on to
       --it;
       if (it->pinned) continue;
-      cudaFree(it->dev_blob);  // synchronises the device: no kernel still reads the evicted plan
+      // The evicted table is not freed at once: another host thread may have fetched it a moment ago and be about
+      // to launch with it.  It is parked and freed kGrace evictions later (cudaFree synchronises the device, so no
+      // kernel still reads it then).
+      g_parked.push_back(it->dev_blob);
       g_lru.erase(it);
+      if (g_parked.size() > kGrace) {
+        cudaFree(g_parked.front());
+        g_parked.pop_front();
+      }
       break;
     }
   }
