@@ -169,3 +169,39 @@ def test_gradients_produced_in_the_arena(prb, dtype, amp, clip):
             bits_equal(oa._accumulators[a.name]["moment2"].numpy(), ob._accumulators[b.name]["moment2"].numpy())
         if clip:
             bits_equal(ca.last_clip.numpy(), cb.last_clip.numpy())
+
+
+@pytest.mark.parametrize("dtype", [orc.BF16, orc.F32])
+def test_clip_with_exactly_representable_norm(prb, dtype):
+    """Gradients whose squares and partial sums are exact whatever the summation order, so norm and clip factor must
+    equal the oracle's BIT FOR BIT.  bf16: two tensors of 4097 ones have per-tensor sums 4097, which the op's T-typed
+    output rounds to 4096 (squared_l2_norm_kernel.cu:23-35 writes T); with 2048 twos (8192) the group sum is 16384,
+    the norm 128 and the factor 2^-7 -- an implementation that forgot the per-tensor rounding gets sqrt(16386)."""
+    sizes = [4097, 4097, 2048]
+    vals = [1.0, 1.0, 2.0]
+    grads = [orc.from_f32(np.full(n, v, np.float32), dtype) for n, v in zip(sizes, vals)]
+    want_norm, want_clip = orc.global_norm_clip([g.copy() for g in grads], [dtype] * 3, 1.0)
+    if dtype == orc.BF16:
+        assert want_norm == 128.0 and want_clip == 2.0 ** -7
+    else:
+        assert want_norm == np.float32(np.sqrt(np.float32(16386.0)))
+    # (1) the operator
+    ts = [prb.Tensor.from_numpy(g, dtype) for g in grads]
+    norm, clip = prb._C_ops.clip_grad_by_global_norm_(ts, 1.0)
+    assert norm.numpy()[0] == np.float32(want_norm) and clip.numpy()[0] == np.float32(want_clip)
+    # (2) the fused step, pass 1 in the tail (step 0) and in the reducer's pack (step 1)
+    params = []
+    for i, g in enumerate(grads):
+        p = prb.Tensor.from_numpy(orc.from_f32(np.zeros(g.size, np.float32), dtype), dtype, name="e_%d" % i)
+        p.grad = prb.Tensor.from_numpy(g, dtype)
+        params.append(p)
+    c = prb.nn.ClipGradByGlobalNorm(1.0)
+    opt = prb.optimizer.AdamW(learning_rate=1e-3, parameters=params, grad_clip=c, multi_precision=dtype != orc.F32)
+    dp = prb.DataParallel(params, comm_buffer_size=0.01, last_comm_buffer_size=0.001, consume_from_buckets=True)
+    for step in range(2):
+        dp.prepare_for_backward()
+        dp.mark_all_ready()
+        opt.step()
+        assert dp._epilogue_armed == (step == 1)
+        assert c.last_global_norm.numpy()[0] == np.float32(want_norm), step
+        assert c.last_clip.numpy()[0] == np.float32(want_clip), step
