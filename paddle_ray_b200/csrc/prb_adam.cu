@@ -104,9 +104,9 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
   // Per-tensor coefficients are fetched and derived by ONE thread (while the data loads of the
   // whole CTA are in flight) and broadcast through shared memory.
   __shared__ Coef sk;
-  // ---- prologue: nothing here depends on the kernels that ran earlier in this step (static tables, and the
-  // parameters / moments, which only this kernel writes), so under a programmatic dependent launch it overlaps
-  // the tail of the kernel before it
+  const bool skipped = a.skip != nullptr && *a.skip;
+  if (skipped && !a.zero_grad) return;
+
   const int4 craw = __ldg(reinterpret_cast<const int4*>(a.chunks) + blockIdx.x);
   const int tensor = craw.x;
   const int n = craw.y;
@@ -120,28 +120,7 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
   float* __restrict__ mp_ptr = kMaster ? d->master + offset : nullptr;
   TG* __restrict__ go_ptr = d->grad_out ? reinterpret_cast<TG*>(d->grad_out) + offset : nullptr;
   const bool aligned = d->aligned != 0;
-  const int nvec = n / kVec;
-  Pack<T> pv[kAdamUnroll];
-  Pack<float> mpv[kAdamUnroll];
-  Pack<TG> gv[kAdamUnroll];
-  Pack<float> m1v[kAdamUnroll], m2v[kAdamUnroll];
-  if (aligned) {
-#pragma unroll
-    for (int u = 0; u < kAdamUnroll; ++u) {
-      const int v = u * kAdamThreads + threadIdx.x;
-      if (v < nvec) {
-        const int e = v * kVec;
-        if (kMaster) load_vec<float>(mp_ptr + e, mpv[u]);
-        else load_vec<T>(p_ptr + e, pv[u]);
-        load_vec<float>(m1_ptr + e, m1v[u]);
-        load_vec<float>(m2_ptr + e, m2v[u]);
-      }
-    }
-  }
-  // ---- from here on: results of the kernels before this one (gradients, found_inf, clip factor, beta-pows)
-  pdl_wait();
-  const bool skipped = a.skip != nullptr && *a.skip;
-  if (skipped && !a.zero_grad) return;
+
   if (skipped) {
     // found_inf: the update is skipped, but the folded-in clear_grad still zeroes the gradient
     TG* __restrict__ gz = const_cast<TG*>(g_ptr);
@@ -150,11 +129,23 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
   }
 
   if (aligned) {
-    // ---- the gradient loads join the loads already in flight: every load of this thread is issued before the first use
+    const int nvec = n / kVec;
+    Pack<T> pv[kAdamUnroll];
+    Pack<float> mpv[kAdamUnroll];
+    Pack<TG> gv[kAdamUnroll];
+    Pack<float> m1v[kAdamUnroll], m2v[kAdamUnroll];
+    // ---- load phase: every load of this thread is in flight before the first use
 #pragma unroll
     for (int u = 0; u < kAdamUnroll; ++u) {
       const int v = u * kAdamThreads + threadIdx.x;
-      if (v < nvec) load_vec<TG>(g_ptr + v * kVec, gv[u]);
+      if (v < nvec) {
+        const int e = v * kVec;
+        if (kMaster) load_vec<float>(mp_ptr + e, mpv[u]);
+        else load_vec<T>(p_ptr + e, pv[u]);
+        load_vec<TG>(g_ptr + e, gv[u]);
+        load_vec<float>(m1_ptr + e, m1v[u]);
+        load_vec<float>(m2_ptr + e, m2v[u]);
+      }
     }
     if (threadIdx.x == 0) {
       sk = make_coef<TG>(d, a);
@@ -253,11 +244,9 @@ int32_t launch_typed(bool has_master, const AdamArgs& a, cudaStream_t stream) {
   if (a.nchunks == 0) return PRB_SUCCESS;
   KernelTimer kt(KK_ADAM, stream);
   if (has_master)
-    PRB_CUDA(launch_kernel(adam_chunks_kernel<T, TG, true, kAdamThreads, kAdamUnroll, kAdamMinBlocks>, a.nchunks, kAdamThreads,
-                           stream, a.pdl != 0, a));
+    adam_chunks_kernel<T, TG, true, kAdamThreads, kAdamUnroll, kAdamMinBlocks><<<a.nchunks, kAdamThreads, 0, stream>>>(a);
   else
-    PRB_CUDA(launch_kernel(adam_chunks_kernel<T, TG, false, kAdamThreads, kAdamUnroll, kAdamMinBlocks>, a.nchunks, kAdamThreads,
-                           stream, a.pdl != 0, a));
+    adam_chunks_kernel<T, TG, false, kAdamThreads, kAdamUnroll, kAdamMinBlocks><<<a.nchunks, kAdamThreads, 0, stream>>>(a);
   PRB_LAUNCH_CHECK();
   return PRB_SUCCESS;
 }

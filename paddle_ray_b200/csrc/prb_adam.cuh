@@ -41,10 +41,6 @@ struct AdamArgs {
   float* pow_b1;             // nullptr = off
   float* pow_b2;
   unsigned int* pow_ticket;  // zero-initialised device counter of the launching stream, reset by the last CTA
-  // 1: launch as a programmatic dependent of the kernel before it in the stream.  ONLY when that kernel is known
-  // not to write parameters or moments (the tail's own grad pass / finalize): the prologue loads them before
-  // pdl_wait.
-  int32_t pdl;
 };
 
 // Elements per CTA of the active launch geometry (threads * kVec * lane-vectors per thread).

@@ -118,11 +118,13 @@ bool pdl_enabled();  // PRB_PDL=0 switches programmatic dependent launch off (A/
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------- programmatic dependent launch
-// The kernels of one step form a chain on one stream (pack -> norm finalize -> update).  Launched with
-// cudaLaunchAttributeProgrammaticStreamSerialization, a kernel's CTAs may be scheduled while the previous kernel is
-// still draining (as soon as every CTA of that kernel has executed pdl_trigger or exited); whatever depends on the
-// previous kernel's results comes after pdl_wait, which returns only when that kernel has completed and its
-// writes are visible.  Both instructions are no-ops in a normally launched kernel.
+// The pack and the norm finalize of a step follow each other on one stream.  Launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, the finalize's few CTAs are scheduled while the pack is still
+// draining (as soon as every CTA of the pack has executed pdl_trigger or exited); what depends on the pack's results
+// comes after pdl_wait, which returns only when that kernel has completed and its writes are visible.  Both
+// instructions are no-ops in a normally launched kernel.  (Tried and dropped for the update pass: with 100 000
+// small CTAs the wait instruction itself cost 5 % of the kernel, and CTAs parked at the wait held the SMs the
+// finalize needed -- BERT-base step 0.67 -> 0.70 ms, profiles/r2_experiments.md.)
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 

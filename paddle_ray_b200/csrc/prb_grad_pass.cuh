@@ -69,11 +69,11 @@ struct NormFinalizeArgs {
   int32_t pdl;           // 1: launch as a programmatic dependent of the kernel before it in the stream
 };
 
-// How many CTAs the finalize can keep busy: one per tensor of more than 256 chunks, one per 32 smaller ones.
+// How many CTAs the finalize can keep busy: tensor t goes to CTA t % grid (large) or warp t % (grid * 32) (small).
 inline int finalize_grid_hint(const int64_t* numels, int64_t num) {
-  int64_t big = 0, small = 0;
-  for (int64_t i = 0; i < num; ++i) (numels[i] > (int64_t)256 * kGradChunk ? big : small)++;
-  const int64_t g = big + (small + 31) / 32;
+  int64_t big = 0;
+  for (int64_t i = 0; i < num; ++i) big += numels[i] > (int64_t)256 * kGradChunk ? 1 : 0;
+  const int64_t g = big > (num + 31) / 32 ? big : (num + 31) / 32;
   return (int)(g < 1 ? 1 : (g > 64 ? 64 : g));
 }
 

@@ -93,7 +93,6 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
     PRB_ENFORCE(found_inf->numel == 1 && found_inf->dtype == PRB_BOOL && found_inf->device >= 0, PRB_INVALID_ARGUMENT,
                 "dp_step_tail: found_inf must be one bool on the device");
   const float* clip_dev = nullptr;
-  bool launched_before = false;  // this call put a kernel in front of the update pass (it writes no parameter or moment)
 
   // pass1_done: the producer of the gradients (the reducer's pack at one rank, the exchange kernel at several; see
   // prb_reducer_set_grad_epilogue) already cleared found_inf, ran the check and left the norm partials in
@@ -127,7 +126,6 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
       o.found_inf = cfg->use_amp ? found : nullptr;
       o.partials = partials;
       PRB_TRY(launch_grad_pass(dt_g, gt, o, stream));
-      launched_before = true;
     }
     if (cfg->use_clip) {
       NormFinalizeArgs a{};
@@ -147,7 +145,6 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
       a.clip_out = clip_out ? reinterpret_cast<float*>(clip_out->data) : scratch_clip;
       PRB_TRY(launch_norm_finalize(a, stream));
       clip_dev = a.clip_out;
-      launched_before = true;
     }
   }
 
@@ -165,7 +162,6 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   a.loss_scale = ls;
   a.clip = clip_dev;
   a.zero_grad = cfg->zero_grads;
-  a.pdl = launched_before ? 1 : 0;
   // beta-pow accumulators advance inside the update kernel (last-CTA ticket) unless found_inf
   void* tk = nullptr;
   PRB_TRY(ticket_counter(&tk, stream));

@@ -16,7 +16,7 @@ print(d["roofline"]["frac"], d["e2e"]["ms_per_step"], d.get("cpu_baseline",{}).g
 for k,v in d.get("configs",{}).items(): print(k, {a:b for a,b in v.items() if a not in ("kernels","workload","roofline")}, {kk:round(vv["ms_per_step"],4) for kk,vv in v.get("kernels",{}).items()})
 PY
 if [ "$2" = "ncu" ]; then
-  timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/launches.csv \
+  timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"grad_pass_kernel|adam_chunks_kernel|norm_finalize_kernel|map_chunks_kernel|update_loss_scaling" -c 200 --csv --log-file $out/launches.csv \
       python bench.py --steps 5 --warmup 3 --no-configs --no-cpu-baseline > $out/ncu_list.log 2>&1; echo "ncu list rc=$?"
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:"grad_pass_kernel|adam_chunks_kernel|norm_finalize_kernel" \
       --launch-skip 12 --launch-count 3 -o $out/bert_full python bench.py --steps 5 --warmup 3 --no-configs --no-cpu-baseline > $out/ncu_full.log 2>&1; echo "ncu full rc=$?"
