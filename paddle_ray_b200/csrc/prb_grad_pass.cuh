@@ -107,6 +107,11 @@ struct Pair<__nv_bfloat16> {
     const __nv_bfloat162 r = __hmul2(v, v);
     return *reinterpret_cast<const uint32_t*>(&r);
   }
+  static __device__ __forceinline__ uint32_t add_zero(uint32_t w) {
+    uint32_t r;
+    asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(w), "r"(0u));
+    return r;
+  }
 };
 template <>
 struct Pair<__half> {
@@ -125,6 +130,11 @@ struct Pair<__half> {
     const __half2 r = __hmul2(v, v);
     return *reinterpret_cast<const uint32_t*>(&r);
   }
+  static __device__ __forceinline__ uint32_t add_zero(uint32_t w) {
+    uint32_t r;
+    asm("add.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(w), "r"(0u));
+    return r;
+  }
 };
 
 // Scale of the pack (mode 2): out = T(scale * (MT(x) + bias))   (ref scale_kernel.cu:35-40, bias_after_scale = false)
@@ -136,6 +146,14 @@ template <typename T>
 __device__ __forceinline__ void pack_scale_vec(Pack<T>& v, float scale, float bias) {
   if constexpr (sizeof(T) == 2) {
     uint32_t* w = reinterpret_cast<uint32_t*>(v.v);
+    if (scale == 1.0f && bias == 0.0f) {
+      // One rank: T(1.0f * (MT(x) + 0.0f)) only turns -0 into +0 and a NaN into the canonical NaN -- which is exactly
+      // what ONE packed add of +0 in T does (x + 0 is exact in any format; subnormals are kept).  1 instruction per
+      // pair instead of 7; bit-identical on all 65536 patterns (tests/test_gpu_fused_sync.py).
+#pragma unroll
+      for (int j = 0; j < kVec / 2; ++j) w[j] = Pair<T>::add_zero(w[j]);
+      return;
+    }
 #pragma unroll
     for (int j = 0; j < kVec / 2; ++j) {
       float lo, hi;

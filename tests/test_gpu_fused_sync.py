@@ -205,3 +205,25 @@ def test_clip_with_exactly_representable_norm(prb, dtype):
         assert dp._epilogue_armed == (step == 1)
         assert c.last_global_norm.numpy()[0] == np.float32(want_norm), step
         assert c.last_clip.numpy()[0] == np.float32(want_clip), step
+
+
+@pytest.mark.parametrize("dtype", [orc.BF16, orc.F16])
+def test_pack_of_every_16_bit_pattern_equals_the_scale_operator(prb, dtype):
+    """The one-rank pack takes a shortcut for 16-bit types (one packed add of +0 instead of unpack / add / multiply /
+    repack).  It must give the bits of scale_(x, 1.0, 0.0, False) for EVERY bit pattern -- signed zeros, subnormals,
+    infinities, NaNs included -- and the oracle's bits wherever the value is not a NaN."""
+    x = np.arange(65536, dtype=np.uint16)
+    p = prb.Tensor.from_numpy(x.copy(), dtype, name="allbits")
+    p.grad = prb.Tensor.from_numpy(x.copy(), dtype)
+    dp = prb.DataParallel([p], consume_from_buckets=True)
+    active, _ = dp._reducer.set_grad_epilogue(partial_base=np.zeros(1, np.int32))   # norm partials only
+    assert active
+    dp.prepare_for_backward()
+    dp.mark_all_ready()
+    got = dp.bucket_grads()[0].numpy()
+    ref = prb._C_ops.scale(p.grad, 1.0, 0.0, False).numpy()        # the element-wise operator kernel
+    bits_equal(got, ref)
+    want = orc.scale(x, dtype, 1.0)
+    finite = np.isfinite(orc.to_f32(x, dtype)) | np.isinf(orc.to_f32(x, dtype))
+    bits_equal(got[finite], want[finite])
+    assert got[0x8000] == 0                                        # -0 -> +0
