@@ -86,7 +86,12 @@ int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const i
   if (!chunks.empty()) memcpy(blob.data() + chunks_off, chunks.data(), chunks.size() * sizeof(Chunk));
   memcpy(blob.data() + first_off, first.data(), first.size() * 4);
 
-  if (g_lru.size() >= kMaxPlans) {
+  // The LRU bounds the UNPINNED plans only: pinned ones (a reducer's pack / unpack / exchange tables) live as long as
+  // their owner says.  (Counting them used to let a few reducers fill the cache, after which every step of an
+  // unrelated optimizer rebuilt -- and synchronously uploaded -- its tables: nested benchmark configs ran 2x slower.)
+  size_t unpinned = 0;
+  for (const Entry& x : g_lru) unpinned += x.pinned ? 0 : 1;
+  if (unpinned >= kMaxPlans) {
     for (auto it = g_lru.end(); it != g_lru.begin();) {  // least recently used entry that nobody holds on to
       --it;
       if (it->pinned) continue;
@@ -123,6 +128,13 @@ int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const i
   g_lru.push_front(std::move(e));
   *out = g_lru.front().table;
   return PRB_SUCCESS;
+}
+
+void release_table(const DeviceTable& t) {
+  if (t.chunks == nullptr && t.descs == nullptr) return;
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (Entry& e : g_lru)
+    if (e.table.descs == t.descs && e.table.chunks == t.chunks) e.pinned = false;  // evictable from now on
 }
 
 }  // namespace prb

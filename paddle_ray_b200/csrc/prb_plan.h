@@ -26,4 +26,7 @@ struct DeviceTable {
 int32_t get_table(const void* host_descs, size_t desc_bytes, int ndescs, const int64_t* numels, int chunk_elems,
                   cudaStream_t stream, DeviceTable* out, bool pin = false);
 
+// The owner of a pinned plan no longer needs it: it becomes an ordinary LRU entry.
+void release_table(const DeviceTable& t);
+
 }  // namespace prb

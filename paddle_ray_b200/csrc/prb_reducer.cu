@@ -855,6 +855,10 @@ int32_t prb_reducer_create(const PRB_Tensor* grads, int64_t num, const int64_t* 
 int32_t prb_reducer_destroy(PRB_Reducer* r) {
   if (!r) return PRB_SUCCESS;
   if (!r->dry) cudaDeviceSynchronize();
+  for (Group& g : r->groups)
+    for (const DeviceTable* t : {&g.pack_tab, &g.unpack_tab, &g.packep_tab, &g.exch_tab}) release_table(*t);
+  for (const DeviceTable* t : {&r->batch_pack_tab, &r->batch_unpack_tab, &r->batch_packep_tab, &r->batch_exch_tab})
+    release_table(*t);
   if (r->arena_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(r->comm->comm, r->arena_reg);
   if (r->nvl) nvl_destroy(r->nvl);
   for (Group& g : r->groups) {
