@@ -736,7 +736,7 @@ def measure_overlap(prb, w, group, rank_max, device_barrier, steps=40):
     solo_group = prb.distributed.Group(h.value, 0, 1, group.device)
     dp_solo = prb.DataParallel(w["params"], comm_buffer_size=25, last_comm_buffer_size=1, group=solo_group)
     out = {"total_comm_ms": total_comm, "last_bucket_comm_ms": last_comm, "buckets": ng,
-           "overlap_cap": 1.0 - last_comm / total_comm, "cases": []}
+           "overlap_cap_estimate": 1.0 - last_comm / total_comm, "cases": []}
     for mult in (1.0, 2.0, 4.0):
         t_bwd_us = mult * total_comm * 1e3
         dp.consume_from_buckets(True)
@@ -750,11 +750,11 @@ def measure_overlap(prb, w, group, rank_max, device_barrier, steps=40):
                              "host_issue_ms": host_ms[-2]})
     dp.consume_from_buckets(True)
     out["overlap_frac"] = out["cases"][1]["overlap_frac"]
-    out["overlap_frac_of_cap"] = out["overlap_frac"] / out["overlap_cap"] if out["overlap_cap"] > 0 else None
+    out["overlap_frac_of_cap"] = out["overlap_frac"] / out["overlap_cap_estimate"] if out["overlap_cap_estimate"] > 0 else None
     out["definition"] = ("1 - exposed_comm/total_comm; exposed_comm = step - the same schedule (per-bucket pack, same "
                          "optimizer launches) on a single-rank communicator; synthetic backward = spin kernels between "
                          "bucket-ready points; start events lined up by a device-side allreduce; headline at "
-                         "T_bwd = 2 x total_comm.  overlap_cap = 1 - (exchange of the last bucket)/total_comm: the last "
+                         "T_bwd = 2 x total_comm.  overlap_cap_estimate = 1 - (exchange of the last bucket)/total_comm: the last "
                          "bucket's exchange can hide under nothing (BERT-base: the 47 MB word-embedding gradient is a "
                          "bucket of its own by the reference's assignment rule, reducer.cc:45-156)")
     return out
