@@ -195,8 +195,14 @@ struct PRB_Reducer {
   bool batching = false;
   std::vector<size_t> batch;
   std::vector<size_t> batch_key;
-  DeviceTable batch_pack_tab, batch_unpack_tab, batch_packep_tab, batch_exch_tab;
-  bool batch_valid = false, batch_packep_valid = false, batch_exch_valid = false;
+  // Tables of a batch.  With several ranks a batch is issued as two waves (a small first one, the rest) so that
+  // the first wave's exchange runs under the second wave's pack.
+  struct BatchWave {
+    std::vector<size_t> members;
+    DeviceTable pack_tab, unpack_tab, packep_tab, exch_tab;
+    bool valid = false, packep_valid = false, exch_valid = false;
+  };
+  BatchWave waves[2];
   std::vector<int64_t> launched;
 };
 
@@ -465,18 +471,25 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   return PRB_SUCCESS;
 }
 
-int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
-  if (r->batch.empty()) return PRB_SUCCESS;
-  if (r->batch_key != r->batch) r->batch_valid = r->batch_packep_valid = r->batch_exch_valid = false;
+int batch_waves() {
+  static const int v = [] {
+    const char* e = getenv("PRB_BATCH_WAVES");
+    return (e != nullptr && atoi(e) == 1) ? 1 : 2;
+  }();
+  return v;
+}
+
+int32_t flush_wave(PRB_Reducer* r, PRB_Reducer::BatchWave& w, cudaStream_t calc) {
+  if (w.members.empty()) return PRB_SUCCESS;
   PRB_Comm* c = r->comm;
   const bool multi = c->nranks > 1;
   const bool with_ep = epilogue_in_pack(r);
   const bool need_pack = !r->grads_in_arena;
-  if (need_pack && (with_ep ? !r->batch_packep_valid : !r->batch_valid)) {
+  if (need_pack && (with_ep ? !w.packep_valid : !w.valid)) {
     std::vector<MapDesc> pack, unpack;
     std::vector<GradDesc> packep;
     std::vector<int64_t> numels;
-    for (size_t gi : r->batch) {
+    for (size_t gi : w.members) {
       Group& g = r->groups[gi];
       const int es = dtype_size(g.dtype);
       for (size_t s = 0; s < g.vars.size(); ++s) {
@@ -498,43 +511,71 @@ int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
     }
     if (with_ep) {
       PRB_TRY(get_table(packep.data(), sizeof(GradDesc), (int)packep.size(), numels.data(), grad_chunk_elems(), calc,
-                        &r->batch_packep_tab, /*pin=*/true));
-      r->batch_packep_valid = true;
+                        &w.packep_tab, /*pin=*/true));
+      w.packep_valid = true;
     } else {
       PRB_TRY(get_table(pack.data(), sizeof(MapDesc), (int)pack.size(), numels.data(), map_chunk_elems(), calc,
-                        &r->batch_pack_tab, /*pin=*/true));
-      r->batch_valid = true;
+                        &w.pack_tab, /*pin=*/true));
+      w.valid = true;
     }
     PRB_TRY(get_table(unpack.data(), sizeof(MapDesc), (int)unpack.size(), numels.data(), map_chunk_elems(), calc,
-                      &r->batch_unpack_tab, /*pin=*/true));
+                      &w.unpack_tab, /*pin=*/true));
   }
-  if (multi && epilogue_in_exchange(r) && !r->batch_exch_valid) {
-    PRB_TRY(exchange_table(r, r->batch, calc, &r->batch_exch_tab));
-    r->batch_exch_valid = true;
+  if (multi && epilogue_in_exchange(r) && !w.exch_valid) {
+    PRB_TRY(exchange_table(r, w.members, calc, &w.exch_tab));
+    w.exch_valid = true;
   }
-  r->batch_key = r->batch;
-  const size_t first = r->batch.front(), last = r->batch.back();
-  const std::vector<size_t> members = r->batch;
+  const size_t first = w.members.front(), last = w.members.back();
   const int32_t dt = r->groups[first].dtype;
-  r->batch.clear();
-  PRB_TRY(epilogue_begin(r, calc));
-  PRB_TRY(epilogue_begin_exchange(r, calc));
   if (need_pack) {
-    if (with_ep) PRB_TRY(launch_grad_pass(dt, r->batch_packep_tab, packep_opts(r), calc));
-    else PRB_TRY(launch_scale(dt, r->batch_pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
+    if (with_ep) PRB_TRY(launch_grad_pass(dt, w.packep_tab, packep_opts(r), calc));
+    else PRB_TRY(launch_scale(dt, w.pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
   }
   if (!multi) {
-    if (r->unpack && need_pack) PRB_TRY(launch_copy(dtype_size(dt), r->batch_unpack_tab, calc));
+    if (r->unpack && need_pack) PRB_TRY(launch_copy(dtype_size(dt), w.unpack_tab, calc));
     return PRB_SUCCESS;
   }
-  // several ranks: ONE exchange for the whole batch (the groups' regions are adjacent in the arena)
+  // several ranks: ONE exchange for the whole wave (the groups' regions are adjacent in the arena)
   cudaStream_t cs = nvl_next_slot(r->nvl) == 1 ? c->stream2 : c->stream;
   Group& g0 = r->groups[first];
   PRB_CUDA(cudaEventRecord(g0.ready, calc));
   PRB_CUDA(cudaStreamWaitEvent(cs, g0.ready, 0));
-  PRB_TRY(nvl_exchange_groups(r, first, last, &r->batch_exch_tab, cs));
-  if (r->unpack && need_pack) PRB_TRY(launch_copy(dtype_size(dt), r->batch_unpack_tab, cs));
-  for (size_t gi : members) PRB_CUDA(cudaEventRecord(r->groups[gi].done, cs));
+  PRB_TRY(nvl_exchange_groups(r, first, last, &w.exch_tab, cs));
+  if (r->unpack && need_pack) PRB_TRY(launch_copy(dtype_size(dt), w.unpack_tab, cs));
+  for (size_t gi : w.members) PRB_CUDA(cudaEventRecord(r->groups[gi].done, cs));
+  return PRB_SUCCESS;
+}
+
+int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
+  if (r->batch.empty()) return PRB_SUCCESS;
+  if (r->batch_key != r->batch) {
+    // split: one rank -> one wave.  Several ranks -> a first wave of ~1/4 of the bytes (its exchange starts early and
+    // runs under the pack of the rest), then everything else; the exchange, not the pack, bounds the batch.
+    for (auto& w : r->waves) {
+      for (const DeviceTable* t : {&w.pack_tab, &w.unpack_tab, &w.packep_tab, &w.exch_tab}) release_table(*t);
+      w = PRB_Reducer::BatchWave();
+    }
+    size_t split = r->batch.size();
+    if (r->comm->nranks > 1 && batch_waves() > 1 && r->batch.size() >= 2) {
+      size_t total = 0, run = 0;
+      for (size_t gi : r->batch) total += (size_t)r->groups[gi].length * dtype_size(r->groups[gi].dtype);
+      for (split = 0; split + 1 < r->batch.size(); ++split) {
+        run += (size_t)r->groups[r->batch[split]].length * dtype_size(r->groups[r->batch[split]].dtype);
+        if (run * 4 >= total) {
+          ++split;
+          break;
+        }
+      }
+    }
+    r->waves[0].members.assign(r->batch.begin(), r->batch.begin() + (long)split);
+    r->waves[1].members.assign(r->batch.begin() + (long)split, r->batch.end());
+    r->batch_key = r->batch;
+  }
+  r->batch.clear();
+  PRB_TRY(epilogue_begin(r, calc));
+  PRB_TRY(epilogue_begin_exchange(r, calc));
+  PRB_TRY(flush_wave(r, r->waves[0], calc));
+  PRB_TRY(flush_wave(r, r->waves[1], calc));
   return PRB_SUCCESS;
 }
 
@@ -857,8 +898,8 @@ int32_t prb_reducer_destroy(PRB_Reducer* r) {
   if (!r->dry) cudaDeviceSynchronize();
   for (Group& g : r->groups)
     for (const DeviceTable* t : {&g.pack_tab, &g.unpack_tab, &g.packep_tab, &g.exch_tab}) release_table(*t);
-  for (const DeviceTable* t : {&r->batch_pack_tab, &r->batch_unpack_tab, &r->batch_packep_tab, &r->batch_exch_tab})
-    release_table(*t);
+  for (auto& w : r->waves)
+    for (const DeviceTable* t : {&w.pack_tab, &w.unpack_tab, &w.packep_tab, &w.exch_tab}) release_table(*t);
   if (r->arena_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(r->comm->comm, r->arena_reg);
   if (r->nvl) nvl_destroy(r->nvl);
   for (Group& g : r->groups) {
@@ -980,7 +1021,7 @@ int32_t prb_reducer_set_grad_epilogue(PRB_Reducer* r, const PRB_GradEpilogue* e,
   }
   r->ep = ep;
   for (Group& g : r->groups) g.packep_valid = g.exch_valid = false;
-  r->batch_packep_valid = r->batch_exch_valid = false;
+  for (auto& w : r->waves) w.packep_valid = w.exch_valid = false;
   if (partials_out != nullptr) {
     partials_out->data = sidecar(r);
     partials_out->numel = r->sidecar_floats;
