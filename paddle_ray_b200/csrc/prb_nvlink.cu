@@ -309,6 +309,17 @@ void fill_bar(const SignalSet& s, int nranks, int rank, Bar* b) {
   b->host_error = s.host_error_dev;
 }
 
+// Grid of the exchange kernels.  The kernel is NVLink-bound: 64 CTAs move as many bytes per second as one CTA on
+// each of the 148 SMs (8 ranks, 102 MB: 366 vs 374 us), but a grid that sits on EVERY SM slows the kernels of the
+// calc stream it is supposed to hide under -- with a 730 us backward at 8 ranks the exposed communication was 77 us
+// with 148 CTAs and 9 us with 64, 32 or 16 (profiles/r2_exchange_sweep_n8.log; NCCL, 580 us of exchanges: 12 us).
+// PRB_NVL_CTAS overrides; prb_reducer_set_exchange_ctas changes it at run time.
+static int default_ctas() {
+  int n = sm_count() < 64 ? sm_count() : 64;
+  if (const char* e = getenv("PRB_NVL_CTAS")) n = atoi(e) > 0 ? atoi(e) : n;
+  return n;
+}
+
 int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, size_t arena_bytes, cudaStream_t stream,
                   NvlContext** out) {
   *out = nullptr;
@@ -353,10 +364,7 @@ int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, s
     return vote;  // *out stays NULL: the caller keeps using NCCL (or reports the broken communicator)
   }
   fill_bar(c->sigs, nranks, rank, &c->args.bar);
-  int per_sm = 1;  // the kernel is NVLink-bound and mostly waits: more CTAs only take registers from the optimizer
-  if (const char* e = getenv("PRB_NVL_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
-  c->ctas = sm_count() * per_sm;
-  if (const char* e = getenv("PRB_NVL_CTAS")) c->ctas = atoi(e) > 0 ? atoi(e) : c->ctas;
+  c->ctas = default_ctas();
   *out = c;
   return PRB_SUCCESS;
 }
@@ -364,7 +372,7 @@ int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, s
 int nvl_next_slot(const NvlContext* c) { return c ? (int)((c->seq + 1) & (kSlots - 1)) : 0; }
 
 void nvl_set_max_ctas(NvlContext* c, int max_ctas) {
-  if (c) c->ctas = max_ctas > 0 ? max_ctas : sm_count();
+  if (c) c->ctas = max_ctas > 0 ? max_ctas : default_ctas();
 }
 
 namespace {

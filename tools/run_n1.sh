@@ -21,4 +21,8 @@ if [ "$2" = "ncu" ]; then
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:"grad_pass_kernel|adam_chunks_kernel|norm_finalize_kernel" \
       --launch-skip 12 --launch-count 3 -o $out/bert_full python bench.py --steps 5 --warmup 3 --no-configs --no-cpu-baseline > $out/ncu_full.log 2>&1; echo "ncu full rc=$?"
   ncu -i $out/bert_full.ncu-rep --page raw --csv > $out/bert_full_raw.csv 2>/dev/null
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:"map_chunks_kernel|adam_chunks_kernel" \
+      --launch-skip 8 --launch-count 2 -o $out/resnet_full python bench.py --workload resnet50 --steps 5 --warmup 3 --no-configs --no-cpu-baseline > $out/ncu_full_resnet.log 2>&1; echo "ncu resnet rc=$?"
+  ncu -i $out/resnet_full.ncu-rep --page raw --csv > $out/resnet_full_raw.csv 2>/dev/null
+  rm -f $out/*.ncu-rep
 fi
