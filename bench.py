@@ -372,7 +372,9 @@ def cpu_reference_run(workload, nranks, budget_s, threads, min_steps=2, max_step
     b1p, b2p = np.float32(0.9 ** 10), np.float32(0.999 ** 10)
     elems = int(sum(numels))
     # the reference's buckets: 1 MiB for the last parameters, 25 MiB otherwise, launched in reverse order
-    groups = orc.assign_group_by_size(numels, [orc.F32] * len(numels), [False] * len(numels), [1 << 20, 25 << 20])
+    # (grouped by the workload's OWN gradient dtype, so that both arms run the same buckets; the CPU stores them as fp32)
+    gcode = orc.F32 if gdt == "float32" else orc.BF16
+    groups = orc.assign_group_by_size(numels, [gcode] * len(numels), [False] * len(numels), [1 << 20, 25 << 20])
     groups = list(reversed(groups))
     buckets = [np.empty(sum(numels[v] for v in g), np.float32) for g in groups]  # a caching allocator reuses them
     grads = [np.empty(n, np.float32) for n in numels]
@@ -421,8 +423,9 @@ def reference_worker(args):
     import torch
     import torch.distributed as dist
     torch.set_num_threads(1)
+    import datetime
     dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % os.environ["PRB_REF_PORT"], rank=rank,
-                            world_size=world)
+                            world_size=world, timeout=datetime.timedelta(seconds=120))
     r = cpu_reference_run(args.workload, world, budget_s=120.0, threads=threads, min_steps=1, max_steps=args.steps,
                           warmup=args.warmup, dist=dist, rank=rank)
     if rank == 0:
@@ -461,14 +464,24 @@ def run_reference_arm(args):
         per = max(1, cores // n)
         procs = []
         for q in range(n):
-            env = {k: v for k, v in os.environ.items() if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR",
-                                                                     "MASTER_PORT", "OMP_NUM_THREADS", "TORCHELASTIC_RUN_ID")}
+            # a clean environment: under torch.distributed.run the workers would otherwise inherit
+            # TORCHELASTIC_USE_AGENT_STORE and try to JOIN the launcher's store instead of creating their own
+            drop = ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS", "GROUP_RANK",
+                    "GROUP_WORLD_SIZE", "LOCAL_WORLD_SIZE", "ROLE_RANK", "ROLE_NAME", "ROLE_WORLD_SIZE")
+            env = {k: v for k, v in os.environ.items() if k not in drop and not k.startswith("TORCHELASTIC_")}
             env.update({"PRB_REF_RANK": str(q), "PRB_REF_WORLD": str(n), "PRB_REF_PORT": str(port),
                         "PRB_REF_THREADS": str(per), "OMP_NUM_THREADS": str(per)})
             procs.append(subprocess.Popen([sys.executable, os.path.abspath(__file__), "--impl", "reference-worker",
                                            "--workload", args.workload, "--steps", str(args.steps), "--warmup",
                                            str(args.warmup), "--gpus", str(n)], env=env, stdout=subprocess.PIPE))
-        outs = [p.communicate()[0].decode() for p in procs]
+        try:
+            outs = [p.communicate(timeout=600)[0].decode() for p in procs]
+        except subprocess.TimeoutExpired:
+            for p in procs:
+                p.kill()
+            print(json.dumps({"impl": "reference", "unavailable": "the gloo workers of the CPU arm did not finish in 600 s"}),
+                  flush=True)
+            return 0
         if any(p.returncode for p in procs):
             print(json.dumps({"impl": "reference", "unavailable": "a gloo worker of the CPU arm failed"}), flush=True)
             return 0

@@ -88,11 +88,18 @@ def test_bench_reference_arm_runs_gloo_allreduce_with_all_cores():
     import json
     import subprocess
 
-    env = {**os.environ, "OMP_NUM_THREADS": "1", "RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0"}
-    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
-                          "--warmup", "1", "--workload", "resnet18"], env=env, capture_output=True, timeout=300)
+    # launched exactly like the driver launches it: under torch.distributed.run, whose environment
+    # (TORCHELASTIC_USE_AGENT_STORE, OMP_NUM_THREADS=1, ...) must not leak into the arm's own gloo workers
+    port = _free_port()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "bench.py"),
+                          "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "1", "--workload", "resnet18"],
+                         capture_output=True, timeout=240)
     assert out.returncode == 0, out.stderr.decode()[-2000:]
-    line = json.loads(out.stdout.decode().strip().splitlines()[-1])
+    env = {**os.environ, "OMP_NUM_THREADS": "1", "RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0"}
+    lines = [ln for ln in out.stdout.decode().splitlines() if ln.startswith("{")]
+    assert len(lines) == 1, out.stdout.decode()[-1000:]   # rank 0 alone prints, ONE line
+    line = json.loads(lines[0])
     assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0
     assert "gloo" in line["details"]["allreduce"]
     assert line["cpu_baseline"]["cores"] >= 2 and line["cpu_baseline"]["kind"] == "port"
