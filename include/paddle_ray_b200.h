@@ -117,6 +117,27 @@ int32_t prb_fused_adam(const PRB_Tensor* params, const PRB_Tensor* grads, const 
                        PRB_Tensor* beta2_pows_out, PRB_Tensor* master_params_out /* optional list */,
                        void* stream);
 
+/* A SelectedRows gradient (ref: paddle/phi/core/selected_rows.h): `nrows` row indices (a HOST array, as the reference
+ * keeps them; any order, duplicates allowed) into a [height, width] parameter and the dense [nrows, width] values. */
+typedef struct PRB_SelectedRows {
+  const int64_t* rows;
+  int64_t nrows;
+  int64_t height;
+  PRB_Tensor value;
+} PRB_SelectedRows;
+
+/* adam_ with a sparse gradient  ref: paddle/phi/kernels/selected_rows/gpu/adam_kernel.cu:95-260
+ *   (adam_dense_param_sparse_grad, legacy_ops.yaml:45-55).  Duplicate rows are merged first (scatter::MergeAdd);
+ *   lazy_mode updates only the rows that are present, otherwise every element is updated with g = 0 where its row is
+ *   absent.  In place (outputs must alias their inputs); learning rate and beta-pows are device scalars. */
+int32_t prb_adam_dense_param_sparse_grad(
+    const PRB_Tensor* param, const PRB_SelectedRows* grad, const PRB_Tensor* learning_rate, const PRB_Tensor* moment1,
+    const PRB_Tensor* moment2, const PRB_Tensor* beta1_pow, const PRB_Tensor* beta2_pow,
+    const PRB_Tensor* master_param /* optional */, const PRB_Tensor* skip_update /* optional */, double beta1, double beta2,
+    double epsilon, int32_t lazy_mode, int64_t min_row_size_to_use_multithread, int32_t multi_precision,
+    int32_t use_global_beta_pow, PRB_Tensor* param_out, PRB_Tensor* moment1_out, PRB_Tensor* moment2_out,
+    PRB_Tensor* beta1_pow_out, PRB_Tensor* beta2_pow_out, PRB_Tensor* master_param_out /* optional */, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * AMP + global-norm clip
  * ---------------------------------------------------------------------------------------- */
@@ -218,6 +239,9 @@ void* prb_comm_stream(const PRB_Comm* comm);
 /* ref: ProcessGroupNCCL::AllReduce process_group_nccl.cc:841-865 (in place when out == in).
  * op: 0 = sum, 1 = max.  Enqueued on `stream` (pass prb_comm_stream(comm) for the side stream). */
 int32_t prb_comm_all_reduce(PRB_Comm* comm, const PRB_Tensor* in, PRB_Tensor* out, int32_t op, void* stream);
+/* ref: ProcessGroupNCCL::AllGather (the sparse-gradient path, reducer.cc:1165-1215): out holds nranks x in.numel
+ * elements, rank r's contribution at offset r * in.numel. */
+int32_t prb_comm_all_gather(PRB_Comm* comm, const PRB_Tensor* in, PRB_Tensor* out, void* stream);
 /* ref: ProcessGroupNCCL::Broadcast process_group_nccl.cc:867-... (init-time parameter sync) */
 int32_t prb_comm_broadcast(PRB_Comm* comm, PRB_Tensor* buf, int32_t root, void* stream);
 

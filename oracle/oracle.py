@@ -340,3 +340,54 @@ class ReducerModel:
         while self.next_group < len(self.groups) and self.pending[self.next_group] == 0:
             self.launched.append(self.next_group)
             self.next_group += 1
+
+
+# ---------------------------------------------------------------- sparse (SelectedRows) gradients
+def merge_rows(rows, values, dtype, width=None):
+    """scatter::MergeAdd (paddle/phi/kernels/funcs/selected_rows_functor.cu, used by
+    selected_rows/gpu/adam_kernel.cu:180-206): unique rows in ascending order, the value rows of duplicates added.
+    The reference adds with atomics (order unspecified); here: fp32 accumulation in input order, rounded once to T
+    -- identical whenever a row occurs at most twice."""
+    rows = np.asarray(rows, np.int64)
+    values = np.ascontiguousarray(values)
+    if width is None:
+        width = values.size // max(rows.size, 1)
+    v32 = to_f32(values.reshape(-1), dtype).reshape(rows.size, width)
+    urows = np.unique(rows)
+    acc = np.zeros((urows.size, width), np.float32)
+    pos = np.searchsorted(urows, rows)
+    for k in range(rows.size):            # input order
+        acc[pos[k]] = acc[pos[k]] + v32[k]
+    return urows, from_f32(acc.reshape(-1), dtype).reshape(urows.size, width)
+
+
+def sparse_adam(param, rows, values, mom1, mom2, master, *, dtype_param, lr, beta1, beta2, epsilon, beta1_pow,
+                beta2_pow, lazy_mode):
+    """adam with a SelectedRows gradient (selected_rows/gpu/adam_kernel.cu:41-93): per element the dense Adam
+    expression with g = the merged row's value, or 0 where the row is absent; lazy_mode leaves absent rows untouched.
+    ``param`` / moments / master are 2-D [height, width] arrays updated in place."""
+    width = param.shape[1]
+    urows, merged = merge_rows(rows, values, dtype_param, width)
+    kw = dict(dtype_param=dtype_param, dtype_grad=dtype_param, lr=lr, beta1=beta1, beta2=beta2, epsilon=epsilon,
+              beta1_pow=beta1_pow, beta2_pow=beta2_pow)
+    if lazy_mode:
+        for k, r in enumerate(urows):
+            adam(param[r], merged[k], mom1[r], mom2[r], None if master is None else master[r], **kw)
+        return
+    dense = from_f32(np.zeros(param.size, np.float32), dtype_param).reshape(param.shape[0], width)
+    dense[urows] = merged
+    adam(param.reshape(-1), dense.reshape(-1), mom1.reshape(-1), mom2.reshape(-1),
+         None if master is None else master.reshape(-1), **kw)
+
+
+def sparse_allreduce(per_rank, dtype):
+    """EagerReducer::AllReduceSparse (reducer.cc:1072-1277): every rank's values are scaled by 1/nranks (:1075-1076),
+    then rows and values of all ranks are concatenated in rank order (all-gather, or rank-by-rank broadcasts + concat
+    when the ranks hold different numbers of rows: same result).  ``per_rank``: list of (rows, values[nrows, width])."""
+    n = len(per_rank)
+    rows = np.concatenate([np.asarray(r, np.int64) for r, _ in per_rank])
+    width = max(np.asarray(v).shape[1] for _, v in per_rank)
+    parts = [scale(np.ascontiguousarray(v).reshape(-1), dtype, 1.0 / n).reshape(-1, width)
+             for _, v in per_rank if np.asarray(v).size]
+    vals = np.concatenate(parts, axis=0) if parts else np.zeros((0, width), np.asarray(per_rank[0][1]).dtype)
+    return rows, vals

@@ -53,6 +53,18 @@ def adamw_(param, grad, learning_rate, moment1, moment2, beta1_pow, beta2_pow, m
 def adam_(param, grad, learning_rate, moment1, moment2, beta1_pow, beta2_pow, master_param, skip_update, beta1, beta2,
           epsilon, lazy_mode=False, min_row_size_to_use_multithread=1000, multi_precision=False,
           use_global_beta_pow=False, stream=None):
+    if isinstance(grad, core.SelectedRows):
+        # the YAML's kernel dispatch on the gradient's type: adam_dense_param_sparse_grad (legacy_ops.yaml:52)
+        ts = [param, learning_rate, moment1, moment2, beta1_pow, beta2_pow]
+        ps = [t.prb for t in ts]
+        sr, keep = grad.c_struct()
+        mp, mk = _opt(master_param)
+        sp, sk = _opt(skip_update)
+        call("prb_adam_dense_param_sparse_grad", C.byref(ps[0]), C.byref(sr), *[C.byref(p) for p in ps[1:]], mp, sp,
+             float(beta1), float(beta2), float(epsilon), int(bool(lazy_mode)), int(min_row_size_to_use_multithread),
+             int(bool(multi_precision)), int(bool(use_global_beta_pow)), C.byref(ps[0]), C.byref(ps[2]), C.byref(ps[3]),
+             C.byref(ps[4]), C.byref(ps[5]), mp, _stream(stream))
+        return param, moment1, moment2, beta1_pow, beta2_pow, master_param
     ts = [param, grad, learning_rate, moment1, moment2, beta1_pow, beta2_pow]
     ps = [t.prb for t in ts]
     mp, mk = _opt(master_param)

@@ -6,7 +6,7 @@ clip and adamw / adam / merged_adam / fused_adam, as hand-written sm_100a CUDA b
 """
 from . import _lib  # noqa: F401  (raises ImportError if the shared library is not built)
 from . import _C_ops, core  # noqa: F401
-from .core import Event, PinnedBuffer, Stream, Tensor, current_stream, device_count, set_device, synchronize  # noqa: F401
+from .core import Event, PinnedBuffer, SelectedRows, Stream, Tensor, current_stream, device_count, set_device, synchronize  # noqa: F401
 
 from . import amp, distributed, nn, optimizer  # noqa: F401,E402
 from .distributed import DataParallel  # noqa: F401,E402

@@ -32,6 +32,10 @@ class TailConfig(C.Structure):
     ]
 
 
+class SelectedRowsC(C.Structure):
+    _fields_ = [("rows", C.c_void_p), ("nrows", C.c_int64), ("height", C.c_int64), ("value", PRBTensor)]
+
+
 class GradEpilogue(C.Structure):
     _fields_ = [("loss_scale", C.POINTER(PRBTensor)), ("found_inf", C.POINTER(PRBTensor)), ("want_norm", C.c_int32),
                 ("use_mp_type", C.c_int32), ("partial_base", C.c_void_p)]
@@ -64,6 +68,8 @@ SIGNATURES = {
     "prb_adam": [_T] * 9 + [_f64] * 3 + [_i32, _i64, _i32, _i32] + [_T] * 6 + [_vp],
     "prb_merged_adam": [_T] * 8 + [_i64] + [_f64] * 3 + [_i32, _i32] + [_T] * 6 + [_vp],
     "prb_fused_adam": [_T] * 8 + [_i64, _T] + [_f64] * 3 + [_i32, _f32, _i32, _i32, _i32] + [_T] * 6 + [_vp],
+    "prb_adam_dense_param_sparse_grad": [_T, C.POINTER(SelectedRowsC)] + [_T] * 7 + [_f64] * 3 + [_i32, _i64, _i32, _i32] +
+                                        [_T] * 6 + [_vp],
     "prb_check_finite_and_unscale": [_T, _i64, _T, _T, _T, _vp],
     "prb_update_loss_scaling": [_T, _i64, _T, _T, _T, _T, _i32, _i32, _f32, _f32, _i32, _T, _T, _T, _T, _vp],
     "prb_squared_l2_norm": [_T, _T, _vp],
@@ -84,6 +90,7 @@ SIGNATURES = {
     "prb_comm_stream": [_vp],
     "prb_comm_all_reduce": [_vp, _T, _T, _i32, _vp],
     "prb_comm_broadcast": [_vp, _T, _i32, _vp],
+    "prb_comm_all_gather": [_vp, _T, _T, _vp],
     "prb_reducer_create": [_T, _i64, _vp, _vp, _i64, _vp, _i32, C.POINTER(_vp)],
     "prb_reducer_destroy": [_vp],
     "prb_reducer_prepare_for_backward": [_vp],

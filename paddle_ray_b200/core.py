@@ -252,7 +252,9 @@ class Tensor:
         return out
 
     def clear_gradient(self, set_to_zero: bool = True, stream=None):
-        if self.grad is not None:
+        if isinstance(self.grad, SelectedRows):  # a sparse gradient is produced anew by every backward
+            self.grad = None
+        elif self.grad is not None:
             if set_to_zero:
                 self.grad.zero_(stream)
             else:
@@ -267,6 +269,43 @@ class Tensor:
 
     def __repr__(self):
         return "Tensor(numel=%d, dtype=%s, place=%s)" % (self.numel, _lib.DTYPE_NAME[self.dtype], self.place)
+
+
+class SelectedRows:
+    """A sparse gradient (ref paddle/phi/core/selected_rows.h): ``rows`` -- a host int64 array of row indices into a
+    [height, width] parameter, any order, duplicates allowed -- and ``value``, the dense [len(rows), width] device
+    tensor.  The embedding-table case: only the looked-up rows carry a gradient."""
+
+    def __init__(self, rows, height: int, value: Tensor):
+        self.rows = np.ascontiguousarray(rows, np.int64).reshape(-1)
+        self.height = int(height)
+        self.value = value
+        if self.rows.size:
+            assert value.numel % self.rows.size == 0, "value must hold len(rows) x width elements"
+
+    @property
+    def width(self) -> int:
+        return self.value.numel // self.rows.size if self.rows.size else 0
+
+    @property
+    def dtype(self):
+        return self.value.dtype
+
+    @property
+    def device(self):
+        return self.value.device
+
+    def is_selected_rows(self) -> bool:
+        return True
+
+    def c_struct(self):
+        """-> (SelectedRowsC, keepalive) for the C ABI."""
+        s = _lib.SelectedRowsC(self.rows.ctypes.data, self.rows.size, self.height, self.value.prb)
+        return s, (self.rows, self.value)
+
+    def __repr__(self):
+        return "SelectedRows(rows=%d, height=%d, width=%d, dtype=%s)" % (
+            self.rows.size, self.height, self.width, _lib.DTYPE_NAME[self.dtype])
 
 
 class PinnedBuffer:

@@ -41,10 +41,7 @@ __device__ __forceinline__ float clip_grad(float g, const Coef& k) {
 
 __device__ __forceinline__ void adam_elem(float& p, float g, float& m1, float& m2, const Coef& k) {
   if (k.use_decay) p = __fmul_rn(p, k.decay);                                    // p *= 1 - lr*coeff
-  m1 = __fadd_rn(__fmul_rn(k.beta1, m1), __fmul_rn(k.c1, g));                    // b1*m1 + (1-b1)*g
-  m2 = __fadd_rn(__fmul_rn(k.beta2, m2), __fmul_rn(__fmul_rn(k.c2, g), g));      // b2*m2 + (1-b2)*g*g
-  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(m2), k.bc2), k.eps);        // sqrt(m2)/sqrt(1-b2^t) + eps
-  p = __fadd_rn(p, __fmul_rn(__fdiv_rn(m1, denom), k.step));                     // p += (m1/denom) * -(lr/(1-b1^t))
+  adam_moments_and_step(p, g, m1, m2, k.beta1, k.beta2, k.c1, k.c2, k.bc2, k.eps, k.step);
 }
 
 

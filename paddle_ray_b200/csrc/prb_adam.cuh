@@ -43,6 +43,20 @@ struct AdamArgs {
   unsigned int* pow_ticket;  // zero-initialised device counter of the launching stream, reset by the last CTA
 };
 
+#ifdef __CUDACC__
+// The Adam expression every optimizer kernel of the library shares, each operation individually rounded
+// (ref adam_kernel.cu:31-72, adamw_kernel.cu:32-79, selected_rows/gpu/adam_kernel.cu:41-93):
+//   m1 = b1*m1 + (1-b1)*g;  m2 = b2*m2 + (1-b2)*g*g;  p += (m1 / (sqrt(m2)/sqrt(1-b2^t) + eps)) * -(lr/(1-b1^t))
+// c1 = 1-b1, c2 = 1-b2, bc2 = sqrt(1-b2^t), step = -(lr/(1-b1^t)).
+__device__ __forceinline__ void adam_moments_and_step(float& p, float g, float& m1, float& m2, float beta1, float beta2,
+                                                      float c1, float c2, float bc2, float eps, float step) {
+  m1 = __fadd_rn(__fmul_rn(beta1, m1), __fmul_rn(c1, g));
+  m2 = __fadd_rn(__fmul_rn(beta2, m2), __fmul_rn(__fmul_rn(c2, g), g));
+  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(m2), bc2), eps);
+  p = __fadd_rn(p, __fmul_rn(__fdiv_rn(m1, denom), step));
+}
+#endif
+
 // Elements per CTA of the active launch geometry (threads * kVec * lane-vectors per thread).
 int adam_chunk_elems();
 

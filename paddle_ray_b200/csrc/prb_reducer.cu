@@ -750,6 +750,19 @@ int32_t prb_comm_all_reduce(PRB_Comm* c, const PRB_Tensor* in, PRB_Tensor* out, 
   return PRB_SUCCESS;
 }
 
+int32_t prb_comm_all_gather(PRB_Comm* c, const PRB_Tensor* in, PRB_Tensor* out, void* stream) {
+  PRB_ENFORCE(c && in && out && in->dtype == out->dtype && out->numel == in->numel * c->nranks, PRB_INVALID_ARGUMENT,
+              "all_gather: out must hold nranks x in.numel elements of in's dtype");
+  const size_t bytes = (size_t)in->numel * dtype_size(in->dtype);
+  if (c->nranks == 1) {
+    if (out->data != in->data && bytes > 0)
+      PRB_CUDA(cudaMemcpyAsync(out->data, in->data, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return PRB_SUCCESS;
+  }
+  PRB_NCCL(g_nccl.AllGather(in->data, out->data, bytes, ncclChar, c->comm, (cudaStream_t)stream));
+  return PRB_SUCCESS;
+}
+
 int32_t prb_comm_broadcast(PRB_Comm* c, PRB_Tensor* buf, int32_t root, void* stream) {
   PRB_ENFORCE(c && buf && root >= 0 && root < c->nranks, PRB_INVALID_ARGUMENT, "broadcast: bad arguments");
   if (c->nranks == 1) return PRB_SUCCESS;

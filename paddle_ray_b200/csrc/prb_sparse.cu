@@ -1,0 +1,239 @@
+// adam_ with a SelectedRows (sparse) gradient: the embedding-table case.
+//
+//   ref: AdamDenseParamSparseGradKernel  paddle/phi/kernels/selected_rows/gpu/adam_kernel.cu:95-260
+//        SparseAdamCUDAKernelREG          :41-93
+//        scatter::MergeAdd                paddle/phi/kernels/funcs/selected_rows_functor.cu (duplicates summed, rows sorted)
+//        legacy_ops.yaml:45-55 (adam_ -> adam_dense_param_sparse_grad for a selected_rows grad)
+//
+// The gradient is a list of row indices (host array, as phi::SelectedRows keeps them) and a dense [nrows, width]
+// value tensor on the device.  Rows may repeat and come in any order.  The host sorts and deduplicates the indices
+// (a few thousand integers), the device adds the value rows of duplicates (fp32 accumulation in input order,
+// rounded once to T -- the reference adds with atomics in an unspecified order; identical for up to two
+// occurrences), then ONE kernel applies the shared Adam expression:
+//   lazy_mode      only the rows that are present: one thread per element of those rows, no search;
+//   otherwise      every element of the parameter, with g = 0 where the row is absent (binary search per element
+//                  in the sorted unique rows, like the reference).
+#include <algorithm>
+#include <numeric>
+#include <vector>
+
+#include "prb_adam.cuh"
+
+namespace prb {
+namespace {
+
+constexpr int kSpThreads = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(kSpThreads) merge_rows_kernel(const T* __restrict__ values, const int64_t* __restrict__ off,
+                                                                const int64_t* __restrict__ src, int64_t nunique,
+                                                                int64_t width, T* __restrict__ merged) {
+  const int64_t total = nunique * width, stride = (int64_t)gridDim.x * kSpThreads;
+  for (int64_t id = (int64_t)blockIdx.x * kSpThreads + threadIdx.x; id < total; id += stride) {
+    const int64_t u = id / width, j = id % width;
+    float acc = 0.0f;
+    for (int64_t s = off[u]; s < off[u + 1]; ++s) acc = __fadd_rn(acc, Conv<T>::to_f32(values[src[s] * width + j]));
+    merged[id] = Conv<T>::from_f32(acc);
+  }
+}
+
+struct SparseArgs {
+  void* param;
+  float* mom1;
+  float* mom2;
+  float* master;
+  const void* merged;        // [nunique, width]
+  const int64_t* urows;      // sorted unique rows
+  int64_t nunique, width, height;
+  const float* lr;           // device scalars
+  const float* b1pow;
+  const float* b2pow;
+  float beta1, beta2, eps;
+  const bool* skip;
+  int lazy;
+};
+
+__device__ __forceinline__ int64_t find_row(const int64_t* rows, int64_t n, int64_t key) {
+  int64_t lo = 0, hi = n - 1;
+  while (lo <= hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    const int64_t v = rows[mid];
+    if (v == key) return mid;
+    if (v < key) lo = mid + 1;
+    else hi = mid - 1;
+  }
+  return -1;
+}
+
+template <typename T, bool kMaster>
+__global__ void __launch_bounds__(kSpThreads) sparse_adam_kernel(const SparseArgs a) {
+  if (a.skip != nullptr && *a.skip) return;
+  const float lr = __ldg(a.lr), b1p = __ldg(a.b1pow), b2p = __ldg(a.b2pow);
+  const float c1 = __fsub_rn(1.0f, a.beta1), c2 = __fsub_rn(1.0f, a.beta2);
+  const float bc2 = __fsqrt_rn(__fsub_rn(1.0f, b2p));
+  const float step = -__fdiv_rn(lr, __fsub_rn(1.0f, b1p));
+  T* __restrict__ param = reinterpret_cast<T*>(a.param);
+  const T* __restrict__ merged = reinterpret_cast<const T*>(a.merged);
+  const int64_t total = a.lazy ? a.nunique * a.width : a.height * a.width;
+  const int64_t stride = (int64_t)gridDim.x * kSpThreads;
+  for (int64_t id = (int64_t)blockIdx.x * kSpThreads + threadIdx.x; id < total; id += stride) {
+    int64_t e;  // element of the parameter
+    float g;
+    if (a.lazy) {
+      const int64_t u = id / a.width, j = id % a.width;
+      e = a.urows[u] * a.width + j;
+      g = Conv<T>::to_f32(merged[id]);
+    } else {
+      e = id;
+      const int64_t u = find_row(a.urows, a.nunique, id / a.width);
+      g = u >= 0 ? Conv<T>::to_f32(merged[u * a.width + id % a.width]) : 0.0f;
+    }
+    float p = kMaster ? a.master[e] : Conv<T>::to_f32(param[e]);
+    float m1 = a.mom1[e], m2 = a.mom2[e];
+    adam_moments_and_step(p, g, m1, m2, a.beta1, a.beta2, c1, c2, bc2, a.eps, step);
+    a.mom1[e] = m1;
+    a.mom2[e] = m2;
+    param[e] = Conv<T>::from_f32(p);
+    if (kMaster) a.master[e] = p;
+  }
+}
+
+template <typename T>
+int32_t run_sparse(const SparseArgs& a, const T* values, const int64_t* off, const int64_t* src, T* merged, bool need_merge,
+                   bool has_master, cudaStream_t stream) {
+  const int64_t cap = (int64_t)sm_count() * 8;
+  if (need_merge) {
+    const int64_t n = a.nunique * a.width;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + kSpThreads - 1) / kSpThreads, cap));
+    merge_rows_kernel<T><<<grid, kSpThreads, 0, stream>>>(values, off, src, a.nunique, a.width, merged);
+    PRB_LAUNCH_CHECK();
+  }
+  const int64_t total = a.lazy ? a.nunique * a.width : a.height * a.width;
+  if (total == 0) return PRB_SUCCESS;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((total + kSpThreads - 1) / kSpThreads, cap));
+  if (has_master) sparse_adam_kernel<T, true><<<grid, kSpThreads, 0, stream>>>(a);
+  else sparse_adam_kernel<T, false><<<grid, kSpThreads, 0, stream>>>(a);
+  PRB_LAUNCH_CHECK();
+  return PRB_SUCCESS;
+}
+
+}  // namespace
+}  // namespace prb
+
+using namespace prb;
+
+extern "C" int32_t prb_adam_dense_param_sparse_grad(
+    const PRB_Tensor* param, const PRB_SelectedRows* grad, const PRB_Tensor* learning_rate, const PRB_Tensor* moment1,
+    const PRB_Tensor* moment2, const PRB_Tensor* beta1_pow, const PRB_Tensor* beta2_pow, const PRB_Tensor* master_param,
+    const PRB_Tensor* skip_update, double beta1, double beta2, double epsilon, int32_t lazy_mode,
+    int64_t min_row_size_to_use_multithread, int32_t multi_precision, int32_t use_global_beta_pow, PRB_Tensor* param_out,
+    PRB_Tensor* moment1_out, PRB_Tensor* moment2_out, PRB_Tensor* beta1_pow_out, PRB_Tensor* beta2_pow_out,
+    PRB_Tensor* master_param_out, void* stream_) {
+  (void)min_row_size_to_use_multithread;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  PRB_TRY(require_device());
+  PRB_ENFORCE(param && grad && learning_rate && moment1 && moment2 && beta1_pow && beta2_pow, PRB_INVALID_ARGUMENT,
+              "adam (sparse grad): a required input is NULL");
+  const int32_t dt = param->dtype;
+  PRB_ENFORCE(dt == PRB_FLOAT32 || dt == PRB_BFLOAT16 || dt == PRB_FLOAT16, PRB_UNIMPLEMENTED,
+              "adam (sparse grad): dtype %s is not built", dtype_name(dt));
+  PRB_ENFORCE(grad->value.dtype == dt && grad->value.device >= 0 && param->device >= 0, PRB_INVALID_ARGUMENT,
+              "adam (sparse grad): the gradient values must be a device tensor of the parameter's dtype");
+  PRB_ENFORCE(grad->height > 0 && param->numel % grad->height == 0, PRB_INVALID_ARGUMENT,
+              "adam (sparse grad): the parameter's %lld elements are not a whole number of rows of height %lld",
+              (long long)param->numel, (long long)grad->height);
+  const int64_t width = param->numel / grad->height;
+  PRB_ENFORCE(grad->nrows >= 0 && grad->value.numel == grad->nrows * width && (grad->rows != nullptr || grad->nrows == 0),
+              PRB_INVALID_ARGUMENT, "adam (sparse grad): the gradient must hold nrows x %lld values", (long long)width);
+  PRB_ENFORCE(moment1->numel == param->numel && moment2->numel == param->numel && moment1->dtype == PRB_FLOAT32 &&
+                  moment2->dtype == PRB_FLOAT32 && moment1->device >= 0 && moment2->device >= 0,
+              PRB_INVALID_ARGUMENT, "adam (sparse grad): moments must be float32 device tensors of the parameter's size");
+  const bool has_master = multi_precision != 0;
+  PRB_ENFORCE(!has_master || (master_param && master_param->numel == param->numel && master_param->dtype == PRB_FLOAT32),
+              PRB_INVALID_ARGUMENT, "adam (sparse grad): multi_precision requires a float32 master_param");
+  PRB_ENFORCE(learning_rate->numel == 1 && learning_rate->dtype == PRB_FLOAT32 && learning_rate->device >= 0 &&
+                  beta1_pow->numel == 1 && beta2_pow->numel == 1 && beta1_pow->device >= 0 && beta2_pow->device >= 0,
+              PRB_INVALID_ARGUMENT,
+              "adam (sparse grad): learning_rate and the beta-pow accumulators must be single float32 device scalars");
+  for (const PRB_Tensor* o : {param_out, moment1_out, moment2_out, master_param_out})
+    PRB_ENFORCE(o == nullptr || o->data == nullptr || o->data == param->data || o->data == moment1->data ||
+                    o->data == moment2->data || (master_param && o->data == master_param->data),
+                PRB_UNIMPLEMENTED, "adam (sparse grad): outputs must alias their inputs (the op is in place, legacy_ops.yaml:55)");
+  const bool* skip = nullptr;
+  if (skip_update != nullptr) {
+    PRB_ENFORCE(skip_update->numel == 1, PRB_INVALID_ARGUMENT, "Input(SkipUpdate) size must be 1, but get %lld",
+                (long long)skip_update->numel);
+    if (skip_update->device < 0) {
+      if (*reinterpret_cast<const bool*>(skip_update->data)) return PRB_SUCCESS;
+    } else {
+      skip = reinterpret_cast<const bool*>(skip_update->data);
+    }
+  }
+  // ---- host: sort + deduplicate the row indices (stable: duplicates keep their input order)
+  const int64_t n = grad->nrows;
+  std::vector<int64_t> order((size_t)n);
+  std::iota(order.begin(), order.end(), (int64_t)0);
+  std::stable_sort(order.begin(), order.end(), [&](int64_t x, int64_t y) { return grad->rows[x] < grad->rows[y]; });
+  std::vector<int64_t> urows, off;
+  for (int64_t k = 0; k < n; ++k) {
+    const int64_t r = grad->rows[order[(size_t)k]];
+    PRB_ENFORCE(r >= 0 && r < grad->height, PRB_OUT_OF_RANGE, "adam (sparse grad): row %lld is outside [0, %lld)", (long long)r,
+                (long long)grad->height);
+    if (urows.empty() || urows.back() != r) {
+      urows.push_back(r);
+      off.push_back(k);
+    }
+  }
+  off.push_back(n);
+  const int64_t nu = (int64_t)urows.size();
+  bool need_merge = nu != n;
+  for (int64_t k = 0; k < n && !need_merge; ++k) need_merge = order[(size_t)k] != k;  // sorted and unique: use the values as they are
+  // ---- device scratch: [urows | off | src | merged values]
+  const size_t ints = (size_t)nu + (size_t)nu + 1 + (size_t)n;
+  const size_t es = (size_t)dtype_size(dt);
+  const size_t merged_off = (ints * sizeof(int64_t) + 255) / 256 * 256;
+  void* ws = nullptr;
+  PRB_TRY(workspace(merged_off + (size_t)nu * (size_t)width * es + 256, &ws, /*slot=*/3, stream));
+  std::vector<int64_t> host(ints);
+  std::copy(urows.begin(), urows.end(), host.begin());
+  std::copy(off.begin(), off.end(), host.begin() + nu);
+  std::copy(order.begin(), order.end(), host.begin() + nu + nu + 1);
+  if (ints > 0)  // pageable source: staged before the call returns
+    PRB_CUDA(cudaMemcpyAsync(ws, host.data(), ints * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+  const int64_t* d_urows = reinterpret_cast<const int64_t*>(ws);
+  const int64_t* d_off = d_urows + nu;
+  const int64_t* d_src = d_off + nu + 1;
+  void* d_merged = reinterpret_cast<char*>(ws) + merged_off;
+  SparseArgs a{};
+  a.param = param->data;
+  a.mom1 = reinterpret_cast<float*>(moment1->data);
+  a.mom2 = reinterpret_cast<float*>(moment2->data);
+  a.master = has_master ? reinterpret_cast<float*>(master_param->data) : nullptr;
+  a.merged = need_merge ? d_merged : grad->value.data;
+  a.urows = d_urows;
+  a.nunique = nu;
+  a.width = width;
+  a.height = grad->height;
+  a.lr = reinterpret_cast<const float*>(learning_rate->data);
+  a.b1pow = reinterpret_cast<const float*>(beta1_pow->data);
+  a.b2pow = reinterpret_cast<const float*>(beta2_pow->data);
+  a.beta1 = (float)beta1;
+  a.beta2 = (float)beta2;
+  a.eps = (float)epsilon;
+  a.skip = skip;
+  a.lazy = lazy_mode != 0;
+  switch (dt) {
+    case PRB_FLOAT32:
+      PRB_TRY(run_sparse<float>(a, (const float*)grad->value.data, d_off, d_src, (float*)d_merged, need_merge, has_master, stream));
+      break;
+    case PRB_BFLOAT16:
+      PRB_TRY(run_sparse<__nv_bfloat16>(a, (const __nv_bfloat16*)grad->value.data, d_off, d_src, (__nv_bfloat16*)d_merged,
+                                        need_merge, has_master, stream));
+      break;
+    default:
+      PRB_TRY(run_sparse<__half>(a, (const __half*)grad->value.data, d_off, d_src, (__half*)d_merged, need_merge, has_master, stream));
+  }
+  if (!use_global_beta_pow)
+    PRB_TRY(beta_pow_update_device(beta1_pow, beta2_pow, beta1_pow_out, beta2_pow_out, 1, (float)beta1, (float)beta2, skip, stream));
+  return PRB_SUCCESS;
+}

@@ -73,6 +73,14 @@ class Group:
              core._stream_handle(stream))
         return tensor
 
+    def all_gather(self, tensor: Tensor, out: Tensor | None = None, stream=None) -> Tensor:
+        """``out`` holds nranks x tensor.numel elements, rank r's contribution at r * tensor.numel."""
+        if out is None:
+            out = Tensor(tensor.numel * self.nranks, tensor.dtype, tensor.device)
+        a, b = tensor.prb, out.prb
+        call("prb_comm_all_gather", self.handle, C.byref(a), C.byref(b), core._stream_handle(stream))
+        return out
+
     def broadcast(self, tensor: Tensor, src: int = 0, stream=None) -> Tensor:
         p = tensor.prb
         call("prb_comm_broadcast", self.handle, C.byref(p), int(src), core._stream_handle(stream))
@@ -90,6 +98,7 @@ class Group:
             pass
 
 
+_DONE = object()  # a sparse group whose exchange has run in this backward
 _default_group: Group | None = None
 _init_calls = 0  # every rank makes the same sequence of calls, so the count names the communicator
 
@@ -177,44 +186,162 @@ class EagerReducer:
 
     def __init__(self, grads, group_indices, is_sparse_gradient, process_group, group_size_limits=None,
                  find_unused_parameters=False):
-        if any(is_sparse_gradient):
-            raise _lib.PRBError(4, "sparse (SelectedRows) gradients are out of scope (SURVEY.md 8f-4)")
         self._grads = list(grads)
-        flat = [v for g in group_indices for v in g]
-        sizes = [len(g) for g in group_indices]
-        self._flat = (C.c_int64 * max(len(flat), 1))(*flat)
-        self._sizes = (C.c_int64 * max(len(sizes), 1))(*sizes)
-        h = C.c_void_p()
-        call("prb_reducer_create", tensor_array(self._grads), len(self._grads), self._flat, self._sizes, len(sizes),
-             process_group.handle if process_group is not None else None, int(bool(find_unused_parameters)), C.byref(h))
-        self.handle = h.value
         self.group_indices = [list(g) for g in group_indices]
         self._group = process_group
+        # Sparse (SelectedRows) gradients: a sparse variable is always a group of its own (reducer.cc:94-99,543-551).
+        # Those groups are exchanged from here (_allreduce_sparse); the native reducer sees the dense variables only,
+        # renumbered 0..D-1, and its groups keep their relative order.  With no sparse variable nothing is renumbered.
+        is_sparse = [bool(s) for s in is_sparse_gradient] if len(is_sparse_gradient) else [False] * len(self._grads)
+        self._sparse_vars = [i for i, s in enumerate(is_sparse) if s]
+        for g in self.group_indices:
+            if any(is_sparse[v] for v in g) and len(g) != 1:
+                raise _lib.PRBError(2, "a sparse gradient must be a group of its own, got a group of %d" % len(g))
+        self._dense_of = {}
+        for i in range(len(self._grads)):
+            if not is_sparse[i]:
+                self._dense_of[i] = len(self._dense_of)
+        self._sparse_source = {v: (lambda v=v: self._grads[v]) for v in self._sparse_vars}
+        self._sparse_ready = {}
+        dense_groups = [[self._dense_of[v] for v in g] for g in self.group_indices if not is_sparse[g[0]]]
+        dense_grads = [self._grads[i] for i in sorted(self._dense_of)]
+        self.handle = None
+        if dense_groups or not self._sparse_vars:
+            flat = [v for g in dense_groups for v in g]
+            sizes = [len(g) for g in dense_groups]
+            self._flat = (C.c_int64 * max(len(flat), 1))(*flat)
+            self._sizes = (C.c_int64 * max(len(sizes), 1))(*sizes)
+            h = C.c_void_p()
+            call("prb_reducer_create", tensor_array(dense_grads), len(dense_grads), self._flat, self._sizes, len(sizes),
+                 process_group.handle if process_group is not None else None, int(bool(find_unused_parameters)),
+                 C.byref(h))
+            self.handle = h.value
+        self.dense_group_count = len(dense_groups)
+
+    # ---- sparse groups
+    def set_sparse_source(self, var_index: int, getter):
+        """``getter()`` returns the variable's current SelectedRows gradient (a new object after every backward)."""
+        self._sparse_source[var_index] = getter
+
+    def _mark_sparse_ready(self, var_index: int):
+        if self._sparse_vars and self.finalized:  # after finalize hooks are no-ops (reducer.cc:740-758)
+            return
+        sr = self._sparse_source[var_index]()
+        # ref reducer.cc:858-888
+        if sr is None:
+            raise _lib.PRBError(3, "The sparse parameter[%d] should have gradient. Currently, DataParallel does not "
+                                "support sparse parameters without generating gradients during training." % var_index)
+        if not isinstance(sr, core.SelectedRows):
+            raise _lib.PRBError(3, "The sparse parameter[%d] must have a selectedrows gradient." % var_index)
+        if var_index in self._sparse_ready:
+            raise _lib.PRBError(3, "The sparse parameter[%d] was marked ready twice in one backward" % var_index)
+        self._sparse_ready[var_index] = sr
+
+    def _maybe_reduce_sparse(self, stream=None):
+        """Sparse groups are exchanged once every gradient of the backward is there, in variable order (the same
+        order on every rank, whatever order the hooks fired in); the reference launches them in group order between
+        the dense groups (reducer.cc:922-929).  Same result: groups are independent."""
+        if len(self._sparse_ready) != len(self._sparse_vars) or not self._sparse_vars:
+            return
+        if self.handle is not None and self.dense_group_count and not lib.prb_reducer_is_finalized(self.handle):
+            return
+        for v in self._sparse_vars:
+            if self._sparse_ready[v] is not _DONE:
+                self._allreduce_sparse(self._sparse_ready[v], stream)
+                self._sparse_ready[v] = _DONE
+
+    def _allreduce_sparse(self, sr, stream=None):
+        """ref EagerReducer::AllReduceSparse reducer.cc:1072-1277: values scaled by 1/nranks, then every rank ends
+        with all ranks' rows and values concatenated in rank order (duplicates are merged later, by the optimizer).
+        The reference gathers with all-gather when the ranks hold the same number of rows and with 2 x nranks
+        broadcasts otherwise; here the ragged case pads to the longest rank and still uses one all-gather for the
+        rows and one for the values.  Host-synchronous like the reference (the row indices live on the host)."""
+        from .. import _C_ops
+        g = self._group
+        if g is None:  # host-only state machine (CPU tests): no device work
+            return
+        n = g.nranks
+        if sr.rows.size:
+            _C_ops.scale_(sr.value, 1.0 / n, 0.0, False, stream=stream)
+        if n == 1:
+            return
+        st = core._stream_handle(stream)
+        width = sr.value.numel // sr.rows.size if sr.rows.size else 0
+        meta = Tensor.from_numpy(np.array([sr.rows.size, width], np.int64), device=g.device, stream=stream)
+        counts = g.all_gather(meta, stream=stream).numpy(stream).reshape(n, 2)
+        width = int(counts[:, 1].max())
+        longest = int(counts[:, 0].max())
+        if longest == 0:
+            return
+        rows = np.zeros(longest, np.int64)
+        rows[:sr.rows.size] = sr.rows
+        all_rows = g.all_gather(Tensor.from_numpy(rows, device=g.device, stream=stream), stream=stream).numpy(stream)
+        if sr.rows.size == longest:
+            mine = sr.value
+        else:
+            mine = Tensor.zeros(longest * width, sr.value.dtype, g.device, stream=stream)
+            if sr.rows.size:
+                call("prb_memcpy_d2d", mine.data_ptr, sr.value.data_ptr, sr.value.nbytes, st)
+        gathered = g.all_gather(mine, stream=stream)
+        if (counts[:, 0] == longest).all():
+            value = gathered
+        else:
+            es = _lib.DTYPE_SIZE[sr.value.dtype]
+            value = Tensor(int(counts[:, 0].sum()) * width, sr.value.dtype, g.device)
+            at = 0
+            for r in range(n):
+                nb = int(counts[r, 0]) * width * es
+                if nb:
+                    call("prb_memcpy_d2d", value.data_ptr + at, gathered.data_ptr + r * longest * width * es, nb, st)
+                at += nb
+            call("prb_stream_synchronize", st)  # `gathered` and `mine` are released on return
+        sr.rows = np.concatenate([all_rows[r * longest:r * longest + int(counts[r, 0])] for r in range(n)])
+        sr.value = value
 
     def prepare_for_backward(self, unused_vars=()):
+        self._sparse_ready = {}
+        if self.handle is None:
+            return
         call("prb_reducer_prepare_for_backward", self.handle)
         if len(unused_vars):
-            arr = (C.c_int64 * len(unused_vars))(*[int(v) for v in unused_vars])
+            if any(int(v) in self._sparse_source for v in unused_vars):
+                raise _lib.PRBError(3, "a sparse parameter cannot be unused (reducer.cc:858-872)")
+            arr = (C.c_int64 * len(unused_vars))(*[self._dense_of.get(int(v), int(v)) for v in unused_vars])
             call("prb_reducer_set_unused_vars", self.handle, arr, len(unused_vars))
 
     def mark_var_ready(self, var_index: int, stream=None):
-        call("prb_reducer_mark_var_ready", self.handle, int(var_index),
-             core._stream_handle(stream) if self._group is not None else None)
+        if var_index in self._sparse_source:
+            self._mark_sparse_ready(int(var_index))
+        else:
+            call("prb_reducer_mark_var_ready", self.handle, self._dense_of.get(int(var_index), int(var_index)),
+                 core._stream_handle(stream) if self._group is not None else None)
+        if self._sparse_vars:
+            self._maybe_reduce_sparse(stream)
 
     def mark_vars_ready(self, var_indices, stream=None):
+        if self._sparse_vars:
+            for v in var_indices:
+                self.mark_var_ready(int(v), stream)
+            return
         arr = var_indices if isinstance(var_indices, C.Array) else (C.c_int64 * len(var_indices))(*var_indices)
         call("prb_reducer_mark_vars_ready", self.handle, arr, len(arr),
              core._stream_handle(stream) if self._group is not None else None)
 
     def set_unpack(self, enabled: bool):
+        if self.handle is None:  # sparse groups only
+            return
         call("prb_reducer_set_unpack", self.handle, int(bool(enabled)))
 
     def set_grads_in_arena(self, enabled: bool):
+        if self.handle is None:  # sparse groups only
+            return
         call("prb_reducer_set_grads_in_arena", self.handle, int(bool(enabled)))
 
     def set_grad_epilogue(self, loss_scale=None, found_inf=None, partial_base=None, use_mp_type=False):
         """Producer-side pass 1 (see prb_reducer_set_grad_epilogue).  Returns (active, partials view); all arguments
         None switches it off."""
+        if self.handle is None or self._sparse_vars:
+            return False, None
         out = _lib.PRBTensor()
         active = C.c_int32()
         if loss_scale is None and partial_base is None:
@@ -250,22 +377,26 @@ class EagerReducer:
         return bool(e.value)
 
     def set_deferred_wait(self, enabled: bool):
+        if self.handle is None:  # sparse groups only
+            return
         call("prb_reducer_set_deferred_wait", self.handle, int(bool(enabled)))
 
     def wait_group(self, group_index: int, stream=None):
         call("prb_reducer_wait_group", self.handle, int(group_index), core._stream_handle(stream))
 
     def group_of(self, var_index: int) -> int:
+        """Launch-order index of the variable's DENSE group (what wait_group / allreduce_group take)."""
         g = C.c_int64()
-        call("prb_reducer_group_of", self.handle, int(var_index), C.byref(g))
+        call("prb_reducer_group_of", self.handle, self._dense_of.get(int(var_index), int(var_index)), C.byref(g))
         return int(g.value)
 
     @property
     def finalized(self) -> bool:
-        return bool(lib.prb_reducer_is_finalized(self.handle))
+        dense = bool(lib.prb_reducer_is_finalized(self.handle)) if self.handle is not None else True
+        return dense and all(self._sparse_ready.get(v) is _DONE for v in self._sparse_vars)
 
     def launched_groups(self):
-        cap = len(self.group_indices)
+        cap = self.dense_group_count
         out = (C.c_int64 * max(cap, 1))()
         n = C.c_int64()
         call("prb_reducer_launched_groups", self.handle, out, cap, C.byref(n))
@@ -273,12 +404,13 @@ class EagerReducer:
 
     def bucket_view(self, var_index: int) -> Tensor:
         p = _lib.PRBTensor()
-        call("prb_reducer_bucket_view", self.handle, int(var_index), C.byref(p))
+        call("prb_reducer_bucket_view", self.handle, self._dense_of.get(int(var_index), int(var_index)), C.byref(p))
         return Tensor(p.numel, p.dtype, p.device, data_ptr=p.data, owner=self)
 
     def __del__(self):
         try:
-            lib.prb_reducer_destroy(self.handle)
+            if self.handle is not None:
+                lib.prb_reducer_destroy(self.handle)
         except Exception:
             pass
 
@@ -334,7 +466,7 @@ class DataParallel:
             self.group = init_parallel_env()
         self.grads_in_arena = bool(grads_in_arena)
         for p in self._parameters:
-            if p.grad is None and not self.grads_in_arena:
+            if p.grad is None and not self.grads_in_arena and not getattr(p, "is_sparse_grad", False):
                 p.grad = Tensor.zeros(p.numel, p.dtype, p.device)
         sync_params_buffers(self._parameters, self.group)
         self.comm_buffer_size = int(comm_buffer_size * 1024 * 1024)
@@ -361,8 +493,11 @@ class DataParallel:
         self._reducer = EagerReducer(grads, list(reversed(self.group_indices)), is_sparse,
                                      self.group, [self.last_comm_buffer_size, self.comm_buffer_size],
                                      self.find_unused_parameters)
-        if self.grads_in_arena:
-            for i, p in enumerate(self._parameters):
+        self._sparse = is_sparse
+        for i, p in enumerate(self._parameters):
+            if is_sparse[i]:  # the producer hangs a new SelectedRows on p.grad in every backward
+                self._reducer.set_sparse_source(i, lambda p=p: p.grad)
+            elif self.grads_in_arena:
                 p.grad = self._reducer.bucket_view(i)
         # backward produces gradients in reverse parameter order
         self._reverse_order = (C.c_int64 * len(self._parameters))(*reversed(range(len(self._parameters))))
@@ -377,8 +512,11 @@ class DataParallel:
         self._reducer.set_unpack(not self._consume)
         self.pipelined = self._consume and self.group.nranks > 1
         self._reducer.set_deferred_wait(self.pipelined)
-        self._bucket_grads = [self._reducer.bucket_view(i) for i in range(len(self._parameters))] if enabled else None
+        self._bucket_grads = [None if self._sparse[i] else self._reducer.bucket_view(i)
+                              for i in range(len(self._parameters))] if enabled else None
         for i, p in enumerate(self._parameters):
+            if self._sparse[i]:
+                continue
             if enabled:
                 p._reduced_grad = self._bucket_grads[i]
                 p._bucket = (self, self._reducer.group_of(i))
@@ -390,7 +528,7 @@ class DataParallel:
         self._reducer.wait_group(group_index, stream)
 
     def wait_all_groups(self, stream=None):
-        for gi in range(len(self.group_indices)):
+        for gi in range(self._reducer.dense_group_count):
             self._reducer.wait_group(gi, stream)
 
     def bucket_grads(self):

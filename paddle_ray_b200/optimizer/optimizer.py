@@ -24,7 +24,7 @@ import numpy as np
 
 from .. import _C_ops, _lib, core
 from .._lib import BFLOAT16, BOOL, FLOAT16, FLOAT32, TailConfig, call, lib, tensor_array
-from ..core import Tensor
+from ..core import SelectedRows, Tensor
 from ..nn.clip import ClipGradByGlobalNorm, _clip_by_global_norm_using_mp_type
 from .lr import LRScheduler
 
@@ -172,6 +172,13 @@ class Optimizer:
         found_inf = self._get_auxiliary_var("found_inf")
         loss_scale = self._get_auxiliary_var("loss_scale")  # set by GradScaler when the unscale is deferred to us
         clip = self._grad_clip
+        if any(isinstance(g, SelectedRows) for _, g in pg):
+            dense = [(p, g) for p, g in pg if not isinstance(g, SelectedRows)]
+            self._sparse_step([(p, g) for p, g in pg if isinstance(g, SelectedRows)], found_inf, loss_scale,
+                              advance_beta_pow=not dense)
+            pg = dense
+            if not pg:
+                return
         # everything a cached plan bakes in: buffers, flags and hyper-parameters (changing weight decay or the clip
         # norm in the middle of training builds a new plan instead of being ignored)
         key = (tuple(g.data_ptr for _, g in pg), id(clip), loss_scale.data_ptr if loss_scale is not None else 0,
@@ -339,6 +346,23 @@ class Optimizer:
             # the shared device accumulators advance once per step: with the last parameter
             self._append_optimize_op(p, g, lr, acc[self._moment1_acc_str], acc[self._moment2_acc_str], master, found_inf,
                                      float(lr_ratio[i]), bool(with_decay[i]), use_global_beta_pow=i != len(pg) - 1)
+
+    def _sparse_step(self, pg, found_inf, loss_scale, advance_beta_pow):
+        """Parameters whose gradient is a SelectedRows (embedding tables): one adam_ call each, which the YAML
+        dispatches to adam_dense_param_sparse_grad (legacy_ops.yaml:52; ref adam.py:390-470).  They run BEFORE the
+        dense parameters' fused launch, which is the one that advances the shared beta-pow accumulators."""
+        if self._use_adamw:
+            raise _lib.PRBError(4, "adamw_ has no SelectedRows kernel (legacy_ops.yaml:68-77); use Adam for sparse gradients")
+        if loss_scale is not None or self._grad_clip is not None:
+            raise _lib.PRBError(4, "AMP unscaling and global-norm clipping of SelectedRows gradients are not built "
+                                "(merge_selected_rows / multiply_sr, clip.py) -- dense gradients only")
+        lr = self._global_lr()
+        for i, (p, g) in enumerate(pg):
+            acc = self._accumulators[p.name]
+            master = self._master_weights.get(p.name) if self._find_master(p) else None
+            last = advance_beta_pow and i == len(pg) - 1
+            self._append_optimize_op(p, g, lr, acc[self._moment1_acc_str], acc[self._moment2_acc_str], master, found_inf,
+                                     1.0, False, use_global_beta_pow=not last)
 
     # ---- housekeeping
     def clear_grad(self, set_to_zero=True):

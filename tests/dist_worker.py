@@ -134,6 +134,47 @@ def main(out_dir):
         else:
             np.testing.assert_allclose(p.grad.numpy(), want, rtol=1e-6, atol=1e-8)
         np.save(os.path.join(out_dir, "unused_grad_%d_r%d.npy" % (i, rank)), p.grad.numpy())
+    # sparse (SelectedRows) gradients, ref EagerReducer::AllReduceSparse reducer.cc:1072-1277 and
+    # adam_dense_param_sparse_grad: an embedding table next to dense parameters; the ranks hold the same number of rows
+    # in step 0 (the all-gather branch of the reference) and different numbers afterwards (its broadcast branch)
+    height, width = 300, 24
+    emb0 = np.random.default_rng(7).normal(0, 0.02, (height, width)).astype(np.float32)
+    emb = prb.Tensor.from_numpy(emb0.reshape(-1), name="emb")
+    emb.is_sparse_grad = True
+    dn = [prb.Tensor.from_numpy(np.random.default_rng(100 + i).normal(0, 0.02, sz).astype(np.float32), name="sd_%d" % i)
+          for i, sz in enumerate(sizes[:4])]
+    dps = prb.DataParallel([emb] + dn, comm_buffer_size=0.4, last_comm_buffer_size=0.01)
+    opts = prb.optimizer.Adam(learning_rate=1e-3, parameters=[emb] + dn, lazy_mode=False)
+    eo, m1e, m2e = emb0.copy(), np.zeros_like(emb0), np.zeros_like(emb0)
+    b1p, b2p = np.float32(0.9), np.float32(0.999)
+    for step in range(3):
+        per_rank = []
+        for r in range(n):
+            rg = np.random.default_rng(5000 + 10 * step + r)
+            cnt = 11 if step == 0 else 5 + 3 * r + step
+            rws = rg.permutation(height)[:cnt]       # unique within a rank: a row occurs at most nranks times
+            per_rank.append((rws, rg.normal(0, 1e-2, (cnt, width)).astype(np.float32)))
+        dps.prepare_for_backward()
+        for i, p in enumerate(dn):
+            p.grad.copy_from_numpy(np.random.default_rng(6000 + 100 * step + 10 * rank + i).normal(0, 1e-2, p.numel).astype(np.float32))
+        emb.grad = prb.SelectedRows(per_rank[rank][0], height, prb.Tensor.from_numpy(per_rank[rank][1].reshape(-1)))
+        for i in reversed(range(len(dn) + 1)):
+            dps.mark_var_ready(i)
+        assert dps.finalized
+        want_rows, want_vals = orc.sparse_allreduce(per_rank, orc.F32)
+        np.testing.assert_array_equal(emb.grad.rows, want_rows)
+        np.testing.assert_array_equal(emb.grad.value.numpy().reshape(-1, width), want_vals)
+        opts.step()
+        prb.current_stream().synchronize()
+        orc.sparse_adam(eo, want_rows, want_vals, m1e, m2e, None, dtype_param=orc.F32, lr=1e-3, beta1=0.9, beta2=0.999,
+                        epsilon=1e-8, beta1_pow=b1p, beta2_pow=b2p, lazy_mode=False)
+        b1p, b2p = np.float32(0.9) * b1p, np.float32(0.999) * b2p
+        if n == 2:   # two addends per row at most: the merge order cannot matter
+            np.testing.assert_array_equal(emb.numpy().reshape(height, width), eo)
+        else:
+            np.testing.assert_allclose(emb.numpy().reshape(height, width), eo, rtol=1e-5, atol=1e-7)
+        np.save(os.path.join(out_dir, "sparse_emb_%d_r%d.npy" % (step, rank)), emb.numpy())
+        opts.clear_grad()
     # sharded optimizer state (ZeRO-1, ref dygraph_sharding_optimizer.py): each parameter is updated by its owner only
     # and broadcast; every rank must end with exactly the bits of the replicated optimizer
     def make(prefix):

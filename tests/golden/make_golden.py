@@ -332,6 +332,36 @@ def gen_update_loss_scaling():
         json.dump(cases, f, indent=1)
 
 
+def gen_sparse_adam():
+    """TestSparseAdamOp of test_adam_op.py (:355-411): literal inputs (height 10, rows [0, 4, 7], 12 columns, everything
+    5.0, gradient ones with two exceptions), both lazy modes, through the reference's own ``adam_step_sparse`` (:304-352).
+    The literals are reproduced from ``setup`` as written there."""
+    step = extract_function(f"{REF}/test_adam_op.py", "adam_step_sparse")
+    beta1, beta2, epsilon = 0.78, 0.836, 1e-4
+    height, rows, row_numel = 10, [0, 4, 7], 12
+    dense = {
+        "Param": np.full((height, row_numel), 5.0).astype("float32"),
+        "Moment1": np.full((height, row_numel), 5.0).astype("float32"),
+        "Moment2": np.full((height, row_numel), 5.0).astype("float32"),
+        "Beta1Pow": np.array([beta1**10]).astype("float32"),
+        "Beta2Pow": np.array([beta2**10]).astype("float32"),
+        "LearningRate": np.full((1), 2.0).astype("float32"),
+    }
+    attrs = {"epsilon": epsilon, "beta1": beta1, "beta2": beta2, "min_row_size_to_use_multithread": 2}
+    grad = np.ones((len(rows), row_numel)).astype("float32")
+    grad[0, 0] = 2.0
+    grad[2, 8] = 4.0
+    store = {"rows": np.array(rows, np.int64), "height": np.array([height]), "grad": grad,
+             "hyper": np.array([beta1, beta2, epsilon])}
+    for k, v in dense.items():
+        store["in/" + k] = v
+    for lazy in (False, True):
+        p, m1, m2 = step(dense, attrs, height, rows, row_numel, grad, lazy)
+        tag = "lazy" if lazy else "full"
+        store[tag + "/ParamOut"], store[tag + "/Moment1Out"], store[tag + "/Moment2Out"] = p, m1, m2
+    np.savez_compressed(f"{OUT}/sparse_adam_optest.npz", **store)
+
+
 if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("reference tree not present; fixtures can only be regenerated in the build container")
@@ -343,4 +373,5 @@ if __name__ == "__main__":
     gen_fused_adam()
     gen_adamw_layerwise()
     gen_update_loss_scaling()
+    gen_sparse_adam()
     print("fixtures written to", OUT)

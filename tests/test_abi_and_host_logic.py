@@ -269,3 +269,48 @@ def test_sharding_optimizer_partitions_parameters_greedily():
     assert opt._param2rank["p5"] == 2
     with pytest.raises(TypeError):
         DygraphShardingOptimizer(HCG(), None, tuple(params), Inner)
+
+
+def test_reducer_sparse_groups_state_machine(prb):
+    """A sparse variable is a group of its own (reducer.cc:94-99, 543-551); it needs a SelectedRows gradient when its
+    hook fires (:858-888); the backward is finalized once the dense groups are launched AND the sparse groups are
+    exchanged."""
+    from paddle_ray_b200._lib import PRBError
+    sizes = [10, 20, 30, 40]
+    ts = [_T(s, orc.F32) for s in sizes]
+    is_sparse = [False, True, False, False]
+    groups = prb.distributed.assign_group_by_size(ts, is_sparse, [400, 400])
+    assert [1] in groups
+    grads = _host_grads(prb, sizes)
+    grads[1] = None
+    red = prb.distributed.EagerReducer(grads, list(reversed(groups)), is_sparse, None)
+    assert red.dense_group_count == len(groups) - 1
+    holder = {"g": None}
+    red.set_sparse_source(1, lambda: holder["g"])
+    red.prepare_for_backward()
+    with pytest.raises(PRBError, match="should have gradient"):
+        red.mark_var_ready(1)
+    holder["g"] = grads[0]
+    with pytest.raises(PRBError, match="must have a selectedrows gradient"):
+        red.mark_var_ready(1)
+    holder["g"] = prb.SelectedRows([2, 0, 2], 5, prb.Tensor(3 * 4, "float32", device=-1))
+    assert holder["g"].width == 4
+    for v in (3, 2):
+        red.mark_var_ready(v)
+    assert not red.finalized
+    red.mark_var_ready(1)
+    assert not red.finalized          # a dense variable is still missing
+    with pytest.raises(PRBError, match="marked ready twice"):
+        red.mark_var_ready(1)
+    red.mark_var_ready(0)
+    assert red.finalized and red.launched_groups() == list(range(red.dense_group_count))
+    red.prepare_for_backward()
+    assert not red.finalized
+    with pytest.raises(PRBError, match="own"):
+        prb.distributed.EagerReducer(grads, [[0, 1], [2, 3]], is_sparse, None)
+    # sparse variables only: no native reducer at all
+    only = prb.distributed.EagerReducer([None], [[0]], [True], None)
+    only.set_sparse_source(0, lambda: holder["g"])
+    only.prepare_for_backward()
+    only.mark_vars_ready([0])
+    assert only.finalized
