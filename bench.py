@@ -175,7 +175,7 @@ def _fill(prb, t, rng, mean_scale, uniform=False):
     return blk if nb == n else None
 
 
-def build_workload(prb, name, rank, arena=False, host_mirror=False, producer_pass1=True):
+def build_workload(prb, name, rank, arena=False, host_mirror=False, producer_pass1=True, sharded=False):
     shapes_name, pdt, gdt, amp, clip, mp, desc = workload_spec(name)
     numels = bench_configs.param_numels(shapes_name)
     rng = np.random.default_rng(1234 + rank)
@@ -203,17 +203,22 @@ def build_workload(prb, name, rank, arena=False, host_mirror=False, producer_pas
     # the reduced gradients are consumed from the bucket arena; nothing reads an unscaled copy back
     opt._write_back_unscaled_grads = False
     opt._use_producer_pass1 = producer_pass1
-    opt._create_accumulators()
-    # moments start away from zero (BASELINE.md section 3: m1 N(0,1e-3), m2 U(0,1e-3), step 10)
-    for p in params:
-        acc = opt._accumulators[p.name]
-        _fill(prb, acc["moment1"], rng, 1e-3)
-        _fill(prb, acc["moment2"], rng, 1e-3, uniform=True)
-    opt._beta1_pow.copy_from_numpy(np.array([0.9 ** 10], np.float32))
-    opt._beta2_pow.copy_from_numpy(np.array([0.999 ** 10], np.float32))
     scaler = prb.amp.GradScaler(init_loss_scaling=2.0 ** 15) if amp else None
     dp = prb.DataParallel(params, comm_buffer_size=25, last_comm_buffer_size=1, consume_from_buckets=True,
                           grads_in_arena=arena)
+    inner = opt
+    if sharded:
+        # optimizer state and update sharded over the ranks: reduce-scatter -> update of the owned arena ranges ->
+        # gather of the parameters (bit-identical parameters, 28/N instead of 28 B/elem in the update pass)
+        opt = prb.distributed.GroupShardedOptimizerStage2(params, inner, dp.group)
+    inner._create_accumulators()
+    # moments start away from zero (BASELINE.md section 3: m1 N(0,1e-3), m2 U(0,1e-3), step 10)
+    for p in inner._parameter_list:
+        acc = inner._accumulators[p.name]
+        _fill(prb, acc["moment1"], rng, 1e-3)
+        _fill(prb, acc["moment2"], rng, 1e-3, uniform=True)
+    inner._beta1_pow.copy_from_numpy(np.array([0.9 ** 10], np.float32))
+    inner._beta2_pow.copy_from_numpy(np.array([0.999 ** 10], np.float32))
     for p in params:  # grads ~ N(0, 1e-2), times the loss scale for AMP runs
         _fill(prb, p.grad, rng, 1e-2 * (2.0 ** 15 if amp else 1.0))
     if host_mirror and not arena:
@@ -223,7 +228,8 @@ def build_workload(prb, name, rank, arena=False, host_mirror=False, producer_pas
     return {"name": name, "params": params, "opt": opt, "scaler": scaler, "dp": dp, "numels": numels, "desc": desc,
             "grad_arena": grad_arena, "host_arena": host_arena, "offs": offs, "amp": amp, "clip": clip, "pdt": pdt,
             "gdt": gdt, "arena": arena, "elems": int(sum(numels)), "buckets": len(dp.group_indices), "gsz": gsz,
-            "bpe": bytes_per_elem(pdt, gdt, amp, clip, arena, producer_pass1), "clip_obj": grad_clip}
+            "bpe": bytes_per_elem(pdt, gdt, amp, clip, arena, producer_pass1), "clip_obj": grad_clip,
+            "sharded": sharded}
 
 
 def make_step(w):
@@ -269,8 +275,11 @@ def read_kernel_timing(prb, w, nranks, steps, peak):
         bpe = kernel_bytes(name, w, nranks)
         e = {"launches_per_step": n.value / steps, "ms_per_step": per_step}
         if bpe:
-            e["algorithmic_bytes_per_step"] = bpe * w["elems"]
-            e["achieved_gbs"] = bpe * w["elems"] / (per_step * 1e-3) / 1e9
+            elems = w["elems"]
+            if w.get("sharded") and nranks > 1 and name == "adam_chunks_kernel":
+                elems = elems / nranks   # each rank updates the arena ranges it owns only
+            e["algorithmic_bytes_per_step"] = bpe * elems
+            e["achieved_gbs"] = bpe * elems / (per_step * 1e-3) / 1e9
             e["frac_of_measured_hbm_peak"] = e["achieved_gbs"] / peak
         out[name] = e
     return out
@@ -510,13 +519,15 @@ def run_reference_arm(args):
 # --------------------------------------------------------------------------------------------
 # N > 1 parity preamble (untimed, < 1 s): the GPU-test box has one GPU, so the multi-rank path proves itself here
 # --------------------------------------------------------------------------------------------
-def parity_preamble(prb, group, arena=False, save_dir=None):
+def parity_preamble(prb, group, arena=False, save_dir=None, sharded=False):
     """A tiny AMP bf16 + master + clip job through the same API on all ranks: one clean step, one step with an Inf
     injected on ONE rank (every rank must skip and halve its loss scale), two more clean steps (even steps mark all
     gradients ready in one call, odd steps hook by hook).  After each step
     parameters, masters, moments and the scaler state must be bit-equal across ranks (checksums compared through
     the communicator); with one or two ranks (at most one addition, so the order cannot matter) they must also equal the oracle's
-    composition of the reference's stages bit for bit.  Returns "ok" or "fail: <what>"."""
+    composition of the reference's stages bit for bit.  Returns "ok" or "fail: <what>".
+    sharded: the same job through GroupShardedOptimizerStage2 (reduce-scatter, update of the owned ranges only,
+    gather of the parameters): the parameters must still be those bits on every rank."""
     from oracle import oracle as orc
     rank, n = group.rank, group.nranks
     sizes = [64, 3 * 3 * 64 * 16, 1000, 7, 4096, 4097, 250000, 1, 300000]
@@ -536,6 +547,10 @@ def parity_preamble(prb, group, arena=False, save_dir=None):
         scaler = prb.amp.GradScaler(init_loss_scaling=2.0 ** 15, decr_every_n_nan_or_inf=1)
         dp = prb.DataParallel(params, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True,
                               grads_in_arena=arena)
+        inner = opt
+        if sharded:
+            opt = prb.distributed.GroupShardedOptimizerStage2(params, inner, group)
+        tag = "shd" if sharded else "amp"
         scale, b1p, b2p = 2.0 ** 15, np.float32(0.9), np.float32(0.999)
         for step in range(4):
             per_rank = [[orc.from_f32((np.random.default_rng(1000 * r + 10 * step + i).normal(0, 1e-2, sz) * 2.0 ** 15 * 30)
@@ -555,17 +570,18 @@ def parity_preamble(prb, group, arena=False, save_dir=None):
             prb.current_stream().synchronize()
             if save_dir is not None:
                 for i, p in enumerate(params):
-                    np.save(os.path.join(save_dir, "amp%d_param_%d_%d_r%d.npy" % (int(arena), step, i, rank)), p.numpy())
-                    np.save(os.path.join(save_dir, "amp%d_m2_%d_%d_r%d.npy" % (int(arena), step, i, rank)),
-                            opt._accumulators[p.name]["moment2"].numpy())
+                    np.save(os.path.join(save_dir, "%s%d_param_%d_%d_r%d.npy" % (tag, int(arena), step, i, rank)), p.numpy())
+                    if not sharded:
+                        np.save(os.path.join(save_dir, "amp%d_m2_%d_%d_r%d.npy" % (int(arena), step, i, rank)),
+                                opt._accumulators[p.name]["moment2"].numpy())
             found = bool(scaler._found_inf.numpy()[0])
             if found != (step == 1):
                 return "fail: step %d found_inf=%s on rank %d" % (step, found, rank)
             # cross-rank bit equality through a checksum
             h = 0
             for p in params:
-                for t in (p, opt._master_weights[p.name], opt._accumulators[p.name]["moment1"],
-                          opt._accumulators[p.name]["moment2"]):
+                for t in ((p,) if sharded else (p, opt._master_weights[p.name], opt._accumulators[p.name]["moment1"],
+                                                opt._accumulators[p.name]["moment2"])):
                     a = t.numpy()
                     h = (h * 1000003 + int(np.bitwise_xor.reduce(a.view(np.uint16 if a.dtype.itemsize == 2 else np.uint32)
                                                                  .astype(np.uint64) * np.arange(1, a.size + 1, dtype=np.uint64)))) % (1 << 52)
@@ -594,14 +610,22 @@ def parity_preamble(prb, group, arena=False, save_dir=None):
                         orc.adam(hst["param"], g, hst["mom1"], hst["mom2"], hst["master"], dtype_param=orc.BF16,
                                  dtype_grad=orc.BF16, lr=1e-3, beta1=0.9, beta2=0.999, epsilon=1e-8, coeff=0.01,
                                  use_decay=True, beta1_pow=b1p, beta2_pow=b2p)
-                        if p.numpy().tobytes() != hst["param"].tobytes() or \
-                                opt._master_weights[p.name].numpy().tobytes() != hst["master"].tobytes():
+                        if p.numpy().tobytes() != hst["param"].tobytes():
+                            return "fail: step %d %s differs from the oracle" % (step, p.name)
+                        if sharded and p.name in opt._param2range:   # state exists for the owned range only
+                            off, ln = opt._param2range[p.name]
+                            if inner._master_weights[p.name].numpy().tobytes() != hst["master"][off:off + ln].tobytes() or \
+                                    inner._accumulators[p.name]["moment2"].numpy().tobytes() != hst["mom2"][off:off + ln].tobytes():
+                                return "fail: step %d %s: sharded state differs from the oracle" % (step, p.name)
+                        elif not sharded and opt._master_weights[p.name].numpy().tobytes() != hst["master"].tobytes():
                             return "fail: step %d %s differs from the oracle" % (step, p.name)
                     b1p, b2p = np.float32(0.9) * b1p, np.float32(0.999) * b2p
         if float(scaler._scale.numpy()[0]) != 2.0 ** 14:
             return "fail: loss scale %g" % float(scaler._scale.numpy()[0])
         if dp._reducer.comm_error():
             return "fail: exchange kernel reported an error"
+        if sharded and n > 1 and dp._reducer.allreduce_backend == "nvlink" and not dp._sharded_armed:
+            return "fail: the reduce-scatter was never switched on"
         return "ok"
     except Exception as e:  # noqa: BLE001
         return "fail: %s: %s" % (type(e).__name__, str(e)[:200])
@@ -802,6 +826,7 @@ def run_gpu_arm(args):
     t_start = time.perf_counter()
 
     parity = parity_preamble(prb, group) if nranks > 1 else None
+    parity_sharded = parity_preamble(prb, group, sharded=True) if nranks > 1 else None
     gc.collect()
 
     # ---- headline workload
@@ -867,29 +892,34 @@ def run_gpu_arm(args):
     nested = {}
     if not args.no_configs:
         ksteps = max(5, min(args.steps, 20))
-        todo = [(n, False) for n in ("resnet50", "gpt2_medium", "bert_base") if n != args.workload]
-        todo += [(args.workload, True), ("resnet50", True)]          # gradients produced in the arena (no pack)
+        todo = [(n, False, False) for n in ("resnet50", "gpt2_medium", "bert_base") if n != args.workload]
+        if nranks > 1:
+            # the sharded step (GroupShardedOptimizerStage2): same parameters bit for bit, update pass 1/N the size
+            todo = [(args.workload, False, True)] + todo + [("gpt2_medium", False, True), ("resnet50", False, True)]
+        todo += [(args.workload, True, False), ("resnet50", True, False)]   # gradients produced in the arena (no pack)
         if nranks == 1:
-            todo += [(n, False) for n in FLAT_SWEEP]
+            todo += [(n, False, False) for n in FLAT_SWEEP]
         else:
-            todo += [("flat26x1", False), ("flat26x1:bf16", False)]
-        for name, arena in todo:
+            todo += [("flat26x1", False, False), ("flat26x1:bf16", False, False)]
+        for name, arena, shd in todo:
+            label = name + ("+arena" if arena else "") + ("+sharded" if shd else "")
             if time.perf_counter() - t_start > args.config_budget_s:
-                nested["_skipped_for_time"] = nested.get("_skipped_for_time", []) + [name + ("+arena" if arena else "")]
+                nested["_skipped_for_time"] = nested.get("_skipped_for_time", []) + [label]
                 continue
             try:
-                wn = build_workload(prb, name, rank, arena=arena)
+                wn = build_workload(prb, name, rank, arena=arena, sharded=shd)
                 mn = measure_workload(prb, group, wn, ksteps, 3, peak)
                 r = nested_result(mn, peak, nranks)
-                if nranks > 1 and name == "resnet50" and not arena and not args.no_overlap:
+                if nranks > 1 and name == "resnet50" and not arena and not shd and not args.no_overlap:
                     # round 1's overlap workload (5 buckets, the last one small), for comparison with its figures
                     r["overlap"] = measure_overlap(prb, wn, group, mn["rank_max"], mn["device_barrier"], steps=20)
-                r["workload"] = wn["desc"] + (" [gradients produced in the bucket arena: no pack]" if arena else "")
+                r["workload"] = wn["desc"] + (" [gradients produced in the bucket arena: no pack]" if arena else "") + \
+                    (" [sharded step: reduce-scatter -> update of the owned 1/%d -> parameter gather]" % nranks if shd else "")
                 r["steps"] = ksteps
-                nested[name + ("+arena" if arena else "")] = r
+                nested[label] = r
                 del wn, mn
             except Exception as e:  # noqa: BLE001  (e.g. out of memory on a smaller GPU): report, keep the line
-                nested[name + ("+arena" if arena else "")] = {"error": "%s: %s" % (type(e).__name__, str(e)[:160])}
+                nested[label] = {"error": "%s: %s" % (type(e).__name__, str(e)[:160])}
             gc.collect()
 
     if rank == 0:
@@ -907,6 +937,7 @@ def run_gpu_arm(args):
             line["overlap"] = overlap
         if parity is not None:
             line["parity_n"] = parity
+            line["parity_n_sharded"] = parity_sharded
         if nested:
             line["configs"] = nested
         print(json.dumps(line), flush=True)

@@ -129,7 +129,8 @@ typedef struct PRB_SelectedRows {
 /* adam_ with a sparse gradient  ref: paddle/phi/kernels/selected_rows/gpu/adam_kernel.cu:95-260
  *   (adam_dense_param_sparse_grad, legacy_ops.yaml:45-55).  Duplicate rows are merged first (scatter::MergeAdd);
  *   lazy_mode updates only the rows that are present, otherwise every element is updated with g = 0 where its row is
- *   absent.  In place (outputs must alias their inputs); learning rate and beta-pows are device scalars. */
+ *   absent.  In place (outputs must alias their inputs); the learning rate is a device scalar, the beta-pow
+ *   accumulators live both on the device or both on the host (the reference's default). */
 int32_t prb_adam_dense_param_sparse_grad(
     const PRB_Tensor* param, const PRB_SelectedRows* grad, const PRB_Tensor* learning_rate, const PRB_Tensor* moment1,
     const PRB_Tensor* moment2, const PRB_Tensor* beta1_pow, const PRB_Tensor* beta2_pow,
@@ -344,6 +345,26 @@ int32_t prb_reducer_bucket_view(const PRB_Reducer* r, int64_t var_index, PRB_Ten
 /* Number of groups launched so far in this backward, and their order (for tests). */
 int32_t prb_reducer_launched_groups(const PRB_Reducer* r, int64_t* out_order, int64_t capacity, int64_t* out_num);
 
+/* Sharded step (ZeRO-style), built on the reducer's own NVLink exchange.  ref: the reference's optimizer-state
+ * sharding, python/paddle/distributed/fleet/meta_parallel/sharding/group_sharded_optimizer_stage2.py:54-612 and
+ * group_sharded_stage2.py (gradients reduced to the rank that owns them, owner-only update, parameters broadcast);
+ * here the owner of an element is decided by position in the bucket arena, not by parameter:
+ *   prb_reducer_set_sharded      the exchange becomes ONE reduce-scatter over all buckets, launched when the last
+ *                                bucket is packed; rank r owns the r-th n-th of the 8192-element chunk list (groups in
+ *                                launch order) and alone holds the reduced gradient there; inf flag and norm
+ *                                partials of prb_reducer_set_grad_epilogue still reach every rank.  *active = 0 when
+ *                                the reducer cannot do it (one rank, or no peer-memory exchange).
+ *   prb_reducer_shard_ranges     the (variable, element offset, length) ranges a rank owns, in chunk order.
+ *   prb_reducer_allgather_params after the owners updated their ranges with PRB_TailConfig.param_to_grad_slot: every
+ *                                rank pulls the ranges it does not own from the owners' arenas into params[v]
+ *                                (one tensor per variable).  skip (optional bool device flag, equal on all ranks):
+ *                                nothing is copied when set. */
+int32_t prb_reducer_set_sharded(PRB_Reducer* r, int32_t enabled, int32_t* active);
+int32_t prb_reducer_shard_ranges(const PRB_Reducer* r, int32_t rank, int64_t* out_var, int64_t* out_offset,
+                                 int64_t* out_length, int64_t capacity, int64_t* out_num);
+int32_t prb_reducer_allgather_params(PRB_Reducer* r, const PRB_Tensor* params, int64_t num, const PRB_Tensor* skip,
+                                     void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Fused step tail: unscale + inf/nan check + global-norm clip + Adam/AdamW in two passes
  * (norm pass, update pass) over the reducer's bucket arena or over caller gradients.
@@ -369,6 +390,13 @@ typedef struct PRB_TailConfig {
   int32_t pass1_done;        /* 1: the producer already cleared/set found_inf and stored the norm partials
                                 (prb_reducer_set_grad_epilogue); the gradient is read once, by the update pass */
   float* pass1_partials;     /* device: *partials_out of prb_reducer_set_grad_epilogue (required with use_clip) */
+  int32_t stage;             /* 0: the whole tail.  A sharded step (prb_reducer_set_sharded) splits it in two calls:
+                                1 = check + norm + clip factor only, over ALL gradients (moments, masters, learning
+                                rate and beta-pows may be NULL; clip_out / global_norm_out are written);
+                                2 = update only, over the sub-tensors this rank owns: the clip factor is READ from
+                                clip_out (when use_clip), found_inf is read as the skip flag, use_amp still unscales */
+  int32_t param_to_grad_slot; /* 1: the updated parameter (dtype of the gradient) is also stored over its gradient:
+                                the bucket arena then carries it to the peers (prb_reducer_allgather_params) */
 } PRB_TailConfig;
 
 /* Per-tensor attributes follow adamw_: lr_ratio[i], with_decay[i] (NULL = 1.0 / all decayed).

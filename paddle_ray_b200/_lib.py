@@ -28,7 +28,8 @@ class TailConfig(C.Structure):
         ("coeff", C.c_float), ("use_adamw", C.c_int32), ("multi_precision", C.c_int32), ("use_amp", C.c_int32),
         ("use_clip", C.c_int32), ("clip_norm", C.c_float), ("auto_skip_clip", C.c_int32), ("use_mp_type", C.c_int32),
         ("write_back_grads", C.c_int32), ("zero_grads", C.c_int32), ("keep_beta_pow", C.c_int32),
-        ("pass1_done", C.c_int32), ("pass1_partials", C.c_void_p),
+        ("pass1_done", C.c_int32), ("pass1_partials", C.c_void_p), ("stage", C.c_int32),
+        ("param_to_grad_slot", C.c_int32),
     ]
 
 
@@ -93,6 +94,9 @@ SIGNATURES = {
     "prb_comm_all_gather": [_vp, _T, _T, _vp],
     "prb_reducer_create": [_T, _i64, _vp, _vp, _i64, _vp, _i32, C.POINTER(_vp)],
     "prb_reducer_destroy": [_vp],
+    "prb_reducer_set_sharded": [_vp, _i32, _vp],
+    "prb_reducer_shard_ranges": [_vp, _i32, _vp, _vp, _vp, _i64, _vp],
+    "prb_reducer_allgather_params": [_vp, _T, _i64, _T, _vp],
     "prb_reducer_prepare_for_backward": [_vp],
     "prb_reducer_set_unused_vars": [_vp, _vp, _i64],
     "prb_reducer_mark_var_ready": [_vp, _i64, _vp],

@@ -14,6 +14,8 @@
 #include <map>
 #include <vector>
 
+#include <type_traits>
+
 #include "prb_adam.cuh"
 #include "prb_fp64.h"
 
@@ -96,6 +98,17 @@ __device__ __forceinline__ void advance_pows_once(const AdamArgs& a, float b1p, 
   }
 }
 
+// What lands in grad_out: the unscaled gradient (what p.grad holds in the reference after a step), or, in a
+// sharded step, the updated parameter on its way to the peers.
+template <typename T, typename TG>
+__device__ __forceinline__ void store_grad_or_param(TG* dst, float g, float p, int param_to_grad) {
+  if constexpr (std::is_same<T, TG>::value) {
+    *dst = param_to_grad ? Conv<T>::from_f32(p) : Conv<TG>::from_f32(g);
+  } else {
+    *dst = Conv<TG>::from_f32(g);
+  }
+}
+
 template <typename T, typename TG, bool kMaster, int kAdamThreads, int kAdamUnroll, int kMinBlocks>
 __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(const AdamArgs a) {
   // Per-tensor coefficients are fetched and derived by ONE thread (while the data loads of the
@@ -172,7 +185,14 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
         store_vec<T>(p_ptr + e, po);
         if (kMaster) store_vec<float>(mp_ptr + e, mpv[u]);
         if (a.zero_grad) store_vec<TG>(const_cast<TG*>(g_ptr) + e, go);
-        else if (go_ptr) store_vec<TG>(go_ptr + e, go);
+        else if (go_ptr) {
+          if constexpr (std::is_same<T, TG>::value) {
+            if (a.param_to_grad) store_vec<T>(reinterpret_cast<T*>(go_ptr) + e, po);
+            else store_vec<TG>(go_ptr + e, go);
+          } else {
+            store_vec<TG>(go_ptr + e, go);
+          }
+        }
       }
     }
     // ---- ragged tail of the tensor's last chunk (< kVec elements)
@@ -187,7 +207,7 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
       p_ptr[e] = Conv<T>::from_f32(p);
       if (kMaster) mp_ptr[e] = p;
       if (a.zero_grad) const_cast<TG*>(g_ptr)[e] = Conv<TG>::from_f32(0.0f);
-      else if (go_ptr) go_ptr[e] = Conv<TG>::from_f32(g);
+      else if (go_ptr) store_grad_or_param<T, TG>(go_ptr + e, g, p, a.param_to_grad);
     }
   } else {
     // Unaligned tensor (caller passed a pointer that is not 32-/16-byte aligned): coalesced
@@ -208,7 +228,7 @@ __global__ void __launch_bounds__(kAdamThreads, kMinBlocks) adam_chunks_kernel(c
       p_ptr[e] = Conv<T>::from_f32(p);
       if (kMaster) mp_ptr[e] = p;
       if (a.zero_grad) const_cast<TG*>(g_ptr)[e] = Conv<TG>::from_f32(0.0f);
-      else if (go_ptr) go_ptr[e] = Conv<TG>::from_f32(g);
+      else if (go_ptr) store_grad_or_param<T, TG>(go_ptr + e, g, p, a.param_to_grad);
     }
   }
 

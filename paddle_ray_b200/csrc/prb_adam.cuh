@@ -36,6 +36,8 @@ struct AdamArgs {
   const float* loss_scale;   // AMP: g = T(MT(g) * inv), inv = float(1.0 / double(*loss_scale)); nullptr = off
   const float* clip;         // global-norm clip: g = T(MT(g) * MT(T(*clip))); nullptr = off
   int32_t zero_grad;         // 1: store zeros to grad after consuming it (clear_grad folded in)
+  int32_t param_to_grad;     // 1: grad_out receives the updated PARAMETER (same dtype) instead of the unscaled
+                             //    gradient: a sharded step ships it to the peers through the bucket arena
   // Shared beta-pow accumulators advanced by the CTA that draws the LAST ticket, which removes the separate
   // 1-thread launch: every CTA has read the old value (and fenced) before it takes its ticket.
   float* pow_b1;             // nullptr = off

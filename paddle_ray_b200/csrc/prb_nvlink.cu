@@ -56,6 +56,9 @@ struct NvlArgs {
   const float* loss_scale;
   bool* found_local;
   size_t partials_off, flags_off;
+  // sharded step
+  int local_only;          // reduce-scatter: the reduced value stays with its owner
+  const bool* skip;        // gather: nothing was updated (found_inf)
 };
 
 // Loads in flight per thread.  NVLink latency is ~2 us: a thread that waits for ONE remote vector at a time
@@ -109,6 +112,10 @@ __device__ __forceinline__ T load_elem_cv(const char* p) {
 
 template <typename T, int kRanks>
 __device__ __forceinline__ void store_all(const NvlArgs& a, size_t off, const Pack<T>& v) {
+  if (a.local_only) {
+    store_vec<T>(reinterpret_cast<T*>(a.arena[a.bar.rank] + off), v);
+    return;
+  }
 #pragma unroll
   for (int q = 0; q < kRanks; ++q)
     if (q < a.bar.nranks) store_vec<T>(reinterpret_cast<T*>(a.arena[q] + off), v);
@@ -188,7 +195,9 @@ __global__ void __launch_bounds__(kNvlThreads, 2) nvl_exchange_chunks_kernel(con
         acc = (q == 0) ? Conv<T>::to_f32(x) : __fadd_rn(acc, Conv<T>::to_f32(x));
       }
       const T out = Conv<T>::from_f32(acc);
-      for (int q = 0; q < n; ++q) *reinterpret_cast<T*>(a.arena[q] + o) = out;
+      if (a.local_only) *reinterpret_cast<T*>(a.arena[r] + o) = out;
+      else
+        for (int q = 0; q < n; ++q) *reinterpret_cast<T*>(a.arena[q] + o) = out;
       ep.elem(out);
     }
     bool any_bad;
@@ -207,6 +216,53 @@ __global__ void __launch_bounds__(kNvlThreads, 2) nvl_exchange_chunks_kernel(con
   if (last && threadIdx.x == 0 && a.found_local != nullptr &&
       *reinterpret_cast<const volatile unsigned int*>(my_arena + a.flags_off) != 0u)
     *a.found_local = true;
+}
+
+// ---- sharded step, second half: pull the chunks the peers own from their arenas into my parameters.
+// CTA b serves peer (rank + 1 + b mod (n-1)) mod n, so every rank reads from all its peers at once and no rank's
+// links serve more than their share.  E = element size: the copy does not care about the type.
+template <typename T>
+__global__ void __launch_bounds__(kNvlThreads, 2) nvl_gather_chunks_kernel(const NvlArgs a) {
+  const int slot = (int)(a.bar.seq & (kSlots - 1));
+  if (!ready_barrier(a.bar, slot)) return;  // every owner's update pass has finished (kernel order + release)
+  const int n = a.bar.nranks, r = a.bar.rank;
+  const bool skipped = a.skip != nullptr && *a.skip;
+  if (!skipped) {
+    const int peers = n - 1;
+    const int pi = (int)blockIdx.x % peers;
+    const int q = (r + 1 + pi) % n;
+    const int first = (int)blockIdx.x / peers, step = ((int)gridDim.x - pi + peers - 1) / peers;
+    const int c0 = (int)((long long)a.nchunks * q / n), c1 = (int)((long long)a.nchunks * (q + 1) / n);
+    const char* my_arena = a.arena[r];
+    for (int c = c0 + first; c < c1; c += step) {
+      const int4 craw = __ldg(reinterpret_cast<const int4*>(a.chunks) + c);
+      const int cn = craw.y;
+      const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
+      const GradDesc* __restrict__ d = a.descs + craw.x;
+      const size_t off = (size_t)(reinterpret_cast<const char*>(d->x) - my_arena) + (size_t)offset * sizeof(T);
+      const char* src = a.arena[q] + off;
+      T* dst = reinterpret_cast<T*>(d->out) + offset;
+      if (d->aligned) {
+        const int nvec = cn / kVec;
+        Pack<T> v[kGradUnroll];
+#pragma unroll
+        for (int u = 0; u < kGradUnroll; ++u) {
+          const int i = u * kNvlThreads + threadIdx.x;
+          if (i < nvec) load_vec<T>(reinterpret_cast<const T*>(src) + (size_t)i * kVec, v[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < kGradUnroll; ++u) {
+          const int i = u * kNvlThreads + threadIdx.x;
+          if (i < nvec) store_vec<T>(dst + (size_t)i * kVec, v[u]);
+        }
+        const int e = nvec * kVec + threadIdx.x;
+        if (e < cn) dst[e] = load_elem_cv<T>(src + (size_t)e * sizeof(T));
+      } else {  // a parameter that is not 32-/16-byte aligned: element-wise
+        for (int e = threadIdx.x; e < cn; e += kNvlThreads) dst[e] = load_elem_cv<T>(src + (size_t)e * sizeof(T));
+      }
+    }
+  }
+  done_barrier(a.bar, slot);  // no peer overwrites its slots (the next pack) before everybody has read them
 }
 
 }  // namespace
@@ -413,6 +469,7 @@ int32_t nvl_exchange(NvlContext* c, const NvlWork& w, cudaStream_t stream) {
   a.bar.seq = ++c->seq;
   a.scale = w.scale;
   a.bias = 0.0f;
+  a.local_only = w.scatter_only ? 1 : 0;
   int ctas;
   if (w.table != nullptr) {
     PRB_ENFORCE(w.loss_scale == nullptr || w.found_local != nullptr, PRB_INVALID_ARGUMENT,
@@ -438,6 +495,30 @@ int32_t nvl_exchange(NvlContext* c, const NvlWork& w, cudaStream_t stream) {
     case PRB_BFLOAT16: e = launch_exchange_ranks<__nv_bfloat16>(a, w, ctas, stream); break;
     case PRB_FLOAT16: e = launch_exchange_ranks<__half>(a, w, ctas, stream); break;
     default: PRB_FAIL(PRB_UNIMPLEMENTED, "nvlink exchange: dtype %s is not built", dtype_name(w.dtype));
+  }
+  PRB_CUDA(e);
+  PRB_LAUNCH_CHECK();
+  return PRB_SUCCESS;
+}
+
+int32_t nvl_gather_params(NvlContext* c, const NvlGather& w, cudaStream_t stream) {
+  PRB_ENFORCE(c != nullptr && w.table != nullptr, PRB_INVALID_ARGUMENT, "nvlink gather: no context or no table");
+  NvlArgs a = c->args;
+  a.bar.seq = ++c->seq;
+  a.descs = reinterpret_cast<const GradDesc*>(w.table->descs);
+  a.chunks = w.table->chunks;
+  a.nchunks = w.table->nchunks;
+  a.skip = w.skip;
+  const int peers = a.bar.nranks - 1;
+  int ctas = (a.nchunks + a.bar.nranks - 1) / a.bar.nranks * peers;  // one CTA per chunk I pull, capped below
+  if (ctas > c->ctas) ctas = c->ctas / peers * peers;
+  if (ctas < peers) ctas = peers;
+  KernelTimer kt(KK_EXCHANGE, stream);
+  cudaError_t e;
+  switch (dtype_size(w.dtype)) {
+    case 4: e = nvl_launch(nvl_gather_chunks_kernel<float>, ctas, kNvlThreads, stream, a); break;
+    case 2: e = nvl_launch(nvl_gather_chunks_kernel<__nv_bfloat16>, ctas, kNvlThreads, stream, a); break;
+    default: PRB_FAIL(PRB_UNIMPLEMENTED, "nvlink gather: dtype %s is not built", dtype_name(w.dtype));
   }
   PRB_CUDA(e);
   PRB_LAUNCH_CHECK();

@@ -30,6 +30,19 @@ struct NvlWork {
   bool* found_local = nullptr;        // this rank's found_inf (set from the sidecar flag when the exchange ends)
   bool norm = false, mp = false;
   size_t partials_off = 0, flags_off = 0;  // byte offsets of the sidecar inside the arena
+  // Reduce-scatter only: the slice owner keeps the reduced values (its own arena only; flags and partials still go
+  // to every rank).  The first half of a sharded step; nvl_gather_params is the second.
+  bool scatter_only = false;
+};
+
+// Second half of a sharded step: every rank PULLS the chunks its peers own (the same n-th of the chunk table as in
+// the reduce-scatter) from the owner's arena -- where the owner's update pass left the new parameter values in
+// place of the gradients -- into desc.out, its own copy of that parameter.  Nothing moves when *skip is set
+// (found_inf: no rank updated anything, the arena still holds gradients).
+struct NvlGather {
+  const DeviceTable* table = nullptr;  // GradDesc: x = the tensor's slot in THIS rank's arena, out = the parameter
+  int32_t dtype = 0;
+  const bool* skip = nullptr;          // device flag, equal on all ranks
 };
 
 // Collective over all ranks.  On success *out is a context, or NULL when the ranks agreed that peer
@@ -40,6 +53,7 @@ int32_t nvl_setup(const NvlCollectives& nc, int nranks, int rank, void* arena, s
 // streams: nvl_next_slot tells which of the two the next call must use.
 int nvl_next_slot(const NvlContext* c);
 int32_t nvl_exchange(NvlContext* c, const NvlWork& w, cudaStream_t stream);
+int32_t nvl_gather_params(NvlContext* c, const NvlGather& w, cudaStream_t stream);
 // Cap on the grid of the exchange kernels (0 = one CTA per SM).
 void nvl_set_max_ctas(NvlContext* c, int max_ctas);
 // 1 if an exchange of this context ran into its time limit or a peer aborted (read from a mapped host word: no sync).

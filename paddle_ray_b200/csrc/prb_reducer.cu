@@ -174,6 +174,13 @@ struct PRB_Reducer {
   int64_t total_chunks = 0;
   Epilogue ep;
   bool grads_in_arena = false;  // gradients are produced in their bucket slots: no pack, no unpack
+  // Sharded step (prb_reducer_set_sharded): ONE reduce-scatter over all groups when the last one is ready instead of
+  // an allreduce per group; rank r owns the r-th n-th of the chunk list of all groups in launch order.
+  bool sharded = false;
+  DeviceTable shard_tab;          // GradDesc chunk table of every slot, groups in launch order
+  bool shard_valid = false;
+  DeviceTable gather_tab;         // the same chunks with out = the caller's parameters (prb_reducer_allgather_params)
+  std::vector<void*> gather_key;
   void* arena_reg = nullptr;  // ncclCommRegister handle of the arena (NULL when unavailable)
   NvlContext* nvl = nullptr;    // allreduce over NVLink peer memory (prb_nvlink.cu)
   NvlsContext* nvls = nullptr;  // allreduce through NVLink multicast (prb_nvls.cu); owns the arena when set
@@ -374,6 +381,49 @@ int32_t check_comm_alive(const PRB_Reducer* r) {
   return PRB_SUCCESS;
 }
 
+bool sharded_active(const PRB_Reducer* r) { return r->sharded && r->comm->nranks > 1 && r->nvl != nullptr; }
+
+std::vector<size_t> all_groups(const PRB_Reducer* r) {
+  std::vector<size_t> gis(r->groups.size());
+  for (size_t i = 0; i < gis.size(); ++i) gis[i] = i;
+  return gis;
+}
+
+// Sharded step, first half: every bucket is packed; one reduce-scatter over all of them on the comm stream.  The
+// slice owner keeps the reduced gradient and leaves the inf flag and the norm partials on EVERY rank.
+int32_t launch_sharded_reduce_scatter(PRB_Reducer* r, cudaStream_t calc) {
+  PRB_Comm* c = r->comm;
+  if (!r->shard_valid) {
+    PRB_TRY(exchange_table(r, all_groups(r), calc, &r->shard_tab));
+    r->shard_valid = true;
+  }
+  cudaStream_t cs = nvl_next_slot(r->nvl) == 1 ? c->stream2 : c->stream;
+  Group& g0 = r->groups.front();
+  Group& g1 = r->groups.back();
+  PRB_CUDA(cudaEventRecord(g0.ready, calc));
+  PRB_CUDA(cudaStreamWaitEvent(cs, g0.ready, 0));
+  const int es = dtype_size(g0.dtype);
+  NvlWork w;
+  w.region_off = g0.arena_off;
+  w.numel = (int64_t)((g1.arena_off + (size_t)g1.length * es - g0.arena_off) / es);
+  w.dtype = g0.dtype;
+  w.fold_scale = r->grads_in_arena;
+  w.scale = (float)(1.0 / (double)c->nranks);
+  w.table = &r->shard_tab;
+  w.scatter_only = true;
+  if (r->ep.on) {
+    w.loss_scale = r->ep.loss_scale;
+    w.found_local = r->ep.found_inf;
+    w.norm = r->ep.norm;
+    w.mp = r->ep.mp;
+    w.partials_off = r->sidecar_off;
+    w.flags_off = sidecar_flags_off(r);
+  }
+  PRB_TRY(nvl_exchange(r->nvl, w, cs));
+  for (Group& g : r->groups) PRB_CUDA(cudaEventRecord(g.done, cs));
+  return PRB_SUCCESS;
+}
+
 // ref: FusedAllReduceSchedule reducer.cc:1037-1070 ("concat > div_nranks > allreduce > split")
 int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   Group& g = r->groups[gi];
@@ -390,7 +440,8 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   // (With find_unused_parameters the ranks may disagree about which groups hold unused parameters, and every rank
   // must issue the same sequence of exchanges: no batching then.)
   const bool batch_here = (c->nranks == 1 && !r->grads_in_arena) ||
-                          (c->nranks > 1 && epilogue_in_exchange(r) && batch_exchange_enabled() && !r->find_unused);
+                          (c->nranks > 1 && epilogue_in_exchange(r) && batch_exchange_enabled() && !r->find_unused) ||
+                          (sharded_active(r) && !r->grads_in_arena);
   if (r->batching && batch_here && !g.has_unused && !g.pack_had_unused && !g.packep_had_unused &&
       (r->batch.empty() || r->groups[r->batch.front()].dtype == g.dtype)) {
     r->batch.push_back(gi);
@@ -431,6 +482,12 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
       g.pack_had_unused = g.has_unused;
     }
     PRB_TRY(launch_scale(g.dtype, g.pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
+  }
+  if (sharded_active(r)) {
+    // nothing to exchange yet: the reduce-scatter covers all groups and starts when the last one is packed
+    r->launched.push_back((int64_t)gi);
+    if (gi + 1 == r->groups.size()) PRB_TRY(launch_sharded_reduce_scatter(r, calc));
+    return PRB_SUCCESS;
   }
   if (c->nranks > 1) {
     // SyncDefaultStream: comm stream waits for the calc stream (ref process_group_nccl.cc:658-667)
@@ -521,7 +578,7 @@ int32_t flush_wave(PRB_Reducer* r, PRB_Reducer::BatchWave& w, cudaStream_t calc)
     PRB_TRY(get_table(unpack.data(), sizeof(MapDesc), (int)unpack.size(), numels.data(), map_chunk_elems(), calc,
                       &w.unpack_tab, /*pin=*/true));
   }
-  if (multi && epilogue_in_exchange(r) && !w.exch_valid) {
+  if (multi && epilogue_in_exchange(r) && !w.exch_valid && !sharded_active(r)) {
     PRB_TRY(exchange_table(r, w.members, calc, &w.exch_tab));
     w.exch_valid = true;
   }
@@ -535,6 +592,7 @@ int32_t flush_wave(PRB_Reducer* r, PRB_Reducer::BatchWave& w, cudaStream_t calc)
     if (r->unpack && need_pack) PRB_TRY(launch_copy(dtype_size(dt), w.unpack_tab, calc));
     return PRB_SUCCESS;
   }
+  if (sharded_active(r)) return PRB_SUCCESS;  // flush_batch launches the one reduce-scatter after the last pack
   // several ranks: ONE exchange for the whole wave (the groups' regions are adjacent in the arena)
   cudaStream_t cs = nvl_next_slot(r->nvl) == 1 ? c->stream2 : c->stream;
   Group& g0 = r->groups[first];
@@ -556,7 +614,7 @@ int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
       w = PRB_Reducer::BatchWave();
     }
     size_t split = r->batch.size();
-    if (r->comm->nranks > 1 && batch_waves() > 1 && r->batch.size() >= 2) {
+    if (r->comm->nranks > 1 && batch_waves() > 1 && r->batch.size() >= 2 && !sharded_active(r)) {
       size_t total = 0, run = 0;
       for (size_t gi : r->batch) total += (size_t)r->groups[gi].length * dtype_size(r->groups[gi].dtype);
       for (split = 0; split + 1 < r->batch.size(); ++split) {
@@ -574,8 +632,12 @@ int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
   r->batch.clear();
   PRB_TRY(epilogue_begin(r, calc));
   PRB_TRY(epilogue_begin_exchange(r, calc));
+  const bool holds_last = !r->waves[0].members.empty() &&
+                          (r->waves[1].members.empty() ? r->waves[0].members.back() : r->waves[1].members.back()) + 1 ==
+                              r->groups.size();
   PRB_TRY(flush_wave(r, r->waves[0], calc));
   PRB_TRY(flush_wave(r, r->waves[1], calc));
+  if (sharded_active(r) && holds_last) PRB_TRY(launch_sharded_reduce_scatter(r, calc));
   return PRB_SUCCESS;
 }
 
@@ -913,6 +975,8 @@ int32_t prb_reducer_destroy(PRB_Reducer* r) {
     for (const DeviceTable* t : {&g.pack_tab, &g.unpack_tab, &g.packep_tab, &g.exch_tab}) release_table(*t);
   for (auto& w : r->waves)
     for (const DeviceTable* t : {&w.pack_tab, &w.unpack_tab, &w.packep_tab, &w.exch_tab}) release_table(*t);
+  release_table(r->shard_tab);
+  release_table(r->gather_tab);
   if (r->arena_reg && g_nccl.CommDeregister) g_nccl.CommDeregister(r->comm->comm, r->arena_reg);
   if (r->nvl) nvl_destroy(r->nvl);
   for (Group& g : r->groups) {
@@ -1033,6 +1097,7 @@ int32_t prb_reducer_set_grad_epilogue(PRB_Reducer* r, const PRB_GradEpilogue* e,
     ep.on = ep.norm || ep.loss_scale != nullptr;
   }
   r->ep = ep;
+  r->shard_valid = false;
   for (Group& g : r->groups) g.packep_valid = g.exch_valid = false;
   for (auto& w : r->waves) w.packep_valid = w.exch_valid = false;
   if (partials_out != nullptr) {
@@ -1136,6 +1201,95 @@ int32_t prb_reducer_launched_groups(const PRB_Reducer* r, int64_t* out_order, in
   *out_num = (int64_t)r->launched.size();
   for (int64_t i = 0; i < capacity && i < (int64_t)r->launched.size(); ++i) out_order[i] = r->launched[(size_t)i];
   return PRB_SUCCESS;
+}
+
+// ---------------------------------------------------------------- sharded step
+int32_t prb_reducer_set_sharded(PRB_Reducer* r, int32_t enabled, int32_t* active) {
+  PRB_ENFORCE(r && !r->dry, PRB_INVALID_ARGUMENT, "reducer: bad handle");
+  PRB_ENFORCE(r->finalized, PRB_PRECONDITION_NOT_MET, "reducer: cannot change the exchange in the middle of a backward");
+  if (enabled) {
+    PRB_ENFORCE(!r->find_unused, PRB_UNIMPLEMENTED,
+                "sharded step: find_unused_parameters is not supported (every rank must pack every bucket)");
+    for (const Group& g : r->groups)
+      PRB_ENFORCE(g.dtype == r->groups.front().dtype, PRB_UNIMPLEMENTED,
+                  "sharded step: all gradients must share one dtype (one reduce-scatter covers every bucket)");
+  }
+  r->sharded = enabled != 0;
+  r->shard_valid = false;
+  r->batch_key.clear();  // the wave split differs between the two modes
+  if (active != nullptr) *active = sharded_active(r) ? 1 : 0;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_shard_ranges(const PRB_Reducer* r, int32_t rank, int64_t* out_var, int64_t* out_offset,
+                                 int64_t* out_length, int64_t capacity, int64_t* out_num) {
+  PRB_ENFORCE(r && out_num, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
+  const int n = r->dry ? 1 : r->comm->nranks;
+  PRB_ENFORCE(rank >= 0 && rank < n, PRB_OUT_OF_RANGE, "shard_ranges: rank %d of %d", rank, n);
+  // the chunk list of launch_sharded_reduce_scatter: groups in launch order, slots in order, 8192-element chunks
+  const int64_t ce = grad_chunk_elems();
+  const int64_t c0 = r->total_chunks * rank / n, c1 = r->total_chunks * (rank + 1) / n;
+  int64_t c = 0, k = 0;
+  for (const Group& g : r->groups) {
+    for (int64_t v : g.vars) {
+      const int64_t numel = r->grads[(size_t)v].numel, nch = (numel + ce - 1) / ce;
+      const int64_t lo = std::max(c, c0), hi = std::min(c + nch, c1);
+      if (lo < hi) {
+        if (k < capacity) {
+          out_var[k] = v;
+          out_offset[k] = (lo - c) * ce;
+          out_length[k] = std::min(numel, (hi - c) * ce) - (lo - c) * ce;
+        }
+        ++k;
+      }
+      c += nch;
+    }
+  }
+  *out_num = k;
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_allgather_params(PRB_Reducer* r, const PRB_Tensor* params, int64_t num, const PRB_Tensor* skip,
+                                     void* stream) {
+  PRB_ENFORCE(r && !r->dry && params, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
+  PRB_ENFORCE(num == (int64_t)r->grads.size(), PRB_INVALID_ARGUMENT,
+              "allgather_params: expected one parameter per gradient (%zu), got %lld", r->grads.size(), (long long)num);
+  if (r->comm->nranks == 1) return PRB_SUCCESS;
+  PRB_ENFORCE(r->nvl != nullptr, PRB_UNIMPLEMENTED, "allgather_params: needs the NVLink peer-memory exchange (PRB_ALLREDUCE=nvlink)");
+  PRB_TRY(check_comm_alive(r));
+  if (skip != nullptr)
+    PRB_ENFORCE(skip->numel == 1 && skip->dtype == PRB_BOOL && skip->device >= 0, PRB_INVALID_ARGUMENT,
+                "allgather_params: skip must be one bool on the device");
+  std::vector<void*> key((size_t)num);
+  for (int64_t v = 0; v < num; ++v) key[(size_t)v] = params[v].data;
+  if (key != r->gather_key) {
+    std::vector<GradDesc> descs;
+    std::vector<int64_t> numels;
+    for (const Group& g : r->groups) {
+      const int es = dtype_size(g.dtype);
+      for (size_t s = 0; s < g.vars.size(); ++s) {
+        const PRB_Tensor& p = params[(size_t)g.vars[s]];
+        PRB_ENFORCE(p.dtype == g.dtype && p.numel == r->grads[(size_t)g.vars[s]].numel && p.device >= 0,
+                    PRB_INVALID_ARGUMENT, "allgather_params: parameter %lld must have its gradient's dtype and size",
+                    (long long)g.vars[s]);
+        GradDesc d{};
+        d.x = r->arena + g.arena_off + (size_t)g.slot_off[s] * es;
+        d.out = p.data;
+        d.aligned = ((uintptr_t)p.data % ((uintptr_t)es * kVec)) == 0 ? 1 : 0;
+        descs.push_back(d);
+        numels.push_back(p.numel);
+      }
+    }
+    release_table(r->gather_tab);
+    PRB_TRY(get_table(descs.data(), sizeof(GradDesc), (int)descs.size(), numels.data(), grad_chunk_elems(),
+                      (cudaStream_t)stream, &r->gather_tab, /*pin=*/true));
+    r->gather_key = key;
+  }
+  NvlGather w;
+  w.table = &r->gather_tab;
+  w.dtype = r->groups.front().dtype;
+  w.skip = skip ? reinterpret_cast<const bool*>(skip->data) : nullptr;
+  return nvl_gather_params(r->nvl, w, (cudaStream_t)stream);
 }
 
 }  // extern "C"

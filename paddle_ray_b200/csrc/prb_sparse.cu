@@ -45,9 +45,10 @@ struct SparseArgs {
   const void* merged;        // [nunique, width]
   const int64_t* urows;      // sorted unique rows
   int64_t nunique, width, height;
-  const float* lr;           // device scalars
-  const float* b1pow;
+  const float* lr;           // device scalar
+  const float* b1pow;        // device scalars, or NULL when the accumulators live on the host (values below)
   const float* b2pow;
+  float b1pow_host, b2pow_host;
   float beta1, beta2, eps;
   const bool* skip;
   int lazy;
@@ -68,7 +69,9 @@ __device__ __forceinline__ int64_t find_row(const int64_t* rows, int64_t n, int6
 template <typename T, bool kMaster>
 __global__ void __launch_bounds__(kSpThreads) sparse_adam_kernel(const SparseArgs a) {
   if (a.skip != nullptr && *a.skip) return;
-  const float lr = __ldg(a.lr), b1p = __ldg(a.b1pow), b2p = __ldg(a.b2pow);
+  const float lr = __ldg(a.lr);
+  const float b1p = a.b1pow != nullptr ? __ldg(a.b1pow) : a.b1pow_host;
+  const float b2p = a.b2pow != nullptr ? __ldg(a.b2pow) : a.b2pow_host;
   const float c1 = __fsub_rn(1.0f, a.beta1), c2 = __fsub_rn(1.0f, a.beta2);
   const float bc2 = __fsqrt_rn(__fsub_rn(1.0f, b2p));
   const float step = -__fdiv_rn(lr, __fsub_rn(1.0f, b1p));
@@ -151,10 +154,15 @@ extern "C" int32_t prb_adam_dense_param_sparse_grad(
   const bool has_master = multi_precision != 0;
   PRB_ENFORCE(!has_master || (master_param && master_param->numel == param->numel && master_param->dtype == PRB_FLOAT32),
               PRB_INVALID_ARGUMENT, "adam (sparse grad): multi_precision requires a float32 master_param");
-  PRB_ENFORCE(learning_rate->numel == 1 && learning_rate->dtype == PRB_FLOAT32 && learning_rate->device >= 0 &&
-                  beta1_pow->numel == 1 && beta2_pow->numel == 1 && beta1_pow->device >= 0 && beta2_pow->device >= 0,
+  PRB_ENFORCE(learning_rate->numel == 1 && learning_rate->dtype == PRB_FLOAT32 && learning_rate->device >= 0,
+              PRB_INVALID_ARGUMENT, "adam (sparse grad): learning_rate must be a single float32 device scalar");
+  // the accumulators may live on the host, as the reference's do by default (adam_kernel.cu:207-229 / :230-252)
+  const bool pows_on_host = beta1_pow->device < 0;
+  PRB_ENFORCE(beta1_pow->numel == 1 && beta2_pow->numel == 1 && beta1_pow->dtype == PRB_FLOAT32 &&
+                  beta2_pow->dtype == PRB_FLOAT32 && (beta2_pow->device < 0) == pows_on_host,
               PRB_INVALID_ARGUMENT,
-              "adam (sparse grad): learning_rate and the beta-pow accumulators must be single float32 device scalars");
+              "adam (sparse grad): the beta-pow accumulators must be single float32 scalars, both on the host or both on "
+              "the device");
   for (const PRB_Tensor* o : {param_out, moment1_out, moment2_out, master_param_out})
     PRB_ENFORCE(o == nullptr || o->data == nullptr || o->data == param->data || o->data == moment1->data ||
                     o->data == moment2->data || (master_param && o->data == master_param->data),
@@ -165,6 +173,13 @@ extern "C" int32_t prb_adam_dense_param_sparse_grad(
                 (long long)skip_update->numel);
     if (skip_update->device < 0) {
       if (*reinterpret_cast<const bool*>(skip_update->data)) return PRB_SUCCESS;
+    } else if (pows_on_host) {
+      // host accumulators advance on the host, so the flag has to be known here: read it back, as the reference
+      // always does (TensorToVector + Wait, adam_kernel.cu:133-143)
+      bool flag = false;
+      PRB_CUDA(cudaMemcpyAsync(&flag, skip_update->data, sizeof(bool), cudaMemcpyDeviceToHost, stream));
+      PRB_CUDA(cudaStreamSynchronize(stream));
+      if (flag) return PRB_SUCCESS;
     } else {
       skip = reinterpret_cast<const bool*>(skip_update->data);
     }
@@ -215,8 +230,13 @@ extern "C" int32_t prb_adam_dense_param_sparse_grad(
   a.width = width;
   a.height = grad->height;
   a.lr = reinterpret_cast<const float*>(learning_rate->data);
-  a.b1pow = reinterpret_cast<const float*>(beta1_pow->data);
-  a.b2pow = reinterpret_cast<const float*>(beta2_pow->data);
+  if (pows_on_host) {
+    a.b1pow_host = *reinterpret_cast<const float*>(beta1_pow->data);
+    a.b2pow_host = *reinterpret_cast<const float*>(beta2_pow->data);
+  } else {
+    a.b1pow = reinterpret_cast<const float*>(beta1_pow->data);
+    a.b2pow = reinterpret_cast<const float*>(beta2_pow->data);
+  }
   a.beta1 = (float)beta1;
   a.beta2 = (float)beta2;
   a.eps = (float)epsilon;
@@ -233,7 +253,13 @@ extern "C" int32_t prb_adam_dense_param_sparse_grad(
     default:
       PRB_TRY(run_sparse<__half>(a, (const __half*)grad->value.data, d_off, d_src, (__half*)d_merged, need_merge, has_master, stream));
   }
-  if (!use_global_beta_pow)
+  if (!use_global_beta_pow && pows_on_host) {
+    const PRB_Tensor* o1 = beta1_pow_out && beta1_pow_out->data ? beta1_pow_out : beta1_pow;
+    const PRB_Tensor* o2 = beta2_pow_out && beta2_pow_out->data ? beta2_pow_out : beta2_pow;
+    *reinterpret_cast<float*>(o1->data) = (float)beta1 * a.b1pow_host;
+    *reinterpret_cast<float*>(o2->data) = (float)beta2 * a.b2pow_host;
+  } else if (!use_global_beta_pow) {
     PRB_TRY(beta_pow_update_device(beta1_pow, beta2_pow, beta1_pow_out, beta2_pow_out, 1, (float)beta1, (float)beta2, skip, stream));
+  }
   return PRB_SUCCESS;
 }

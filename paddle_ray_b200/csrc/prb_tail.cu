@@ -30,14 +30,28 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
                                     PRB_Tensor* global_norm_out, PRB_Tensor* clip_out, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   PRB_TRY(require_device());
-  PRB_ENFORCE(cfg && params && grads && learning_rate && moments1 && moments2 && beta1_pow && beta2_pow && num > 0,
-              PRB_INVALID_ARGUMENT, "dp_step_tail: a required argument is NULL");
-  PRB_ENFORCE(!cfg->multi_precision || master_params, PRB_INVALID_ARGUMENT,
+  PRB_ENFORCE(cfg && params && grads && num > 0, PRB_INVALID_ARGUMENT, "dp_step_tail: a required argument is NULL");
+  PRB_ENFORCE(cfg->stage >= 0 && cfg->stage <= 2, PRB_INVALID_ARGUMENT, "dp_step_tail: stage must be 0, 1 or 2");
+  // A sharded step runs the tail as two calls: stage 1 (check + norm + clip factor over ALL gradients, no update)
+  // and stage 2 (the update over the sub-tensors this rank owns, clip factor and skip flag taken as inputs).
+  const bool check_only = cfg->stage == 1, update_only = cfg->stage == 2;
+  PRB_ENFORCE(check_only || (learning_rate && moments1 && moments2 && beta1_pow && beta2_pow), PRB_INVALID_ARGUMENT,
+              "dp_step_tail: a required argument is NULL");
+  PRB_ENFORCE(check_only || !cfg->multi_precision || master_params, PRB_INVALID_ARGUMENT,
               "dp_step_tail: multi_precision requires master_params");
-  PRB_ENFORCE(learning_rate->numel == 1 && learning_rate->dtype == PRB_FLOAT32 && learning_rate->device >= 0,
-              PRB_INVALID_ARGUMENT, "dp_step_tail: learning_rate must be one float32 on the device");
-  PRB_ENFORCE(beta1_pow->numel == 1 && beta2_pow->numel == 1 && beta1_pow->device >= 0 && beta2_pow->device >= 0,
-              PRB_INVALID_ARGUMENT, "dp_step_tail: beta-pow accumulators must be single device floats");
+  if (!check_only) {
+    PRB_ENFORCE(learning_rate->numel == 1 && learning_rate->dtype == PRB_FLOAT32 && learning_rate->device >= 0,
+                PRB_INVALID_ARGUMENT, "dp_step_tail: learning_rate must be one float32 on the device");
+    PRB_ENFORCE(beta1_pow->numel == 1 && beta2_pow->numel == 1 && beta1_pow->device >= 0 && beta2_pow->device >= 0,
+                PRB_INVALID_ARGUMENT, "dp_step_tail: beta-pow accumulators must be single device floats");
+  }
+  if (update_only && cfg->use_clip)
+    PRB_ENFORCE(clip_out && clip_out->numel == 1 && clip_out->dtype == PRB_FLOAT32 && clip_out->device >= 0,
+                PRB_INVALID_ARGUMENT, "dp_step_tail: stage 2 with use_clip reads the clip factor from clip_out");
+  if (cfg->param_to_grad_slot)
+    PRB_ENFORCE(params[0].dtype == grads[0].dtype && !cfg->zero_grads && !cfg->write_back_grads, PRB_INVALID_ARGUMENT,
+                "dp_step_tail: param_to_grad_slot needs gradients of the parameters' dtype and excludes zero_grads / "
+                "write_back_grads");
   if (cfg->use_amp) {
     PRB_ENFORCE(loss_scale && loss_scale->numel == 1 && loss_scale->dtype == PRB_FLOAT32 && loss_scale->device >= 0,
                 PRB_INVALID_ARGUMENT, "dp_step_tail: use_amp needs a float32 device loss_scale");
@@ -45,20 +59,28 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
                 PRB_INVALID_ARGUMENT, "dp_step_tail: use_amp needs a bool device found_inf");
   }
   const int32_t dt_p = params[0].dtype, dt_g = grads[0].dtype;
-  const bool master = cfg->multi_precision != 0;
+  const bool master = cfg->multi_precision != 0 && !check_only;
 
   std::vector<AdamDesc> descs((size_t)num);
   std::vector<GradDesc> gdescs((size_t)num);
   std::vector<int64_t> numels((size_t)num);
   for (int64_t i = 0; i < num; ++i) {
-    const PRB_Tensor &p = params[i], &g = grads[i], &m1 = moments1[i], &m2 = moments2[i];
+    const PRB_Tensor &p = params[i], &g = grads[i];
     PRB_ENFORCE(p.dtype == dt_p && g.dtype == dt_g, PRB_INVALID_ARGUMENT,
                 "dp_step_tail: tensor %lld: all params (and all grads) must share one dtype per call", (long long)i);
-    PRB_ENFORCE(g.numel == p.numel && m1.numel == p.numel && m2.numel == p.numel && m1.dtype == PRB_FLOAT32 &&
-                    m2.dtype == PRB_FLOAT32,
+    PRB_ENFORCE(g.numel == p.numel && p.device >= 0 && g.device >= 0, PRB_INVALID_ARGUMENT,
+                "dp_step_tail: tensor %lld: parameter and gradient must be device tensors of one size", (long long)i);
+    numels[(size_t)i] = p.numel;
+    GradDesc& gd = gdescs[(size_t)i];
+    memset(&gd, 0, sizeof(gd));
+    gd.x = g.data;
+    gd.out = g.data;
+    gd.aligned = ((uintptr_t)g.data % ((uintptr_t)dtype_size(dt_g) * kVec)) == 0 ? 1 : 0;
+    if (check_only) continue;
+    const PRB_Tensor &m1 = moments1[i], &m2 = moments2[i];
+    PRB_ENFORCE(m1.numel == p.numel && m2.numel == p.numel && m1.dtype == PRB_FLOAT32 && m2.dtype == PRB_FLOAT32,
                 PRB_INVALID_ARGUMENT, "dp_step_tail: tensor %lld: sizes differ or moments are not float32", (long long)i);
-    PRB_ENFORCE(p.device >= 0 && g.device >= 0 && m1.device >= 0 && m2.device >= 0, PRB_INVALID_ARGUMENT,
-                "dp_step_tail: device tensors required");
+    PRB_ENFORCE(m1.device >= 0 && m2.device >= 0, PRB_INVALID_ARGUMENT, "dp_step_tail: device tensors required");
     AdamDesc& d = descs[(size_t)i];
     memset(&d, 0, sizeof(d));
     d.param = p.data;
@@ -66,7 +88,7 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
     d.mom1 = reinterpret_cast<float*>(m1.data);
     d.mom2 = reinterpret_cast<float*>(m2.data);
     d.master = master ? reinterpret_cast<float*>(master_params[i].data) : nullptr;
-    d.grad_out = (cfg->write_back_grads && !cfg->zero_grads) ? g.data : nullptr;
+    d.grad_out = ((cfg->write_back_grads && !cfg->zero_grads) || cfg->param_to_grad_slot) ? g.data : nullptr;
     d.lr = reinterpret_cast<const float*>(learning_rate->data);
     d.b1pow = reinterpret_cast<const float*>(beta1_pow->data);
     d.b2pow = reinterpret_cast<const float*>(beta2_pow->data);
@@ -78,12 +100,6 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
     const bool al = ((uintptr_t)d.param % ap) == 0 && ((uintptr_t)d.grad % ag) == 0 && vec_aligned<float>(d.mom1) &&
                     vec_aligned<float>(d.mom2) && (!master || vec_aligned<float>(d.master));
     d.aligned = al ? 1 : 0;
-    GradDesc& gd = gdescs[(size_t)i];
-    memset(&gd, 0, sizeof(gd));
-    gd.x = g.data;
-    gd.out = g.data;
-    gd.aligned = ((uintptr_t)g.data % ag) == 0 ? 1 : 0;
-    numels[(size_t)i] = p.numel;
   }
 
   const float* ls = cfg->use_amp ? reinterpret_cast<const float*>(loss_scale->data) : nullptr;
@@ -101,8 +117,12 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   if (pass1_done)
     PRB_ENFORCE(!cfg->use_clip || cfg->pass1_partials != nullptr, PRB_INVALID_ARGUMENT,
                 "dp_step_tail: pass1_done with use_clip needs pass1_partials");
-  if (cfg->use_amp && !pass1_done) PRB_CUDA(cudaMemsetAsync(found, 0, 1, stream));
-  if (cfg->use_amp || cfg->use_clip) {
+  if (update_only) {
+    if (cfg->use_clip) clip_dev = reinterpret_cast<const float*>(clip_out->data);
+  } else if (cfg->use_amp && !pass1_done) {
+    PRB_CUDA(cudaMemsetAsync(found, 0, 1, stream));
+  }
+  if (!update_only && (cfg->use_amp || cfg->use_clip)) {
     DeviceTable gt;
     PRB_TRY(get_table(gdescs.data(), sizeof(GradDesc), (int)num, numels.data(), grad_chunk_elems(), stream, &gt));
     float* partials = nullptr;
@@ -148,6 +168,8 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
     }
   }
 
+  if (check_only) return PRB_SUCCESS;
+
   DeviceTable tab;
   PRB_TRY(get_table(descs.data(), sizeof(AdamDesc), (int)num, numels.data(), adam_chunk_elems(), stream, &tab));
   AdamArgs a;
@@ -162,6 +184,7 @@ extern "C" int32_t prb_dp_step_tail(const PRB_TailConfig* cfg, const PRB_Tensor*
   a.loss_scale = ls;
   a.clip = clip_dev;
   a.zero_grad = cfg->zero_grads;
+  a.param_to_grad = cfg->param_to_grad_slot;
   // beta-pow accumulators advance inside the update kernel (last-CTA ticket) unless found_inf
   void* tk = nullptr;
   PRB_TRY(ticket_counter(&tk, stream));

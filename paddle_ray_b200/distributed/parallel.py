@@ -376,6 +376,33 @@ class EagerReducer:
         call("prb_reducer_comm_error", self.handle, C.byref(e))
         return bool(e.value)
 
+    def set_sharded(self, enabled: bool) -> bool:
+        """One reduce-scatter over all buckets instead of an allreduce per bucket (prb_reducer_set_sharded).
+        Returns whether the reducer can do it (several ranks and the peer-memory exchange)."""
+        if self.handle is None or self._sparse_vars:
+            return False
+        active = C.c_int32()
+        call("prb_reducer_set_sharded", self.handle, int(bool(enabled)), C.byref(active))
+        return bool(active.value)
+
+    def shard_ranges(self, rank: int):
+        """[(variable, element offset, length)] owned by ``rank`` in a sharded step, in arena order."""
+        cap = len(self._grads)
+        var, off, ln = ((C.c_int64 * max(cap, 1))() for _ in range(3))
+        n = C.c_int64()
+        call("prb_reducer_shard_ranges", self.handle, int(rank), var, off, ln, cap, C.byref(n))
+        return [(int(var[i]), int(off[i]), int(ln[i])) for i in range(n.value)]
+
+    def allgather_params(self, params, skip=None, stream=None):
+        """Every rank pulls the ranges it does not own from their owners' arenas into ``params`` (one tensor per
+        variable, prb_reducer_allgather_params)."""
+        key = tuple(p.data_ptr for p in params)
+        if getattr(self, "_gather_key", None) != key:
+            self._gather_arr, self._gather_key = tensor_array(params), key
+        sk = skip.prb if skip is not None else None
+        call("prb_reducer_allgather_params", self.handle, self._gather_arr, len(params),
+             C.byref(sk) if sk is not None else None, core._stream_handle(stream))
+
     def set_deferred_wait(self, enabled: bool):
         if self.handle is None:  # sparse groups only
             return
@@ -477,6 +504,8 @@ class DataParallel:
         self._epilogue_key = None     # what the reducer's grad epilogue is currently configured for
         self._epilogue_armed = False  # True once a backward has run with it (its results are there to consume)
         self._epilogue_partials = None
+        self._sharded = False         # the exchange is a reduce-scatter from the NEXT backward on (set_sharded)
+        self._sharded_armed = False   # ... and the backward that just ended ran that way
         if consume_from_buckets or self.grads_in_arena:
             self.consume_from_buckets(True)
 
@@ -524,6 +553,22 @@ class DataParallel:
                 p._reduced_grad = None
                 p._bucket = (None, 0)
 
+    def set_sharded(self, enabled: bool = True) -> bool:
+        """From the next backward on the buckets are reduce-scattered: each rank ends up with the reduced gradient
+        of the arena ranges it owns only (``shard_ranges``) -- the exchange half of a sharded optimizer step
+        (``GroupShardedOptimizerStage2``).  Needs ``consume_from_buckets``; returns False when the reducer cannot do
+        it (one rank, NCCL / NVLS backend, sparse parameters), in which case nothing changes."""
+        if enabled and not self._consume:
+            raise _lib.PRBError(3, "set_sharded: the optimizer must read the buckets (consume_from_buckets=True)")
+        self._sharded = self._reducer.set_sharded(enabled)
+        return self._sharded
+
+    def shard_ranges(self, rank=None):
+        return self._reducer.shard_ranges(self.group.rank if rank is None else rank)
+
+    def allgather_params(self, skip=None, stream=None):
+        self._reducer.allgather_params(self._parameters, skip, stream)
+
     def wait_group(self, group_index: int, stream=None):
         self._reducer.wait_group(group_index, stream)
 
@@ -541,6 +586,7 @@ class DataParallel:
         if self.grad_need_sync:
             self._reducer.prepare_for_backward(unused_vars)
             self._epilogue_armed = self._epilogue_key is not None
+            self._sharded_armed = self._sharded
 
     def _configure_epilogue(self, key, loss_scale=None, found_inf=None, partial_base=None, use_mp_type=False):
         """Called by the optimizer between two backward passes.  key None switches the epilogue off.  Returns True when

@@ -202,6 +202,37 @@ def main(out_dir):
             assert a.numpy().tobytes() == b.numpy().tobytes(), "sharded step %d param %d" % (step, i)
             np.save(os.path.join(out_dir, "shard_param_%d_%d_r%d.npy" % (step, i, rank)), b.numpy())
     assert set(ob._accumulators) == {p.name for p in owned}   # moments exist for the local shard only
+    # the B200-native sharded step (GroupShardedOptimizerStage2: reduce-scatter -> update of the owned arena ranges ->
+    # gather of the parameters) against the replicated optimizer: fp32, no AMP, no clip; then AMP bf16 + master + clip
+    # with an Inf on one rank against the oracle
+    pc = make("gs2")
+    dpc = prb.DataParallel(pc, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True)
+    oc = prb.distributed.GroupShardedOptimizerStage2(pc, prb.optimizer.AdamW(learning_rate=1e-3, parameters=pc, weight_decay=0.01), group)
+    mine = dpc.shard_ranges()
+    everyone = [dpc.shard_ranges(r) for r in range(n)]
+    assert sum(ln for rr in everyone for _, _, ln in rr) == sum(sizes) and mine == everyone[rank]
+    pd = make("rep2")
+    dpd = prb.DataParallel(pd, comm_buffer_size=0.4, last_comm_buffer_size=0.01, consume_from_buckets=True)
+    od = prb.optimizer.AdamW(learning_rate=1e-3, parameters=pd, weight_decay=0.01)
+    for step in range(4):
+        for dp_, op_ in ((dpd, od), (dpc, oc)):
+            dp_.prepare_for_backward()
+            if step % 2 == 0:
+                dp_.mark_all_ready()
+            else:
+                for i in reversed(range(len(pc))):
+                    dp_.mark_var_ready(i)
+            op_.step()
+        prb.current_stream().synchronize()
+        assert dpc._sharded == (dpc._reducer.allreduce_backend == "nvlink")
+        for i, (a, b) in enumerate(zip(pd, pc)):
+            assert a.numpy().tobytes() == b.numpy().tobytes(), "GroupShardedOptimizerStage2 step %d param %d" % (step, i)
+            np.save(os.path.join(out_dir, "gs2_param_%d_%d_r%d.npy" % (step, i, rank)), b.numpy())
+    assert sum(v.numel for v in oc.local_params) == sum(ln for _, _, ln in mine)
+    assert abs(sum(ln for _, _, ln in mine) - sum(sizes) / n) <= 2 * 8192 + max(sizes) * 0   # equal shares to a chunk
+    for arena in (False, True):
+        verdict = bench.parity_preamble(prb, group, arena=arena, save_dir=out_dir, sharded=True)
+        assert verdict == "ok", "sharded AMP + clip parity (arena=%s): %s" % (arena, verdict)
     # timing helper used by bench.py: max over ranks through the communicator
     t = prb.Tensor.from_numpy(np.array([float(rank + 1)], np.float32))
     group.all_reduce(t, "max")

@@ -22,7 +22,7 @@ def prb():
 
 
 def _run_op(prb, p0, rows, vals, m10, m20, master0, dtype, lazy, b1p0, b2p0, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8,
-            skip=None, use_global_beta_pow=False):
+            skip=None, use_global_beta_pow=False, pows_on_host=False, skip_on_host=False):
     T = prb.Tensor
     height = p0.shape[0]
     p = T.from_numpy(p0.reshape(-1), dtype)
@@ -31,8 +31,9 @@ def _run_op(prb, p0, rows, vals, m10, m20, master0, dtype, lazy, b1p0, b2p0, lr=
     value = T.from_numpy(np.ascontiguousarray(vals).reshape(-1), dtype) if vals.size else T(0, dtype)
     g = prb.SelectedRows(rows, height, value)
     lrt = T.from_numpy(np.array([lr], np.float32))
-    b1p, b2p = T.from_numpy(np.array([b1p0], np.float32)), T.from_numpy(np.array([b2p0], np.float32))
-    sk = T.from_numpy(np.array([skip], np.bool_)) if skip is not None else None
+    dev = -1 if pows_on_host else None
+    b1p, b2p = T.from_numpy(np.array([b1p0], np.float32), device=dev), T.from_numpy(np.array([b2p0], np.float32), device=dev)
+    sk = T.from_numpy(np.array([skip], np.bool_), device=-1 if skip_on_host else None) if skip is not None else None
     prb._C_ops.adam_(p, g, lrt, m1, m2, b1p, b2p, master, sk, beta1, beta2, eps, lazy, 1000, master is not None,
                      use_global_beta_pow)
     shape = p0.shape
@@ -119,6 +120,18 @@ def test_sorted_unique_rows_use_the_values_in_place_and_edge_cases(prb):
     assert got[4] == b1p and got[5] == b2p
     got = _run_op(prb, p0, rows, vals, m10, m20, None, orc.F32, False, b1p, b2p, use_global_beta_pow=True)
     assert got[4] == b1p and got[5] == b2p and not np.array_equal(got[0], p0)
+    # beta-pow accumulators on the host (the reference's default placement): same bits, advanced on the host; a skip
+    # flag on the device is read back first, like the reference does
+    dev_run = _run_op(prb, p0, rows, vals, m10, m20, None, orc.F32, True, b1p, b2p)
+    host_run = _run_op(prb, p0, rows, vals, m10, m20, None, orc.F32, True, b1p, b2p, pows_on_host=True)
+    for a, b in zip(dev_run[:3], host_run[:3]):
+        bits_equal(a, b)
+    assert host_run[4] == dev_run[4] == np.float32(0.9) * b1p and host_run[5] == dev_run[5]
+    for skip_on_host in (False, True):
+        got = _run_op(prb, p0, rows, vals, m10, m20, None, orc.F32, True, b1p, b2p, pows_on_host=True, skip=True,
+                      skip_on_host=skip_on_host)
+        bits_equal(got[0], p0)
+        assert got[4] == b1p and got[5] == b2p
     # a row outside the table is refused before anything is launched
     with pytest.raises(prb._lib.PRBError):
         _run_op(prb, p0, np.array([height]), vals[:1], m10, m20, None, orc.F32, False, b1p, b2p)

@@ -294,3 +294,14 @@ def test_reducer_hooks_in_any_order_unused_params_and_no_sync(prb):
     assert dp.finalized
     for p, h in zip(params, host):
         bits_equal(p.grad.numpy(), orc.scale(h["grad"], orc.F32, 1.0))
+
+
+def test_group_sharded_optimizer_on_one_rank_matches_the_oracle(prb):
+    """GroupShardedOptimizerStage2 with a single rank owns everything: the tail split in two calls (check + norm +
+    clip factor over all gradients, then the update with the parameter written over its gradient) must give the
+    bits of the one-call tail -- the AMP bf16 + master + clip job of bench.parity_preamble, gradients packed and
+    produced in the arena.  (Several ranks: tests/dist_worker.py.)"""
+    import bench
+    group = prb.distributed.init_parallel_env()
+    for arena in (False, True):
+        assert bench.parity_preamble(prb, group, arena=arena, sharded=True) == "ok"
