@@ -370,6 +370,16 @@ void fill_bar(const SignalSet& s, int nranks, int rank, Bar* b) {
 // calc stream it is supposed to hide under -- with a 730 us backward at 8 ranks the exposed communication was 77 us
 // with 148 CTAs and 9 us with 64, 32 or 16 (profiles/r2_exchange_sweep_n8.log; NCCL, 580 us of exchanges: 12 us).
 // PRB_NVL_CTAS overrides; prb_reducer_set_exchange_ctas changes it at run time.
+// The two kernels of a sharded step run when the backward is over (the reduce-scatter starts after the LAST bucket,
+// the gather after the update): nothing on the calc stream to slow down, and remote loads need bytes in flight --
+// two ranks, 16-byte vectors, 4 per thread: 449 GB/s per direction with 64 CTAs, 614 with 148, 619 with 296
+// (tools/probe/p2p_probe.cu, profiles/r2_p2p_probe.log).  PRB_NVL_SHARD_CTAS overrides.
+static int shard_ctas() {
+  int n = 2 * sm_count();
+  if (const char* e = getenv("PRB_NVL_SHARD_CTAS")) n = atoi(e) > 0 ? atoi(e) : n;
+  return n;
+}
+
 static int default_ctas() {
   int n = sm_count() < 64 ? sm_count() : 64;
   if (const char* e = getenv("PRB_NVL_CTAS")) n = atoi(e) > 0 ? atoi(e) : n;
@@ -486,7 +496,8 @@ int32_t nvl_exchange(NvlContext* c, const NvlWork& w, cudaStream_t stream) {
     const long long per_rank = (a.nvec + a.bar.nranks - 1) / a.bar.nranks;
     ctas = (int)((per_rank + kNvlThreads - 1) / kNvlThreads);
   }
-  if (ctas > c->ctas) ctas = c->ctas;  // at most one CTA per SM, each looping over its share of the slice
+  const int cap = w.scatter_only ? shard_ctas() : c->ctas;
+  if (ctas > cap) ctas = cap;  // each CTA loops over its share of the slice
   if (ctas < 1) ctas = 1;
   KernelTimer kt(KK_EXCHANGE, stream);
   cudaError_t e;
@@ -511,7 +522,7 @@ int32_t nvl_gather_params(NvlContext* c, const NvlGather& w, cudaStream_t stream
   a.skip = w.skip;
   const int peers = a.bar.nranks - 1;
   int ctas = (a.nchunks + a.bar.nranks - 1) / a.bar.nranks * peers;  // one CTA per chunk I pull, capped below
-  if (ctas > c->ctas) ctas = c->ctas / peers * peers;
+  if (ctas > shard_ctas()) ctas = shard_ctas() / peers * peers;
   if (ctas < peers) ctas = peers;
   KernelTimer kt(KK_EXCHANGE, stream);
   cudaError_t e;

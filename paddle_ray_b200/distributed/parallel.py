@@ -396,6 +396,13 @@ class EagerReducer:
     def allgather_params(self, params, skip=None, stream=None):
         """Every rank pulls the ranges it does not own from their owners' arenas into ``params`` (one tensor per
         variable, prb_reducer_allgather_params)."""
+        if self._group is not None and self._group.nranks > 1 and self.allreduce_backend != "nvlink":
+            # NCCL / NVLS reducers: every owner broadcasts its ranges (a step that found an Inf broadcasts the
+            # unchanged values)
+            for r in range(self._group.nranks):
+                for v, off, ln in self.shard_ranges(r):
+                    self._group.broadcast(params[v].view(off, ln), r, stream)
+            return
         key = tuple(p.data_ptr for p in params)
         if getattr(self, "_gather_key", None) != key:
             self._gather_arr, self._gather_key = tensor_array(params), key
