@@ -797,6 +797,47 @@ def measure_overlap(prb, w, group, rank_max, device_barrier, steps=40):
     return out
 
 
+def measure_sparse_adam(prb, peak, iters=20):
+    """adam_ with a SelectedRows gradient on BERT-base's word-embedding table (30522 x 768, fp32): 8192 looked-up rows
+    per step with duplicates (a batch of token ids), lazy_mode.  One call = host sort + dedup of the indices, one
+    H2D copy of the index tables, the merge kernel, the update kernel, the beta-pow kernel; timed with CUDA events
+    around `iters` calls (so the host part counts when it is slower than the device part).  Algorithmic bytes:
+    merge r nrows x w x 4 + w u x w x 4, update 28 B per element of the u unique rows."""
+    height, width, nrows = 30522, 768, 8192
+    rng = np.random.default_rng(99)
+    T = prb.Tensor
+    p = T.from_numpy(rng.normal(0, 0.02, height * width).astype(np.float32))
+    m1, m2 = T.zeros(height * width, "float32"), T.zeros(height * width, "float32")
+    lr = T.from_numpy(np.array([1e-3], np.float32))
+    b1p, b2p = T.from_numpy(np.array([0.9], np.float32)), T.from_numpy(np.array([0.999], np.float32))
+    rows = rng.integers(0, height, nrows)
+    uniq = int(np.unique(rows).size)
+    g = prb.SelectedRows(rows, height, T.from_numpy(rng.normal(0, 1e-2, nrows * width).astype(np.float32)))
+
+    def call():
+        prb._C_ops.adam_(p, g, lr, m1, m2, b1p, b2p, None, None, 0.9, 0.999, 1e-8, True, 1000, False, False)
+
+    for _ in range(3):
+        call()
+    prb.current_stream().synchronize()
+    e0, e1 = prb.Event(), prb.Event()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(iters):
+        call()
+    e1.record()
+    host_ms = (time.perf_counter() - t0) * 1e3 / iters
+    e1.synchronize()
+    ms = e0.elapsed_ms(e1) / iters
+    nbytes = nrows * width * 4 + uniq * width * 4 + 28 * uniq * width
+    return {"workload": "adam_ (SelectedRows grad, lazy_mode) on a 30522 x 768 fp32 embedding table, %d rows per step, "
+                        "%d unique" % (nrows, uniq),
+            "ms_per_step": ms, "host_issue_ms_per_step": host_ms, "algorithmic_bytes_per_step": nbytes,
+            "value": nbytes / (ms * 1e-3) / 1e9, "pct_of_measured_hbm_peak_per_gpu": 100.0 * nbytes / (ms * 1e-3) / 1e9 / peak,
+            "launches_per_step": 3.0, "steps": iters,
+            "dense_equivalent_bytes": 28 * height * width}
+
+
 # --------------------------------------------------------------------------------------------
 # the GPU arm
 # --------------------------------------------------------------------------------------------
@@ -921,6 +962,12 @@ def run_gpu_arm(args):
             except Exception as e:  # noqa: BLE001  (e.g. out of memory on a smaller GPU): report, keep the line
                 nested[label] = {"error": "%s: %s" % (type(e).__name__, str(e)[:160])}
             gc.collect()
+
+    if not args.no_configs and nranks == 1:
+        try:
+            nested["sparse_adam:bert_embedding"] = measure_sparse_adam(prb, peak)
+        except Exception as e:  # noqa: BLE001
+            nested["sparse_adam:bert_embedding"] = {"error": "%s: %s" % (type(e).__name__, str(e)[:160])}
 
     if rank == 0:
         line = {

@@ -172,6 +172,11 @@ class Optimizer:
         found_inf = self._get_auxiliary_var("found_inf")
         loss_scale = self._get_auxiliary_var("loss_scale")  # set by GradScaler when the unscale is deferred to us
         clip = self._grad_clip
+        dp0 = pg[0][0]._bucket[0]
+        if dp0 is not None and dp0._sharded_armed:
+            raise _lib.PRBError(3, "this backward was reduce-scattered (DataParallel.set_sharded): every rank holds the "
+                                   "reduced gradient of its own arena ranges only; step through "
+                                   "GroupShardedOptimizerStage2")
         if any(isinstance(g, SelectedRows) for _, g in pg):
             dense = [(p, g) for p, g in pg if not isinstance(g, SelectedRows)]
             self._sparse_step([(p, g) for p, g in pg if isinstance(g, SelectedRows)], found_inf, loss_scale,

@@ -13,7 +13,7 @@ except Exception as e:
 print(d["ms_per_step"], d["value"], d["ms_per_step_instrumented"], d["gpu_launches"])
 print({k:(round(v["ms_per_step"],4), v["launches_per_step"]) for k,v in d["kernels"].items()})
 print(d["roofline"]["frac"], d["e2e"]["ms_per_step"], d.get("cpu_baseline",{}).get("value"))
-for k,v in d.get("configs",{}).items(): print(k, {a:b for a,b in v.items() if a not in ("kernels","workload","roofline")}, {kk:round(vv["ms_per_step"],4) for kk,vv in v.get("kernels",{}).items()})
+for k,v in d.get("configs",{}).items(): print(k, {a:b for a,b in v.items() if a not in ("kernels","workload","roofline","overlap")}, {kk:round(vv["ms_per_step"],4) for kk,vv in v.get("kernels",{}).items()})
 PY
 if [ "$2" = "ncu" ]; then
   timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"grad_pass_kernel|adam_chunks_kernel|norm_finalize_kernel|map_chunks_kernel|update_loss_scaling" -c 200 --csv --log-file $out/launches.csv \

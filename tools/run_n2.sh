@@ -18,5 +18,5 @@ print(d["ms_per_step"], d["value"], d["ms_per_step_instrumented"], d["gpu_launch
 print({k:(round(v["ms_per_step"],4), v["launches_per_step"]) for k,v in d["kernels"].items()})
 print(d["e2e"]["ms_per_step"])
 print(d["overlap"]["total_comm_ms"], [(round(c["t_bwd_ms"],3),round(c["step_ms"],3),round(c["step_no_comm_ms"],3),round(c["overlap_frac"],3)) for c in d["overlap"]["cases"]])
-for k,v in d.get("configs",{}).items(): print(k, {a:b for a,b in v.items() if a not in ("kernels","workload","roofline")}, {kk:round(vv["ms_per_step"],4) for kk,vv in v.get("kernels",{}).items()})
+for k,v in d.get("configs",{}).items(): print(k, {a:b for a,b in v.items() if a not in ("kernels","workload","roofline","overlap")}, {kk:round(vv["ms_per_step"],4) for kk,vv in v.get("kernels",{}).items()})
 PY
