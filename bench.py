@@ -210,7 +210,7 @@ def build_workload(prb, name, rank, arena=False, host_mirror=False, producer_pas
     if sharded:
         # optimizer state and update sharded over the ranks: reduce-scatter -> update of the owned arena ranges ->
         # gather of the parameters (bit-identical parameters, 28/N instead of 28 B/elem in the update pass)
-        opt = prb.distributed.GroupShardedOptimizerStage2(params, inner, dp.group)
+        opt = prb.distributed.GroupShardedOptimizerStage2(params, inner, dp.group, reduce_overlap=(sharded == "bucket"))
     inner._create_accumulators()
     # moments start away from zero (m1 N(0,1e-3), m2 U(0,1e-3), step 10)
     for p in inner._parameter_list:
@@ -549,8 +549,8 @@ def parity_preamble(prb, group, arena=False, save_dir=None, sharded=False):
                               grads_in_arena=arena)
         inner = opt
         if sharded:
-            opt = prb.distributed.GroupShardedOptimizerStage2(params, inner, group)
-        tag = "shd" if sharded else "amp"
+            opt = prb.distributed.GroupShardedOptimizerStage2(params, inner, group, reduce_overlap=(sharded == "bucket"))
+        tag = ("shb" if sharded == "bucket" else "shd") if sharded else "amp"
         scale, b1p, b2p = 2.0 ** 15, np.float32(0.9), np.float32(0.999)
         for step in range(4):
             per_rank = [[orc.from_f32((np.random.default_rng(1000 * r + 10 * step + i).normal(0, 1e-2, sz) * 2.0 ** 15 * 30)
@@ -797,6 +797,39 @@ def measure_overlap(prb, w, group, rank_max, device_barrier, steps=40):
     return out
 
 
+def measure_exposed_tail(prb, group, w, t_bwd_us, rank_max, device_barrier, steps=20):
+    """What a training job pays AFTER its backward pass ends: a synthetic backward (spin kernels on the calc stream,
+    t_bwd_us in total, one slice per bucket) marks the buckets ready one by one, then the optimizer steps; returned
+    is step time minus the backward time.  The replicated step hides all exchanges but the last under the backward;
+    the sharded step hides its reduce-scatters only with the per-bucket layout."""
+    stream = prb.current_stream()
+    dp = w["dp"]
+    _, tail = make_step(w)
+    groups = list(reversed(dp.group_indices))  # launch order
+    idx = [(C.c_int64 * len(g))(*sorted(g, reverse=True)) for g in groups]
+    per = max(1, int(t_bwd_us / len(groups)))
+
+    def one():
+        dp.prepare_for_backward()
+        for arr in idx:
+            prb._lib.call("prb_spin", per, stream.handle)
+            dp._reducer.mark_vars_ready(arr)
+        tail()
+    for _ in range(4):
+        one()
+    group.barrier()
+    prb.synchronize()
+    a, b = prb.Event(), prb.Event()
+    device_barrier()
+    a.record()
+    for _ in range(steps):
+        one()
+    b.record()
+    b.synchronize()
+    step_ms = rank_max(a.elapsed_ms(b)) / steps
+    return {"t_bwd_ms": per * len(groups) / 1e3, "step_ms": step_ms, "exposed_tail_ms": step_ms - per * len(groups) / 1e3}
+
+
 def measure_sparse_adam(prb, peak, iters=20):
     """adam_ with a SelectedRows gradient on BERT-base's word-embedding table (30522 x 768, fp32): 8192 looked-up rows
     per step with duplicates (a batch of token ids), lazy_mode.  One call = host sort + dedup of the indices, one
@@ -868,6 +901,7 @@ def run_gpu_arm(args):
 
     parity = parity_preamble(prb, group) if nranks > 1 else None
     parity_sharded = parity_preamble(prb, group, sharded=True) if nranks > 1 else None
+    parity_sharded_pb = parity_preamble(prb, group, sharded="bucket") if nranks > 1 else None
     gc.collect()
 
     # ---- headline workload
@@ -906,8 +940,12 @@ def run_gpu_arm(args):
     e2e = measure_e2e(prb, group, w, args.steps, rank_max)
 
     overlap = None
+    t_bwd_tail_us = 0.0
     if nranks > 1 and not args.no_overlap:
         overlap = measure_overlap(prb, w, group, rank_max, device_barrier)
+        # the same synthetic backward (2 x the exchanges' total) in front of the replicated and the sharded steps
+        t_bwd_tail_us = overlap["cases"][1]["t_bwd_ms"] * 1e3
+        overlap["after_backward"] = measure_exposed_tail(prb, group, w, t_bwd_tail_us, rank_max, device_barrier)
 
     # CPU baseline (rank 0, N = 1 only): bounded sample of the same workload on the host cores
     cpu_baseline = None
@@ -936,14 +974,15 @@ def run_gpu_arm(args):
         todo = [(n, False, False) for n in ("resnet50", "gpt2_medium", "bert_base") if n != args.workload]
         if nranks > 1:
             # the sharded step (GroupShardedOptimizerStage2): same parameters bit for bit, update pass 1/N the size
-            todo = [(args.workload, False, True)] + todo + [("gpt2_medium", False, True), ("resnet50", False, True)]
+            todo = [(args.workload, False, True), (args.workload, False, "bucket")] + todo + \
+                [("gpt2_medium", False, True), ("resnet50", False, True)]
         todo += [(args.workload, True, False), ("resnet50", True, False)]   # gradients produced in the arena (no pack)
         if nranks == 1:
             todo += [(n, False, False) for n in FLAT_SWEEP]
         else:
             todo += [("flat26x1", False, False), ("flat26x1:bf16", False, False)]
         for name, arena, shd in todo:
-            label = name + ("+arena" if arena else "") + ("+sharded" if shd else "")
+            label = name + ("+arena" if arena else "") + (("+sharded_per_bucket" if shd == "bucket" else "+sharded") if shd else "")
             if time.perf_counter() - t_start > args.config_budget_s:
                 nested["_skipped_for_time"] = nested.get("_skipped_for_time", []) + [label]
                 continue
@@ -954,8 +993,12 @@ def run_gpu_arm(args):
                 if nranks > 1 and name == "resnet50" and not arena and not shd and not args.no_overlap:
                     # round 1's overlap workload (5 buckets, the last one small), for comparison with its figures
                     r["overlap"] = measure_overlap(prb, wn, group, mn["rank_max"], mn["device_barrier"], steps=20)
+                if nranks > 1 and name == args.workload and shd and t_bwd_tail_us:
+                    r["after_backward"] = measure_exposed_tail(prb, group, wn, t_bwd_tail_us, mn["rank_max"],
+                                                               mn["device_barrier"])
                 r["workload"] = wn["desc"] + (" [gradients produced in the bucket arena: no pack]" if arena else "") + \
-                    (" [sharded step: reduce-scatter -> update of the owned 1/%d -> parameter gather]" % nranks if shd else "")
+                    (" [sharded step: reduce-scatter -> update of the owned 1/%d -> parameter gather%s]"
+                     % (nranks, "; ownership and reduce-scatter per bucket" if shd == "bucket" else "") if shd else "")
                 r["steps"] = ksteps
                 nested[label] = r
                 del wn, mn
@@ -985,6 +1028,7 @@ def run_gpu_arm(args):
         if parity is not None:
             line["parity_n"] = parity
             line["parity_n_sharded"] = parity_sharded
+            line["parity_n_sharded_per_bucket"] = parity_sharded_pb
         if nested:
             line["configs"] = nested
         print(json.dumps(line), flush=True)

@@ -360,8 +360,17 @@ int32_t prb_reducer_launched_groups(const PRB_Reducer* r, int64_t* out_order, in
  *                                (one tensor per variable).  skip (optional bool device flag, equal on all ranks):
  *                                nothing is copied when set. */
 int32_t prb_reducer_set_sharded(PRB_Reducer* r, int32_t enabled, int32_t* active);
-int32_t prb_reducer_shard_ranges(const PRB_Reducer* r, int32_t rank, int64_t* out_var, int64_t* out_offset,
-                                 int64_t* out_length, int64_t capacity, int64_t* out_num);
+int32_t prb_reducer_shard_ranges(const PRB_Reducer* r, int32_t rank, int32_t nranks /* 0: the communicator's */,
+                                 int64_t* out_var, int64_t* out_offset, int64_t* out_length, int64_t capacity,
+                                 int64_t* out_num);
+/* Ownership layout, chosen before prb_reducer_set_sharded and before anybody asks for shard_ranges:
+ *   per_bucket = 0 (default)  rank r owns the r-th n-th of the chunk list of ALL buckets; ONE reduce-scatter, launched
+ *                             after the last bucket is packed (fewest launches and barriers: best when no backward
+ *                             pass is left to hide under);
+ *   per_bucket = 1            rank r owns the r-th n-th of EACH bucket; one reduce-scatter per bucket, launched when
+ *                             that bucket is packed, on the comm streams like the allreduce (ref: the per-parameter
+ *                             reduce hooks of group_sharded_stage2.py:308-420, which also overlap the backward). */
+int32_t prb_reducer_set_shard_layout(PRB_Reducer* r, int32_t per_bucket);
 int32_t prb_reducer_allgather_params(PRB_Reducer* r, const PRB_Tensor* params, int64_t num, const PRB_Tensor* skip,
                                      void* stream);
 

@@ -95,7 +95,8 @@ SIGNATURES = {
     "prb_reducer_create": [_T, _i64, _vp, _vp, _i64, _vp, _i32, C.POINTER(_vp)],
     "prb_reducer_destroy": [_vp],
     "prb_reducer_set_sharded": [_vp, _i32, _vp],
-    "prb_reducer_shard_ranges": [_vp, _i32, _vp, _vp, _vp, _i64, _vp],
+    "prb_reducer_shard_ranges": [_vp, _i32, _i32, _vp, _vp, _vp, _i64, _vp],
+    "prb_reducer_set_shard_layout": [_vp, _i32],
     "prb_reducer_allgather_params": [_vp, _T, _i64, _T, _vp],
     "prb_reducer_prepare_for_backward": [_vp],
     "prb_reducer_set_unused_vars": [_vp, _vp, _i64],

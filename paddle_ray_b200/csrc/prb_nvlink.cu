@@ -59,6 +59,8 @@ struct NvlArgs {
   // sharded step
   int local_only;          // reduce-scatter: the reduced value stays with its owner
   const bool* skip;        // gather: nothing was updated (found_inf)
+  int nseg;                // gather: ownership segments of the chunk list
+  int seg_first[kMaxShardSegments + 1];
 };
 
 // Loads in flight per thread.  NVLink latency is ~2 us: a thread that waits for ONE remote vector at a time
@@ -232,9 +234,23 @@ __global__ void __launch_bounds__(kNvlThreads, 2) nvl_gather_chunks_kernel(const
     const int pi = (int)blockIdx.x % peers;
     const int q = (r + 1 + pi) % n;
     const int first = (int)blockIdx.x / peers, step = ((int)gridDim.x - pi + peers - 1) / peers;
-    const int c0 = (int)((long long)a.nchunks * q / n), c1 = (int)((long long)a.nchunks * (q + 1) / n);
     const char* my_arena = a.arena[r];
-    for (int c = c0 + first; c < c1; c += step) {
+    // peer q owns the q-th n-th of every segment; the CTAs that serve q walk its chunks as one list
+    int seg = 0, seg_base = 0;  // chunks of q in the segments before `seg`
+    int s0 = a.seg_first[0] + (int)((long long)(a.seg_first[1] - a.seg_first[0]) * q / n);
+    int s1 = a.seg_first[0] + (int)((long long)(a.seg_first[1] - a.seg_first[0]) * (q + 1) / n);
+    for (int fi = first;; fi += step) {
+      while (seg < a.nseg && fi - seg_base >= s1 - s0) {
+        seg_base += s1 - s0;
+        ++seg;
+        if (seg < a.nseg) {
+          const int f = a.seg_first[seg], len = a.seg_first[seg + 1] - f;
+          s0 = f + (int)((long long)len * q / n);
+          s1 = f + (int)((long long)len * (q + 1) / n);
+        }
+      }
+      if (seg >= a.nseg) break;
+      const int c = s0 + (fi - seg_base);
       const int4 craw = __ldg(reinterpret_cast<const int4*>(a.chunks) + c);
       const int cn = craw.y;
       const int64_t offset = (int64_t)(((uint64_t)(uint32_t)craw.w << 32) | (uint32_t)craw.z);
@@ -496,7 +512,7 @@ int32_t nvl_exchange(NvlContext* c, const NvlWork& w, cudaStream_t stream) {
     const long long per_rank = (a.nvec + a.bar.nranks - 1) / a.bar.nranks;
     ctas = (int)((per_rank + kNvlThreads - 1) / kNvlThreads);
   }
-  const int cap = w.scatter_only ? shard_ctas() : c->ctas;
+  const int cap = (w.scatter_only && !w.overlap_grid) ? shard_ctas() : c->ctas;
   if (ctas > cap) ctas = cap;  // each CTA loops over its share of the slice
   if (ctas < 1) ctas = 1;
   KernelTimer kt(KK_EXCHANGE, stream);
@@ -520,6 +536,9 @@ int32_t nvl_gather_params(NvlContext* c, const NvlGather& w, cudaStream_t stream
   a.chunks = w.table->chunks;
   a.nchunks = w.table->nchunks;
   a.skip = w.skip;
+  PRB_ENFORCE(w.nseg >= 1 && w.nseg <= kMaxShardSegments, PRB_INVALID_ARGUMENT, "nvlink gather: bad segment count %d", w.nseg);
+  a.nseg = w.nseg;
+  for (int s = 0; s <= w.nseg; ++s) a.seg_first[s] = w.seg_first[s];
   const int peers = a.bar.nranks - 1;
   int ctas = (a.nchunks + a.bar.nranks - 1) / a.bar.nranks * peers;  // one CTA per chunk I pull, capped below
   if (ctas > shard_ctas()) ctas = shard_ctas() / peers * peers;

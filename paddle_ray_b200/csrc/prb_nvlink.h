@@ -33,7 +33,10 @@ struct NvlWork {
   // Reduce-scatter only: the slice owner keeps the reduced values (its own arena only; flags and partials still go
   // to every rank).  The first half of a sharded step; nvl_gather_params is the second.
   bool scatter_only = false;
+  bool overlap_grid = false;  // scatter_only while a backward is running: keep the allreduce's grid cap
 };
+
+constexpr int kMaxShardSegments = 64;
 
 // Second half of a sharded step: every rank PULLS the chunks its peers own (the same n-th of the chunk table as in
 // the reduce-scatter) from the owner's arena -- where the owner's update pass left the new parameter values in
@@ -43,6 +46,10 @@ struct NvlGather {
   const DeviceTable* table = nullptr;  // GradDesc: x = the tensor's slot in THIS rank's arena, out = the parameter
   int32_t dtype = 0;
   const bool* skip = nullptr;          // device flag, equal on all ranks
+  // Ownership: rank q owns the q-th n-th of every segment [seg_first[s], seg_first[s + 1]) of the chunk list
+  // (one segment = the whole table, or one segment per bucket: prb_reducer_set_shard_layout)
+  int nseg = 1;
+  int seg_first[kMaxShardSegments + 1] = {0};
 };
 
 // Collective over all ranks.  On success *out is a context, or NULL when the ranks agreed that peer

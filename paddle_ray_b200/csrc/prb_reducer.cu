@@ -177,6 +177,11 @@ struct PRB_Reducer {
   // Sharded step (prb_reducer_set_sharded): ONE reduce-scatter over all groups when the last one is ready instead of
   // an allreduce per group; rank r owns the r-th n-th of the chunk list of all groups in launch order.
   bool sharded = false;
+  // Ownership layout of a sharded step (prb_reducer_set_shard_layout, fixed before the optimizer builds its views):
+  //   false  rank r owns the r-th n-th of the chunk list of ALL groups: one reduce-scatter after the last pack;
+  //   true   rank r owns the r-th n-th of EACH group's chunk list: one reduce-scatter per bucket, launched as soon as
+  //          the bucket is packed, so that all but the last hide under the rest of the backward pass.
+  bool shard_per_bucket = false;
   DeviceTable shard_tab;          // GradDesc chunk table of every slot, groups in launch order
   bool shard_valid = false;
   DeviceTable gather_tab;         // the same chunks with out = the caller's parameters (prb_reducer_allgather_params)
@@ -343,7 +348,8 @@ size_t sidecar_flags_off(const PRB_Reducer* r) {
 }
 
 // The library's own exchange of the contiguous arena region of groups [first, last] on comm stream `cs`.
-int32_t nvl_exchange_groups(PRB_Reducer* r, size_t first, size_t last, const DeviceTable* table, cudaStream_t cs) {
+int32_t nvl_exchange_groups(PRB_Reducer* r, size_t first, size_t last, const DeviceTable* table, cudaStream_t cs,
+                            bool scatter_only = false) {
   const Group &g0 = r->groups[first], &g1 = r->groups[last];
   const int es = dtype_size(g0.dtype);
   NvlWork w;
@@ -352,6 +358,13 @@ int32_t nvl_exchange_groups(PRB_Reducer* r, size_t first, size_t last, const Dev
   w.dtype = g0.dtype;
   w.fold_scale = r->grads_in_arena;
   w.scale = (float)(1.0 / (double)r->comm->nranks);
+  if (scatter_only) {
+    // reduce-scatter of one bucket while the backward pass is still running: the owner keeps the reduced values;
+    // the grid stays at the allreduce's cap so that the calc stream's kernels are not slowed down
+    w.table = table;
+    w.scatter_only = true;
+    w.overlap_grid = true;
+  }
   if (table != nullptr && epilogue_in_exchange(r)) {
     w.table = table;
     w.loss_scale = r->ep.loss_scale;
@@ -439,9 +452,12 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
   // without such a dependency buckets stay separate so that the optimizer can consume them one by one.
   // (With find_unused_parameters the ranks may disagree about which groups hold unused parameters, and every rank
   // must issue the same sequence of exchanges: no batching then.)
-  const bool batch_here = (c->nranks == 1 && !r->grads_in_arena) ||
-                          (c->nranks > 1 && epilogue_in_exchange(r) && batch_exchange_enabled() && !r->find_unused) ||
-                          (sharded_active(r) && !r->grads_in_arena);
+  const bool shard_unit = sharded_active(r) && !r->shard_per_bucket;   // one reduce-scatter for all buckets
+  const bool shard_each = sharded_active(r) && r->shard_per_bucket;    // one per bucket, like the allreduce
+  const bool batch_here = !shard_each &&
+                          ((c->nranks == 1 && !r->grads_in_arena) ||
+                           (c->nranks > 1 && epilogue_in_exchange(r) && batch_exchange_enabled() && !r->find_unused) ||
+                           (shard_unit && !r->grads_in_arena));
   if (r->batching && batch_here && !g.has_unused && !g.pack_had_unused && !g.packep_had_unused &&
       (r->batch.empty() || r->groups[r->batch.front()].dtype == g.dtype)) {
     r->batch.push_back(gi);
@@ -483,7 +499,7 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
     }
     PRB_TRY(launch_scale(g.dtype, g.pack_tab, 1.0 / (double)c->nranks, 0.0f, false, calc));
   }
-  if (sharded_active(r)) {
+  if (shard_unit) {
     // nothing to exchange yet: the reduce-scatter covers all groups and starts when the last one is packed
     r->launched.push_back((int64_t)gi);
     if (gi + 1 == r->groups.size()) PRB_TRY(launch_sharded_reduce_scatter(r, calc));
@@ -499,17 +515,17 @@ int32_t schedule_group(PRB_Reducer* r, size_t gi, cudaStream_t calc) {
     if (r->nvls != nullptr) {
       PRB_TRY(nvls_allreduce(r->nvls, g.arena_off, g.length, g.dtype, cs));
     } else if (r->nvl != nullptr) {
-      if (epilogue_in_exchange(r) && !g.exch_valid) {
+      if ((epilogue_in_exchange(r) || shard_each) && !g.exch_valid) {
         PRB_TRY(exchange_table(r, {gi}, cs, &g.exch_tab));
         g.exch_valid = true;
       }
-      PRB_TRY(nvl_exchange_groups(r, gi, gi, epilogue_in_exchange(r) ? &g.exch_tab : nullptr, cs));
+      PRB_TRY(nvl_exchange_groups(r, gi, gi, (epilogue_in_exchange(r) || shard_each) ? &g.exch_tab : nullptr, cs, shard_each));
     } else {
       ncclDataType_t nt;
       PRB_TRY(nccl_dtype(g.dtype, &nt));
       PRB_NCCL(g_nccl.AllReduce(region, region, (size_t)g.length, nt, ncclSum, c->comm, cs));
     }
-    if (r->unpack && !r->grads_in_arena) {  // the reference also splits on the comm stream (reducer.cc:1062-1069)
+    if (r->unpack && !r->grads_in_arena && !shard_each) {  // the reference also splits on the comm stream (reducer.cc:1062-1069)
       if (!g.unpack_valid) {
         PRB_TRY(group_tables(r, g, true, cs, &g.unpack_tab));
         g.unpack_valid = true;
@@ -637,7 +653,7 @@ int32_t flush_batch(PRB_Reducer* r, cudaStream_t calc) {
                               r->groups.size();
   PRB_TRY(flush_wave(r, r->waves[0], calc));
   PRB_TRY(flush_wave(r, r->waves[1], calc));
-  if (sharded_active(r) && holds_last) PRB_TRY(launch_sharded_reduce_scatter(r, calc));
+  if (sharded_active(r) && !r->shard_per_bucket && holds_last) PRB_TRY(launch_sharded_reduce_scatter(r, calc));
   return PRB_SUCCESS;
 }
 
@@ -1221,29 +1237,51 @@ int32_t prb_reducer_set_sharded(PRB_Reducer* r, int32_t enabled, int32_t* active
   return PRB_SUCCESS;
 }
 
-int32_t prb_reducer_shard_ranges(const PRB_Reducer* r, int32_t rank, int64_t* out_var, int64_t* out_offset,
+int32_t prb_reducer_set_shard_layout(PRB_Reducer* r, int32_t per_bucket) {
+  PRB_ENFORCE(r, PRB_INVALID_ARGUMENT, "reducer: NULL handle");
+  PRB_ENFORCE(r->finalized && !r->sharded, PRB_PRECONDITION_NOT_MET,
+              "reducer: the ownership layout is fixed before the sharded step is switched on");
+  PRB_ENFORCE(!per_bucket || (int)r->groups.size() <= kMaxShardSegments, PRB_UNIMPLEMENTED,
+              "sharded step: a per-bucket layout supports at most %d buckets, this reducer has %zu", kMaxShardSegments,
+              r->groups.size());
+  r->shard_per_bucket = per_bucket != 0;
+  r->gather_key.clear();
+  return PRB_SUCCESS;
+}
+
+int32_t prb_reducer_shard_ranges(const PRB_Reducer* r, int32_t rank, int32_t nranks, int64_t* out_var, int64_t* out_offset,
                                  int64_t* out_length, int64_t capacity, int64_t* out_num) {
   PRB_ENFORCE(r && out_num, PRB_INVALID_ARGUMENT, "reducer: bad arguments");
-  const int n = r->dry ? 1 : r->comm->nranks;
+  const int n = nranks > 0 ? nranks : (r->dry ? 1 : r->comm->nranks);
   PRB_ENFORCE(rank >= 0 && rank < n, PRB_OUT_OF_RANGE, "shard_ranges: rank %d of %d", rank, n);
-  // the chunk list of launch_sharded_reduce_scatter: groups in launch order, slots in order, 8192-element chunks
+  // The chunk list of the exchange kernels: groups in launch order, slots in order, 8192-element chunks.  One
+  // ownership segment = the whole list, or one per group (prb_reducer_set_shard_layout); rank r owns the r-th n-th
+  // of every segment: chunks [f + len * r / n, f + len * (r + 1) / n) -- the formula the kernels use.
   const int64_t ce = grad_chunk_elems();
-  const int64_t c0 = r->total_chunks * rank / n, c1 = r->total_chunks * (rank + 1) / n;
-  int64_t c = 0, k = 0;
-  for (const Group& g : r->groups) {
+  int64_t k = 0, c = 0;
+  auto emit = [&](const Group& g, int64_t c0, int64_t c1, int64_t& cc) {
     for (int64_t v : g.vars) {
       const int64_t numel = r->grads[(size_t)v].numel, nch = (numel + ce - 1) / ce;
-      const int64_t lo = std::max(c, c0), hi = std::min(c + nch, c1);
+      const int64_t lo = std::max(cc, c0), hi = std::min(cc + nch, c1);
       if (lo < hi) {
         if (k < capacity) {
           out_var[k] = v;
-          out_offset[k] = (lo - c) * ce;
-          out_length[k] = std::min(numel, (hi - c) * ce) - (lo - c) * ce;
+          out_offset[k] = (lo - cc) * ce;
+          out_length[k] = std::min(numel, (hi - cc) * ce) - (lo - cc) * ce;
         }
         ++k;
       }
-      c += nch;
+      cc += nch;
     }
+  };
+  for (size_t gi = 0; gi < r->groups.size(); ++gi) {
+    const Group& g = r->groups[gi];
+    int64_t f = 0, len = r->total_chunks;
+    if (r->shard_per_bucket) {
+      f = g.first_chunk;
+      len = (gi + 1 < r->groups.size() ? r->groups[gi + 1].first_chunk : r->total_chunks) - f;
+    }
+    emit(g, f + len * rank / n, f + len * (rank + 1) / n, c);
   }
   *out_num = k;
   return PRB_SUCCESS;
@@ -1288,6 +1326,15 @@ int32_t prb_reducer_allgather_params(PRB_Reducer* r, const PRB_Tensor* params, i
   NvlGather w;
   w.table = &r->gather_tab;
   w.dtype = r->groups.front().dtype;
+  if (r->shard_per_bucket) {
+    w.nseg = (int)r->groups.size();
+    for (size_t gi = 0; gi < r->groups.size(); ++gi) w.seg_first[gi] = (int)r->groups[gi].first_chunk;
+    w.seg_first[w.nseg] = (int)r->total_chunks;
+  } else {
+    w.nseg = 1;
+    w.seg_first[0] = 0;
+    w.seg_first[1] = (int)r->total_chunks;
+  }
   w.skip = skip ? reinterpret_cast<const bool*>(skip->data) : nullptr;
   return nvl_gather_params(r->nvl, w, (cudaStream_t)stream);
 }

@@ -385,13 +385,18 @@ class EagerReducer:
         call("prb_reducer_set_sharded", self.handle, int(bool(enabled)), C.byref(active))
         return bool(active.value)
 
-    def shard_ranges(self, rank: int):
-        """[(variable, element offset, length)] owned by ``rank`` in a sharded step, in arena order."""
+    def shard_ranges(self, rank: int, nranks: int = 0):
+        """[(variable, element offset, length)] owned by ``rank`` in a sharded step, in arena order (``nranks`` 0: the
+        communicator's size; any other value answers for a hypothetical job of that size)."""
         cap = len(self._grads)
         var, off, ln = ((C.c_int64 * max(cap, 1))() for _ in range(3))
         n = C.c_int64()
-        call("prb_reducer_shard_ranges", self.handle, int(rank), var, off, ln, cap, C.byref(n))
+        call("prb_reducer_shard_ranges", self.handle, int(rank), int(nranks), var, off, ln, cap, C.byref(n))
         return [(int(var[i]), int(off[i]), int(ln[i])) for i in range(n.value)]
+
+    def set_shard_layout(self, per_bucket: bool):
+        if self.handle is not None:
+            call("prb_reducer_set_shard_layout", self.handle, int(bool(per_bucket)))
 
     def allgather_params(self, params, skip=None, stream=None):
         """Every rank pulls the ranges it does not own from their owners' arenas into ``params`` (one tensor per
@@ -569,6 +574,12 @@ class DataParallel:
             raise _lib.PRBError(3, "set_sharded: the optimizer must read the buckets (consume_from_buckets=True)")
         self._sharded = self._reducer.set_sharded(enabled)
         return self._sharded
+
+    def set_shard_layout(self, per_bucket: bool):
+        """False (default): a rank owns one n-th of the whole arena, one reduce-scatter after the last bucket.  True: a
+        rank owns one n-th of every bucket, one reduce-scatter per bucket as soon as it is packed (they hide under
+        the rest of the backward pass).  To be chosen before the sharded optimizer is built."""
+        self._reducer.set_shard_layout(per_bucket)
 
     def shard_ranges(self, rank=None):
         return self._reducer.shard_ranges(self.group.rank if rank is None else rank)

@@ -161,7 +161,11 @@ class GroupShardedOptimizerStage2:
     """
 
     def __init__(self, params, optim, group=None, offload=False, device="gpu", pertrain_sync_models=True,
-                 dp_group=None, **kw):
+                 dp_group=None, reduce_overlap=False, **kw):
+        """``reduce_overlap`` (ref ``_set_reduce_overlap``, group_sharded_optimizer_stage2.py:237-239): True shards every
+        BUCKET over the ranks and reduce-scatters each bucket as soon as it is packed, so that all but the last
+        exchange hide under the rest of the backward pass; False (default) shards the arena as a whole and runs ONE
+        reduce-scatter after the last bucket (fewer launches and barriers when there is nothing to hide under)."""
         if offload:
             raise _lib.PRBError(4, "GroupShardedOptimizerStage2: offload is not built")
         self._all_params = list(params)
@@ -176,6 +180,7 @@ class GroupShardedOptimizerStage2:
         if len({p.dtype for p in self._all_params}) != 1:
             raise _lib.PRBError(4, "GroupShardedOptimizerStage2: parameters of one dtype only")
         self._dp = dp
+        dp.set_shard_layout(bool(reduce_overlap))
         self._group = group if group is not None else dp.group
         self._rank, self._nranks = self._group.rank, self._group.nranks
         # the ranges this rank owns, as parameter-like views (what the wrapped optimizer now optimizes)

@@ -232,8 +232,9 @@ def main(out_dir):
     chunks = [sum((ln + 8191) // 8192 for _, _, ln in rr) for rr in everyone]   # equal shares, to within one chunk
     assert max(chunks) - min(chunks) <= 1, chunks
     for arena in (False, True):
-        verdict = bench.parity_preamble(prb, group, arena=arena, save_dir=out_dir, sharded=True)
-        assert verdict == "ok", "sharded AMP + clip parity (arena=%s): %s" % (arena, verdict)
+        for layout in (True, "bucket"):   # one reduce-scatter for the whole arena / one per bucket
+            verdict = bench.parity_preamble(prb, group, arena=arena, save_dir=out_dir, sharded=layout)
+            assert verdict == "ok", "sharded AMP + clip parity (arena=%s, layout=%s): %s" % (arena, layout, verdict)
     # timing helper used by bench.py: max over ranks through the communicator
     t = prb.Tensor.from_numpy(np.array([float(rank + 1)], np.float32))
     group.all_reduce(t, "max")

@@ -314,3 +314,45 @@ def test_reducer_sparse_groups_state_machine(prb):
     only.prepare_for_backward()
     only.mark_vars_ready([0])
     assert only.finalized
+
+
+def test_shard_ranges_cover_every_element_once(prb):
+    """prb_reducer_shard_ranges on the host-only reducer (one rank owns everything): ranges follow the arena order
+    (groups in launch order, slots in order), one range per variable, all elements covered."""
+    sizes = [10, 20000, 8192, 1, 30000]
+    groups = [[4, 3], [2], [1, 0]]
+    red = prb.distributed.EagerReducer(_host_grads(prb, sizes), groups, [False] * 5, None)
+    got = red.shard_ranges(0)
+    assert got == [(4, 0, 30000), (3, 0, 1), (2, 0, 8192), (1, 0, 20000), (0, 0, 10)]
+    from paddle_ray_b200._lib import PRBError
+    with pytest.raises(PRBError):
+        red.shard_ranges(1)
+    # any world size, both layouts: every element owned exactly once, one range per variable and rank, chunk-aligned
+    # offsets; equal shares to within a chunk -- of the whole arena, or of every bucket
+    rng = np.random.default_rng(4)
+    for trial in range(20):
+        n = int(rng.integers(3, 40))
+        sizes = [int(x) for x in rng.integers(1, 60000, n)]
+        groups = list(reversed(prb.distributed.assign_group_by_size([_T(s, orc.F32) for s in sizes], [False] * n, [60000, 200000])))
+        for per_bucket in (False, True):
+            red = prb.distributed.EagerReducer(_host_grads(prb, sizes), groups, [False] * n, None)
+            red.set_shard_layout(per_bucket)
+            for world in (2, 3, 8):
+                owned = np.zeros(sum(sizes), np.int32)
+                start = np.concatenate([[0], np.cumsum(sizes)])
+                per_rank = []
+                for r in range(world):
+                    rr = red.shard_ranges(r, world)
+                    assert len({v for v, _, _ in rr}) == len(rr)
+                    for v, off, ln in rr:
+                        assert off % 8192 == 0 and ln > 0 and off + ln <= sizes[v]
+                        owned[start[v] + off:start[v] + off + ln] += 1
+                    per_rank.append(rr)
+                assert (owned == 1).all()
+                if per_bucket:
+                    for g in groups:
+                        ch = [sum((ln + 8191) // 8192 for v, _, ln in rr if v in g) for rr in per_rank]
+                        assert max(ch) - min(ch) <= 1, (g, ch)
+                else:
+                    ch = [sum((ln + 8191) // 8192 for _, _, ln in rr) for rr in per_rank]
+                    assert max(ch) - min(ch) <= 1, ch

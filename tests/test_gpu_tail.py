@@ -304,4 +304,5 @@ def test_group_sharded_optimizer_on_one_rank_matches_the_oracle(prb):
     import bench
     group = prb.distributed.init_parallel_env()
     for arena in (False, True):
-        assert bench.parity_preamble(prb, group, arena=arena, sharded=True) == "ok"
+        for layout in (True, "bucket"):
+            assert bench.parity_preamble(prb, group, arena=arena, sharded=layout) == "ok"

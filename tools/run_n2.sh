@@ -14,7 +14,7 @@ try:
     d=json.loads([l for l in open("$out/bench_n$N.json") if l.startswith("{")][-1])
 except Exception as e:
     print("no bench line:", e); raise SystemExit
-print(d["ms_per_step"], d["value"], d["ms_per_step_instrumented"], d["gpu_launches"], d.get("parity_n"))
+print(d["ms_per_step"], d["value"], d["ms_per_step_instrumented"], d["gpu_launches"], d.get("parity_n"), d.get("parity_n_sharded"), d.get("parity_n_sharded_per_bucket")); print("after_backward", d["overlap"].get("after_backward"), {k:v.get("after_backward") for k,v in d.get("configs",{}).items() if isinstance(v,dict) and "after_backward" in v})
 print({k:(round(v["ms_per_step"],4), v["launches_per_step"]) for k,v in d["kernels"].items()})
 print(d["e2e"]["ms_per_step"])
 print(d["overlap"]["total_comm_ms"], [(round(c["t_bwd_ms"],3),round(c["step_ms"],3),round(c["step_no_comm_ms"],3),round(c["overlap_frac"],3)) for c in d["overlap"]["cases"]])
