@@ -356,3 +356,54 @@ def test_shard_ranges_cover_every_element_once(prb):
                 else:
                     ch = [sum((ln + 8191) // 8192 for _, _, ln in rr) for rr in per_rank]
                     assert max(ch) - min(ch) <= 1, ch
+
+
+def test_gather_kernel_chunk_walk_restated():
+    """The index arithmetic of nvl_gather_chunks_kernel (csrc/prb_nvlink.cu: CTA b serves peer (rank + 1 + b mod (n-1))
+    mod n and walks that peer's chunks of every ownership segment as one list), restated in Python: for every rank,
+    grid size and segment table, the CTAs that serve peer q visit exactly q's chunks -- the n-th of every segment
+    that prb_reducer_shard_ranges assigns to q -- once each, and never the rank's own."""
+    import random
+
+    def walk(nseg, seg_first, n, r, grid):
+        peers, got = n - 1, {}
+        for b in range(grid):
+            pi = b % peers
+            q = (r + 1 + pi) % n
+            fi, step = b // peers, (grid - pi + peers - 1) // peers
+            seg = seg_base = 0
+            s0 = seg_first[0] + (seg_first[1] - seg_first[0]) * q // n
+            s1 = seg_first[0] + (seg_first[1] - seg_first[0]) * (q + 1) // n
+            while True:
+                while seg < nseg and fi - seg_base >= s1 - s0:
+                    seg_base += s1 - s0
+                    seg += 1
+                    if seg < nseg:
+                        f, ln = seg_first[seg], seg_first[seg + 1] - seg_first[seg]
+                        s0, s1 = f + ln * q // n, f + ln * (q + 1) // n
+                if seg >= nseg:
+                    break
+                got.setdefault(q, []).append(s0 + (fi - seg_base))
+                fi += step
+        return got
+
+    random.seed(1)
+    for trial in range(200):
+        n = random.choice([2, 3, 4, 8])
+        nseg = random.randint(1, 30)
+        lens = [random.randint(0, 3 if trial % 3 == 0 else 40) for _ in range(nseg)]
+        sf = [0]
+        for ln in lens:
+            sf.append(sf[-1] + ln)
+        for r in range(n):
+            peers = n - 1
+            ctas = (sf[-1] + n - 1) // n * peers                    # nvl_gather_params' grid
+            cap = random.choice([296, 64, 14])
+            ctas = max(peers, cap // peers * peers if ctas > cap else ctas)
+            got = walk(nseg, sf, n, r, ctas)
+            assert r not in got
+            for q in range(n):
+                if q != r:
+                    want = [c for s in range(nseg)
+                            for c in range(sf[s] + (sf[s + 1] - sf[s]) * q // n, sf[s] + (sf[s + 1] - sf[s]) * (q + 1) // n)]
+                    assert sorted(got.get(q, [])) == want
