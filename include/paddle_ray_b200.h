@@ -139,6 +139,14 @@ int32_t prb_adam_dense_param_sparse_grad(
     int32_t use_global_beta_pow, PRB_Tensor* param_out, PRB_Tensor* moment1_out, PRB_Tensor* moment2_out,
     PRB_Tensor* beta1_pow_out, PRB_Tensor* beta2_pow_out, PRB_Tensor* master_param_out /* optional */, void* stream);
 
+/* merge_selected_rows  ref: legacy_ops.yaml:1082-1088, paddle/phi/kernels/selected_rows/merge_selected_rows_kernel.h,
+ *   scatter::MergeAdd (selected_rows_functor.cu:340-420): unique rows in ascending order (written to the HOST array
+ *   out_rows, capacity x->nrows; their number to *out_nrows), the value rows of duplicates added in input order in
+ *   fp32 and rounded once (written to out_value, a device tensor with room for x->nrows x width elements).
+ *   ClipGradByGlobalNorm takes the norm of a sparse gradient from this (clip.py:655-664). */
+int32_t prb_merge_selected_rows(const PRB_SelectedRows* x, int64_t* out_rows, int64_t* out_nrows, PRB_Tensor* out_value,
+                                void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * AMP + global-norm clip
  * ---------------------------------------------------------------------------------------- */
@@ -188,6 +196,10 @@ int32_t prb_squared_l2_norm_noalloc(const PRB_Tensor* x, PRB_Tensor* out, void* 
 int32_t prb_clip_grad_by_global_norm(PRB_Tensor* grads, int64_t num, float clip_norm, int32_t auto_skip_clip,
                                      int32_t use_mp_type, PRB_Tensor* global_norm_out /* optional */,
                                      PRB_Tensor* clip_out /* optional */, void* stream);
+/* The multiply of _dygraph_clip alone (ref clip.py:715-727: paddle.multiply(g, clip_var.astype(g.dtype))), in place on a
+ * list: x = T(MT(x) * MT(T(*clip))); a no-op when *clip == 1.  Used for the VALUES of sparse (SelectedRows) gradients,
+ * whose norm is taken from their merged rows (prb_merge_selected_rows) but which are scaled as they are. */
+int32_t prb_multiply_by_clip(PRB_Tensor* xs, int64_t num, const PRB_Tensor* clip, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Bucket operators

@@ -76,6 +76,26 @@ def adam_(param, grad, learning_rate, moment1, moment2, beta1_pow, beta2_pow, ma
     return param, moment1, moment2, beta1_pow, beta2_pow, master_param
 
 
+def merge_selected_rows(x, stream=None):
+    """-> a new SelectedRows: unique rows ascending, duplicates' value rows added (legacy_ops.yaml:1082-1088)."""
+    import numpy as np
+    sr, keep = x.c_struct()
+    rows = np.zeros(max(x.rows.size, 1), np.int64)
+    n = C.c_int64()
+    value = Tensor(max(x.value.numel, 1), x.value.dtype, x.value.device)
+    v = value.prb
+    call("prb_merge_selected_rows", C.byref(sr), rows.ctypes.data, C.byref(n), C.byref(v), _stream(stream))
+    width = x.width
+    return core.SelectedRows(rows[:n.value].copy(), x.height, value.view(0, n.value * width))
+
+
+def multiply_by_clip_(xs, clip, stream=None):
+    """In place on the list: x = T(MT(x) * MT(T(clip)))  (the multiply of ClipGradByGlobalNorm, clip.py:715-727)."""
+    c = clip.prb
+    call("prb_multiply_by_clip", tensor_array(xs), len(xs), C.byref(c), _stream(stream))
+    return xs
+
+
 def merged_adam_(param, grad, learning_rate, moment1, moment2, beta1_pow, beta2_pow, master_param, beta1, beta2,
                  epsilon, multi_precision=False, use_global_beta_pow=False, stream=None):
     n = len(param)

@@ -71,6 +71,8 @@ SIGNATURES = {
     "prb_fused_adam": [_T] * 8 + [_i64, _T] + [_f64] * 3 + [_i32, _f32, _i32, _i32, _i32] + [_T] * 6 + [_vp],
     "prb_adam_dense_param_sparse_grad": [_T, C.POINTER(SelectedRowsC)] + [_T] * 7 + [_f64] * 3 + [_i32, _i64, _i32, _i32] +
                                         [_T] * 6 + [_vp],
+    "prb_multiply_by_clip": [_T, _i64, _T, _vp],
+    "prb_merge_selected_rows": [C.POINTER(SelectedRowsC), _vp, _vp, _T, _vp],
     "prb_check_finite_and_unscale": [_T, _i64, _T, _T, _T, _vp],
     "prb_update_loss_scaling": [_T, _i64, _T, _T, _T, _T, _i32, _i32, _f32, _f32, _i32, _T, _T, _T, _T, _vp],
     "prb_squared_l2_norm": [_T, _T, _vp],

@@ -490,6 +490,26 @@ int32_t prb_clip_grad_by_global_norm(PRB_Tensor* grads, int64_t num, float clip_
   return PRB_SUCCESS;
 }
 
+int32_t prb_multiply_by_clip(PRB_Tensor* xs, int64_t num, const PRB_Tensor* clip, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  PRB_TRY(require_device());
+  PRB_ENFORCE(num >= 0 && (xs || num == 0) && clip, PRB_INVALID_ARGUMENT, "multiply_by_clip: NULL argument");
+  PRB_ENFORCE(clip->numel == 1 && clip->dtype == PRB_FLOAT32 && clip->device >= 0, PRB_INVALID_ARGUMENT,
+              "multiply_by_clip: the factor must be one float32 on the device");
+  const int32_t classes[3] = {PRB_FLOAT16, PRB_BFLOAT16, PRB_FLOAT32};
+  for (int64_t i = 0; i < num; ++i) {
+    PRB_ENFORCE(xs[i].dtype == PRB_FLOAT32 || xs[i].dtype == PRB_BFLOAT16 || xs[i].dtype == PRB_FLOAT16, PRB_UNIMPLEMENTED,
+                "multiply_by_clip: dtype %s is not built", dtype_name(xs[i].dtype));
+    PRB_ENFORCE(xs[i].device >= 0 || xs[i].numel == 0, PRB_INVALID_ARGUMENT, "multiply_by_clip: device tensors required");
+  }
+  for (int c = 0; c < 3; ++c) {
+    DeviceTable tab;
+    PRB_TRY(grad_table(xs, nullptr, num, classes[c], stream, &tab));
+    if (tab.ndescs) PRB_TRY(launch_clip_mul(classes[c], tab, reinterpret_cast<const float*>(clip->data), stream));
+  }
+  return PRB_SUCCESS;
+}
+
 int32_t prb_update_loss_scaling(const PRB_Tensor* xs, int64_t num, const PRB_Tensor* found_infinite,
                                 const PRB_Tensor* prev_loss_scaling, const PRB_Tensor* in_good_steps,
                                 const PRB_Tensor* in_bad_steps, int32_t incr_every_n_steps,

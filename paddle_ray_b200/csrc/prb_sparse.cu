@@ -169,6 +169,83 @@ int32_t run_sparse(const SparseArgs& a, const T* values, const int64_t* off, con
   return run_sparse_v<T, 1>(a, values, off, src, merged, need_merge, has_master, stream);
 }
 
+// Host side shared by the sparse adam and merge_selected_rows: stable sort + dedup of the row indices.
+// Stable (duplicates keep their input order): an LSD radix sort, 11 bits per pass over the bits the table's height
+// needs -- 8192 indices into a 30522-row table: 64 us, where std::stable_sort through the index indirection took
+// 556 us (and the reference's std::set insertion, more).
+struct RowPlan {
+  std::vector<int64_t> order;  // input positions, sorted by row (stable)
+  std::vector<int64_t> urows;  // unique rows, ascending
+  std::vector<int64_t> off;    // segment k of `order` = positions [off[k], off[k + 1]) of unique row k
+  bool need_merge = false;     // false: the rows were already strictly ascending (ref is_strict_sorted)
+};
+
+int32_t plan_rows(const PRB_SelectedRows* x, const char* op, RowPlan* out) {
+  const int64_t n = x->nrows;
+  for (int64_t k = 0; k < n; ++k)
+    PRB_ENFORCE(x->rows[k] >= 0 && x->rows[k] < x->height, PRB_OUT_OF_RANGE, "%s: row %lld is outside [0, %lld)", op,
+                (long long)x->rows[k], (long long)x->height);
+  std::vector<int64_t>& order = out->order;
+  std::vector<int64_t> other((size_t)n);
+  order.resize((size_t)n);
+  std::iota(order.begin(), order.end(), (int64_t)0);
+  int bits = 0;
+  while (((int64_t)1 << bits) < x->height) ++bits;
+  for (int sh = 0; sh < bits && n > 1; sh += 11) {
+    uint32_t cnt[2049];
+    memset(cnt, 0, sizeof(cnt));
+    for (int64_t k = 0; k < n; ++k) cnt[((x->rows[order[(size_t)k]] >> sh) & 2047) + 1]++;
+    for (int d = 0; d < 2048; ++d) cnt[d + 1] += cnt[d];
+    for (int64_t k = 0; k < n; ++k) other[cnt[(x->rows[order[(size_t)k]] >> sh) & 2047]++] = order[(size_t)k];
+    order.swap(other);
+  }
+  for (int64_t k = 0; k < n; ++k) {
+    const int64_t r = x->rows[order[(size_t)k]];
+    if (out->urows.empty() || out->urows.back() != r) {
+      out->urows.push_back(r);
+      out->off.push_back(k);
+    }
+  }
+  out->off.push_back(n);
+  out->need_merge = (int64_t)out->urows.size() != n;
+  for (int64_t k = 0; k < n && !out->need_merge; ++k) out->need_merge = order[(size_t)k] != k;
+  return PRB_SUCCESS;
+}
+
+// [urows | off | src] -> the stream's workspace (one pageable H2D copy, staged before the call returns), followed by
+// room for `extra` bytes at a 256-byte boundary.
+int32_t upload_plan(const RowPlan& rp, size_t extra, cudaStream_t stream, const int64_t** d_urows, const int64_t** d_off,
+                    const int64_t** d_src, void** d_extra) {
+  const size_t nu = rp.urows.size(), n = rp.order.size();
+  const size_t ints = nu + nu + 1 + n;
+  const size_t extra_off = (ints * sizeof(int64_t) + 255) / 256 * 256;
+  void* ws = nullptr;
+  PRB_TRY(workspace(extra_off + extra + 256, &ws, /*slot=*/3, stream));
+  std::vector<int64_t> host(ints);
+  std::copy(rp.urows.begin(), rp.urows.end(), host.begin());
+  std::copy(rp.off.begin(), rp.off.end(), host.begin() + (long)nu);
+  std::copy(rp.order.begin(), rp.order.end(), host.begin() + (long)(nu + nu + 1));
+  if (ints > 0) PRB_CUDA(cudaMemcpyAsync(ws, host.data(), ints * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+  *d_urows = reinterpret_cast<const int64_t*>(ws);
+  *d_off = *d_urows + nu;
+  *d_src = *d_off + nu + 1;
+  *d_extra = reinterpret_cast<char*>(ws) + extra_off;
+  return PRB_SUCCESS;
+}
+
+template <typename T>
+int32_t run_merge(const T* values, const int64_t* off, const int64_t* src, int64_t nunique, int64_t width, T* merged,
+                  cudaStream_t stream) {
+  if (nunique == 0 || width == 0) return PRB_SUCCESS;
+  const int64_t cap = (int64_t)sm_count() * 8, wpc = kSpThreads / 32;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nunique + wpc - 1) / wpc, cap));
+  const bool vec = width % 4 == 0 && ((uintptr_t)values % (sizeof(T) * 4)) == 0 && ((uintptr_t)merged % (sizeof(T) * 4)) == 0;
+  if (vec) merge_rows_kernel<T, 4><<<grid, kSpThreads, 0, stream>>>(values, off, src, nunique, width, merged);
+  else merge_rows_kernel<T, 1><<<grid, kSpThreads, 0, stream>>>(values, off, src, nunique, width, merged);
+  PRB_LAUNCH_CHECK();
+  return PRB_SUCCESS;
+}
+
 }  // namespace
 }  // namespace prb
 
@@ -233,53 +310,14 @@ extern "C" int32_t prb_adam_dense_param_sparse_grad(
       skip = reinterpret_cast<const bool*>(skip_update->data);
     }
   }
-  // ---- host: sort + deduplicate the row indices.  Stable (duplicates keep their input order): an LSD radix sort, 11
-  // bits per pass over the bits the table's height needs -- 8192 indices into a 30522-row table: 64 us, where
-  // std::stable_sort through the index indirection took 556 us (and the reference's std::set insertion, more).
-  const int64_t n = grad->nrows;
-  for (int64_t k = 0; k < n; ++k)
-    PRB_ENFORCE(grad->rows[k] >= 0 && grad->rows[k] < grad->height, PRB_OUT_OF_RANGE,
-                "adam (sparse grad): row %lld is outside [0, %lld)", (long long)grad->rows[k], (long long)grad->height);
-  std::vector<int64_t> order((size_t)n), other((size_t)n);
-  std::iota(order.begin(), order.end(), (int64_t)0);
-  int bits = 0;
-  while (((int64_t)1 << bits) < grad->height) ++bits;
-  for (int sh = 0; sh < bits && n > 1; sh += 11) {
-    uint32_t cnt[2049];
-    memset(cnt, 0, sizeof(cnt));
-    for (int64_t k = 0; k < n; ++k) cnt[((grad->rows[order[(size_t)k]] >> sh) & 2047) + 1]++;
-    for (int d = 0; d < 2048; ++d) cnt[d + 1] += cnt[d];
-    for (int64_t k = 0; k < n; ++k) other[cnt[(grad->rows[order[(size_t)k]] >> sh) & 2047]++] = order[(size_t)k];
-    order.swap(other);
-  }
-  std::vector<int64_t> urows, off;
-  for (int64_t k = 0; k < n; ++k) {
-    const int64_t r = grad->rows[order[(size_t)k]];
-    if (urows.empty() || urows.back() != r) {
-      urows.push_back(r);
-      off.push_back(k);
-    }
-  }
-  off.push_back(n);
-  const int64_t nu = (int64_t)urows.size();
-  bool need_merge = nu != n;
-  for (int64_t k = 0; k < n && !need_merge; ++k) need_merge = order[(size_t)k] != k;  // sorted and unique: use the values as they are
-  // ---- device scratch: [urows | off | src | merged values]
-  const size_t ints = (size_t)nu + (size_t)nu + 1 + (size_t)n;
-  const size_t es = (size_t)dtype_size(dt);
-  const size_t merged_off = (ints * sizeof(int64_t) + 255) / 256 * 256;
-  void* ws = nullptr;
-  PRB_TRY(workspace(merged_off + (size_t)nu * (size_t)width * es + 256, &ws, /*slot=*/3, stream));
-  std::vector<int64_t> host(ints);
-  std::copy(urows.begin(), urows.end(), host.begin());
-  std::copy(off.begin(), off.end(), host.begin() + nu);
-  std::copy(order.begin(), order.end(), host.begin() + nu + nu + 1);
-  if (ints > 0)  // pageable source: staged before the call returns
-    PRB_CUDA(cudaMemcpyAsync(ws, host.data(), ints * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
-  const int64_t* d_urows = reinterpret_cast<const int64_t*>(ws);
-  const int64_t* d_off = d_urows + nu;
-  const int64_t* d_src = d_off + nu + 1;
-  void* d_merged = reinterpret_cast<char*>(ws) + merged_off;
+  // ---- host: sort + deduplicate the row indices; device scratch: [urows | off | src | merged values]
+  RowPlan rp;
+  PRB_TRY(plan_rows(grad, "adam (sparse grad)", &rp));
+  const int64_t nu = (int64_t)rp.urows.size();
+  const bool need_merge = rp.need_merge;
+  const int64_t *d_urows, *d_off, *d_src;
+  void* d_merged;
+  PRB_TRY(upload_plan(rp, (size_t)nu * (size_t)width * (size_t)dtype_size(dt), stream, &d_urows, &d_off, &d_src, &d_merged));
   SparseArgs a{};
   a.param = param->data;
   a.mom1 = reinterpret_cast<float*>(moment1->data);
@@ -323,4 +361,49 @@ extern "C" int32_t prb_adam_dense_param_sparse_grad(
     PRB_TRY(beta_pow_update_device(beta1_pow, beta2_pow, beta1_pow_out, beta2_pow_out, 1, (float)beta1, (float)beta2, skip, stream));
   }
   return PRB_SUCCESS;
+}
+
+// ref: merge_selected_rows (legacy_ops.yaml:1082-1088, MergeSelectedRowsKernel -> scatter::MergeAdd): unique rows in
+// ascending order, the value rows of duplicates added.
+extern "C" int32_t prb_merge_selected_rows(const PRB_SelectedRows* x, int64_t* out_rows, int64_t* out_nrows,
+                                           PRB_Tensor* out_value, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  PRB_TRY(require_device());
+  PRB_ENFORCE(x && out_nrows && out_value && (out_rows || x->nrows == 0), PRB_INVALID_ARGUMENT,
+              "merge_selected_rows: a required argument is NULL");
+  const int32_t dt = x->value.dtype;
+  PRB_ENFORCE(dt == PRB_FLOAT32 || dt == PRB_BFLOAT16 || dt == PRB_FLOAT16, PRB_UNIMPLEMENTED,
+              "merge_selected_rows: dtype %s is not built", dtype_name(dt));
+  PRB_ENFORCE(x->nrows >= 0 && x->height > 0 && (x->rows != nullptr || x->nrows == 0) && x->value.device >= 0,
+              PRB_INVALID_ARGUMENT, "merge_selected_rows: bad input");
+  if (x->nrows == 0) {
+    *out_nrows = 0;
+    return PRB_SUCCESS;
+  }
+  PRB_ENFORCE(x->value.numel % x->nrows == 0, PRB_INVALID_ARGUMENT, "merge_selected_rows: value must hold nrows x width elements");
+  const int64_t width = x->value.numel / x->nrows;
+  RowPlan rp;
+  PRB_TRY(plan_rows(x, "merge_selected_rows", &rp));
+  const int64_t nu = (int64_t)rp.urows.size();
+  PRB_ENFORCE(out_value->dtype == dt && out_value->device >= 0 && out_value->numel >= nu * width, PRB_INVALID_ARGUMENT,
+              "merge_selected_rows: out_value must be a device tensor of the input's dtype with room for %lld x %lld elements",
+              (long long)nu, (long long)width);
+  std::copy(rp.urows.begin(), rp.urows.end(), out_rows);
+  *out_nrows = nu;
+  if (!rp.need_merge) {  // already strictly ascending: the values are the result
+    if (out_value->data != x->value.data)
+      PRB_CUDA(cudaMemcpyAsync(out_value->data, x->value.data, (size_t)nu * width * dtype_size(dt), cudaMemcpyDeviceToDevice, stream));
+    return PRB_SUCCESS;
+  }
+  PRB_ENFORCE(out_value->data != x->value.data, PRB_INVALID_ARGUMENT, "merge_selected_rows: cannot merge in place");
+  const int64_t *d_urows, *d_off, *d_src;
+  void* unused;
+  PRB_TRY(upload_plan(rp, 0, stream, &d_urows, &d_off, &d_src, &unused));
+  switch (dt) {
+    case PRB_FLOAT32: return run_merge<float>((const float*)x->value.data, d_off, d_src, nu, width, (float*)out_value->data, stream);
+    case PRB_BFLOAT16:
+      return run_merge<__nv_bfloat16>((const __nv_bfloat16*)x->value.data, d_off, d_src, nu, width,
+                                      (__nv_bfloat16*)out_value->data, stream);
+    default: return run_merge<__half>((const __half*)x->value.data, d_off, d_src, nu, width, (__half*)out_value->data, stream);
+  }
 }

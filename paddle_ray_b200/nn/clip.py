@@ -3,7 +3,7 @@ from __future__ import annotations
 
 from .. import _C_ops
 from .._lib import FLOAT32
-from ..core import Tensor
+from ..core import SelectedRows, Tensor
 
 _clip_by_global_norm_using_mp_type_flag = False
 
@@ -54,13 +54,27 @@ class ClipGradByGlobalNorm(ClipGradBase):
         todo = [(p, g) for p, g in params_grads if g is not None and getattr(p, "need_clip", True) is not False]
         if not todo:
             return params_grads  # "all parameters have been filtered out" (ref :676-682)
-        new_grads = {}
+        new_grads, work, sparse_values = {}, [], []
         for p, g in todo:
-            ng = Tensor(g.numel, g.dtype, g.device)
-            ng.copy_(g)
-            new_grads[id(p)] = ng
+            if isinstance(g, SelectedRows):
+                # the norm of a sparse gradient is taken from its MERGED rows (ref :655-662); the gradient itself is
+                # scaled as it is, duplicates and all (paddle.multiply(g, clip_input), :715-727)
+                work.append(_C_ops.merge_selected_rows(g).value)
+                nv = Tensor(max(g.value.numel, 1), g.value.dtype, g.value.device).view(0, g.value.numel)
+                if g.value.numel:
+                    nv.copy_(g.value)
+                sparse_values.append(nv)
+                new_grads[id(p)] = SelectedRows(g.rows.copy(), g.height, nv)
+            else:
+                ng = Tensor(g.numel, g.dtype, g.device)
+                ng.copy_(g)
+                new_grads[id(p)] = ng
+                work.append(ng)
         self._ensure_outputs()
-        _C_ops.clip_grad_by_global_norm_(list(new_grads.values()), self.clip_norm, self.auto_skip_clip,
+        _C_ops.clip_grad_by_global_norm_(work, self.clip_norm, self.auto_skip_clip,
                                          _clip_by_global_norm_using_mp_type(), norm=self.last_global_norm,
                                          clip=self.last_clip)
+        sparse_values = [v for v in sparse_values if v.numel]
+        if sparse_values:
+            _C_ops.multiply_by_clip_(sparse_values, self.last_clip)
         return [(p, new_grads.get(id(p), g)) for p, g in params_grads]

@@ -178,9 +178,20 @@ class Optimizer:
                                    "reduced gradient of its own arena ranges only; step through "
                                    "GroupShardedOptimizerStage2")
         if any(isinstance(g, SelectedRows) for _, g in pg):
+            if loss_scale is not None:
+                # the reference cannot either: check_finite_and_unscale_ has no SelectedRows kernel (legacy_ops.yaml:292-302)
+                raise _lib.PRBError(4, "AMP unscaling of SelectedRows gradients is not supported")
+            if clip is not None:
+                # the global norm spans dense and sparse gradients: the reference-shaped clip (new gradient objects,
+                # sparse norms from merged rows, clip.py:643-736), then one operator call per parameter
+                pg = clip(pg)
             dense = [(p, g) for p, g in pg if not isinstance(g, SelectedRows)]
-            self._sparse_step([(p, g) for p, g in pg if isinstance(g, SelectedRows)], found_inf, loss_scale,
+            self._sparse_step([(p, g) for p, g in pg if isinstance(g, SelectedRows)], found_inf,
                               advance_beta_pow=not dense)
+            if clip is not None:
+                if dense:
+                    self._per_tensor_step(dense, found_inf, None, clipped=True)
+                return
             pg = dense
             if not pg:
                 return
@@ -330,7 +341,7 @@ class Optimizer:
                 ref("ls"), ref("fi"), ref("gn"), ref("cl"))
         return args + (keep,)  # the trailing dict only keeps the ctypes objects alive
 
-    def _per_tensor_step(self, pg, found_inf, loss_scale):
+    def _per_tensor_step(self, pg, found_inf, loss_scale, clipped=False):
         """Reference-shaped loop: one adam(w)_ call per parameter (ref adamw.py:445-465)."""
         if loss_scale is not None:
             by_dtype = {}
@@ -341,7 +352,7 @@ class Optimizer:
             for grads in by_dtype.values():  # one call per dtype list, flags OR-ed (ref grad_scaler.py:367-396)
                 _C_ops.check_finite_and_unscale_(grads, loss_scale, tmp)
                 _or_into(found_inf, tmp)
-        if self._grad_clip is not None:
+        if self._grad_clip is not None and not clipped:
             pg = self._grad_clip(pg)
         lr = self._global_lr()
         lr_ratio, with_decay = self._tensor_attrs(pg)
@@ -352,15 +363,12 @@ class Optimizer:
             self._append_optimize_op(p, g, lr, acc[self._moment1_acc_str], acc[self._moment2_acc_str], master, found_inf,
                                      float(lr_ratio[i]), bool(with_decay[i]), use_global_beta_pow=i != len(pg) - 1)
 
-    def _sparse_step(self, pg, found_inf, loss_scale, advance_beta_pow):
+    def _sparse_step(self, pg, found_inf, advance_beta_pow):
         """Parameters whose gradient is a SelectedRows (embedding tables): one adam_ call each, which the YAML
         dispatches to adam_dense_param_sparse_grad (legacy_ops.yaml:52; ref adam.py:390-470).  They run BEFORE the
         dense parameters' fused launch, which is the one that advances the shared beta-pow accumulators."""
         if self._use_adamw:
             raise _lib.PRBError(4, "adamw_ has no SelectedRows kernel (legacy_ops.yaml:68-77); use Adam for sparse gradients")
-        if loss_scale is not None or self._grad_clip is not None:
-            raise _lib.PRBError(4, "AMP unscaling and global-norm clipping of SelectedRows gradients are not built "
-                                "(merge_selected_rows / multiply_sr, clip.py) -- dense gradients only")
         lr = self._global_lr()
         for i, (p, g) in enumerate(pg):
             acc = self._accumulators[p.name]

@@ -186,3 +186,91 @@ def test_adam_optimizer_with_an_embedding_table_and_dense_parameters(prb):
     emb.grad = prb.SelectedRows([1], height, T.from_numpy(np.ones(width, np.float32)))
     with pytest.raises(prb._lib.PRBError):
         prb.optimizer.AdamW(learning_rate=1e-3, parameters=[emb]).step()
+
+
+@pytest.mark.parametrize("dtype", [orc.F32, orc.BF16, orc.F16])
+def test_merge_selected_rows_and_multiply_by_clip(prb, dtype):
+    """merge_selected_rows (legacy_ops.yaml:1082-1088) against the oracle's MergeAdd, and the clip's multiply
+    (clip.py:715-727: the factor is first cast to the gradient's dtype) against the oracle's clip_mul."""
+    T = prb.Tensor
+    rng = np.random.default_rng(41)
+    for height, width, nrows in ((100, 8, 37), (30522, 768, 500), (9, 5, 30), (50, 16, 0)):
+        rows = rng.integers(0, height, nrows)
+        vals = orc.from_f32(rng.normal(0, 1e-2, nrows * width).astype(np.float32), dtype).reshape(nrows, width)
+        sr = prb.SelectedRows(rows, height, T.from_numpy(vals.reshape(-1), dtype) if nrows else T(0, dtype))
+        m = prb._C_ops.merge_selected_rows(sr)
+        ur, mv = orc.merge_rows(rows, vals, dtype, width)
+        np.testing.assert_array_equal(m.rows, ur)
+        assert m.height == height and m.value.numel == ur.size * width
+        if ur.size:
+            bits_equal(m.value.numpy().reshape(ur.size, width), mv)
+    # already strictly ascending: the values come back unchanged
+    vals = orc.from_f32(rng.normal(0, 1, 3 * 4).astype(np.float32), dtype)
+    m = prb._C_ops.merge_selected_rows(prb.SelectedRows([1, 5, 7], 10, T.from_numpy(vals, dtype)))
+    assert m.rows.tolist() == [1, 5, 7]
+    bits_equal(m.value.numpy(), vals)
+    # x = T(MT(x) * MT(T(clip)))
+    x0 = orc.from_f32(rng.normal(0, 1, 10007).astype(np.float32), dtype)
+    for c in (0.123456789, 1.0, 0.75):
+        x = T.from_numpy(x0.copy(), dtype)
+        prb._C_ops.multiply_by_clip_([x], T.from_numpy(np.array([c], np.float32)))
+        want = x0.copy()
+        orc.clip_mul(want, dtype, float(np.float32(c)))
+        bits_equal(x.numpy(), want)
+
+
+def test_global_norm_clip_spans_dense_and_sparse_gradients(prb):
+    """ClipGradByGlobalNorm with a SelectedRows gradient (clip.py:643-736): the sparse gradient enters the global norm
+    through its MERGED rows and is scaled as it is; Adam then consumes the clipped gradients.  Three steps against the
+    oracle's composition (the clip factor within the tolerance of an unpinned summation order, everything after it
+    bit for bit with that factor)."""
+    T = prb.Tensor
+    rng = np.random.default_rng(29)
+    height, width = 200, 16
+    sizes = [3000, 8193]
+    emb0 = rng.normal(0, 0.02, (height, width)).astype(np.float32)
+    dense0 = [rng.normal(0, 0.02, n).astype(np.float32) for n in sizes]
+    emb = T.from_numpy(emb0.reshape(-1), name="emb")
+    emb.is_sparse_grad = True
+    dense = [T.from_numpy(a, name="w_%d" % i) for i, a in enumerate(dense0)]
+    params = [emb] + dense
+    clip = prb.nn.ClipGradByGlobalNorm(0.05)
+    opt = prb.optimizer.Adam(learning_rate=1e-3, parameters=params, grad_clip=clip, lazy_mode=False)
+    eo, m1e, m2e = emb0.copy(), np.zeros_like(emb0), np.zeros_like(emb0)
+    do = [a.copy() for a in dense0]
+    m1d, m2d = [np.zeros_like(a) for a in dense0], [np.zeros_like(a) for a in dense0]
+    b1p, b2p = np.float32(0.9), np.float32(0.999)
+    for step in range(3):
+        rows = rng.integers(0, height, 50)                       # with duplicates: merged norm != raw norm
+        vals = rng.normal(0, 1e-2, (rows.size, width)).astype(np.float32)
+        gd = [rng.normal(0, 1e-2, n).astype(np.float32) for n in sizes]
+        for p, g in zip(dense, gd):
+            p.grad = T.from_numpy(g)
+        emb.grad = prb.SelectedRows(rows, height, T.from_numpy(vals.reshape(-1)))
+        opt.step()
+        _, merged = orc.merge_rows(rows, vals, orc.F32, width)
+        work = [merged.reshape(-1).copy()] + [g.copy() for g in gd]
+        norm_or, c_or = orc.global_norm_clip(work, [orc.F32] * len(work), 0.05)
+        c = float(clip.last_clip.numpy()[0])
+        assert c < 1.0 and abs(c - c_or) <= 2e-6 * abs(c_or), (c, c_or)
+        np.testing.assert_allclose(clip.last_global_norm.numpy()[0], norm_or, rtol=2e-6)
+        raw_norm = np.sqrt(sum(float(np.sum(a.astype(np.float64) ** 2)) for a in [vals] + gd))
+        assert abs(raw_norm - norm_or) > 1e-4 * norm_or          # the unmerged rows would give another norm
+        vc = vals.copy().reshape(-1)
+        orc.clip_mul(vc, orc.F32, c)
+        kw = dict(lr=1e-3, beta1=0.9, beta2=0.999, epsilon=1e-8, beta1_pow=b1p, beta2_pow=b2p)
+        orc.sparse_adam(eo, rows, vc.reshape(rows.size, width), m1e, m2e, None, dtype_param=orc.F32, lazy_mode=False, **kw)
+        for i in range(len(sizes)):
+            g = gd[i].copy()
+            orc.clip_mul(g, orc.F32, c)
+            orc.adam(do[i], g, m1d[i], m2d[i], None, dtype_param=orc.F32, dtype_grad=orc.F32, **kw)
+        b1p, b2p = np.float32(0.9) * b1p, np.float32(0.999) * b2p
+        bits_equal(emb.numpy().reshape(height, width), eo)
+        for p, w in zip(dense, do):
+            bits_equal(p.numpy(), w)
+        assert opt._beta1_pow.numpy()[0] == b1p
+    # AMP on a sparse gradient: refused, as in the reference (no SelectedRows kernel for check_finite_and_unscale)
+    emb.grad = prb.SelectedRows([1], height, T.from_numpy(np.ones(width, np.float32)))
+    scaler = prb.amp.GradScaler()
+    with pytest.raises(prb._lib.PRBError):
+        scaler.step(opt)
