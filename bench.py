@@ -945,7 +945,10 @@ def run_gpu_arm(args):
         overlap = measure_overlap(prb, w, group, rank_max, device_barrier)
         # the same synthetic backward (2 x the exchanges' total) in front of the replicated and the sharded steps
         t_bwd_tail_us = overlap["cases"][1]["t_bwd_ms"] * 1e3
-        overlap["after_backward"] = measure_exposed_tail(prb, group, w, t_bwd_tail_us, rank_max, device_barrier)
+        try:
+            overlap["after_backward"] = measure_exposed_tail(prb, group, w, t_bwd_tail_us, rank_max, device_barrier)
+        except Exception as e:  # noqa: BLE001  (an extra: never lose the line over it)
+            overlap["after_backward"] = {"error": "%s: %s" % (type(e).__name__, str(e)[:160])}
 
     # CPU baseline (rank 0, N = 1 only): bounded sample of the same workload on the host cores
     cpu_baseline = None
