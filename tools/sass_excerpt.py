@@ -17,6 +17,9 @@ want = {
     "norm_finalize_kernel": "norm_finalize_kernel",
     "nvl_exchange_chunks_kernel<bf16, 8 ranks, no fold, norm>": "nvl_exchange_chunks_kernelI13__nv_bfloat16Li8ELb0ELb1ELb0E",
     "nvl_exchange_kernel<float, 8 ranks, no fold>": "nvl_exchange_kernelIfLi8ELb0E",
+    "nvl_gather_chunks_kernel<bf16> (sharded step: parameter gather)": "nvl_gather_chunks_kernelI13__nv_bfloat16E",
+    "sparse_adam_kernel<float, no master, 4 columns per lane>": "sparse_adam_kernelIfLb0ELi4E",
+    "merge_rows_kernel<float, 4>": "merge_rows_kernelIfLi4E",
 }
 out = ["# SASS excerpt (round 2): cuobjdump -sass paddle_ray_b200/libpaddle_ray_b200.so, sm_100a cubins only",
        "# (tools/sass_excerpt.py).  Per kernel: static counts of the instructions that carry the design.",
