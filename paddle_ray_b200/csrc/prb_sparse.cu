@@ -14,6 +14,8 @@
 //   otherwise      every row of the parameter, with g = 0 where the row is absent (one binary search per row in
 //                  the sorted unique rows; the reference searches per element).
 #include <algorithm>
+#include <map>
+#include <mutex>
 #include <cstring>
 #include <numeric>
 #include <vector>
@@ -212,7 +214,43 @@ int32_t plan_rows(const PRB_SelectedRows* x, const char* op, RowPlan* out) {
   return PRB_SUCCESS;
 }
 
-// [urows | off | src] -> the stream's workspace (one pageable H2D copy, staged before the call returns), followed by
+// Page-locked staging for the index tables: a copy from pageable memory would first wait for the whole stream
+// (CUDA synchronises the stream before it stages a pageable source), which stalls the host behind everything a
+// training step has queued.  Four slots per (device, stream), each guarded by an event recorded after its copy, so the
+// host may run four sparse updates ahead of the device.
+struct StageSlot {
+  void* host = nullptr;
+  size_t bytes = 0;
+  cudaEvent_t copied = nullptr;
+};
+struct StageRing {
+  StageSlot slot[4];
+  unsigned next = 0;
+};
+std::mutex g_stage_mu;
+std::map<std::pair<int, void*>, StageRing> g_stage;
+
+int32_t stage_acquire(size_t bytes, cudaStream_t stream, StageSlot** out) {
+  int dev = 0;
+  PRB_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_stage_mu);
+  StageRing& ring = g_stage[std::make_pair(dev, (void*)stream)];
+  StageSlot& st = ring.slot[ring.next++ & 3u];
+  if (st.copied == nullptr) PRB_CUDA(cudaEventCreateWithFlags(&st.copied, cudaEventDisableTiming));
+  else PRB_CUDA(cudaEventSynchronize(st.copied));  // the copy that last used this slot has been performed
+  if (st.bytes < bytes) {
+    if (st.host != nullptr) PRB_CUDA(cudaFreeHost(st.host));
+    st.host = nullptr;
+    st.bytes = 0;
+    const size_t want = bytes < 65536 ? 65536 : bytes + bytes / 2;
+    PRB_CUDA(cudaHostAlloc(&st.host, want, cudaHostAllocDefault));
+    st.bytes = want;
+  }
+  *out = &st;
+  return PRB_SUCCESS;
+}
+
+// [urows | off | src] -> the stream's workspace (one asynchronous H2D copy out of page-locked staging), followed by
 // room for `extra` bytes at a 256-byte boundary.
 int32_t upload_plan(const RowPlan& rp, size_t extra, cudaStream_t stream, const int64_t** d_urows, const int64_t** d_off,
                     const int64_t** d_src, void** d_extra) {
@@ -221,11 +259,14 @@ int32_t upload_plan(const RowPlan& rp, size_t extra, cudaStream_t stream, const 
   const size_t extra_off = (ints * sizeof(int64_t) + 255) / 256 * 256;
   void* ws = nullptr;
   PRB_TRY(workspace(extra_off + extra + 256, &ws, /*slot=*/3, stream));
-  std::vector<int64_t> host(ints);
-  std::copy(rp.urows.begin(), rp.urows.end(), host.begin());
-  std::copy(rp.off.begin(), rp.off.end(), host.begin() + (long)nu);
-  std::copy(rp.order.begin(), rp.order.end(), host.begin() + (long)(nu + nu + 1));
-  if (ints > 0) PRB_CUDA(cudaMemcpyAsync(ws, host.data(), ints * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+  StageSlot* st = nullptr;
+  PRB_TRY(stage_acquire(ints * sizeof(int64_t), stream, &st));
+  int64_t* host = reinterpret_cast<int64_t*>(st->host);
+  std::copy(rp.urows.begin(), rp.urows.end(), host);
+  std::copy(rp.off.begin(), rp.off.end(), host + nu);
+  std::copy(rp.order.begin(), rp.order.end(), host + nu + nu + 1);
+  PRB_CUDA(cudaMemcpyAsync(ws, host, ints * sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+  PRB_CUDA(cudaEventRecord(st->copied, stream));
   *d_urows = reinterpret_cast<const int64_t*>(ws);
   *d_off = *d_urows + nu;
   *d_src = *d_off + nu + 1;
