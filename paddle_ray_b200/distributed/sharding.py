@@ -19,6 +19,8 @@ from __future__ import annotations
 
 from functools import reduce
 
+import numpy as np
+
 from .. import _C_ops, _lib, core
 from . import parallel as _parallel
 from .fleet_utils import build_groups
@@ -250,7 +252,7 @@ class GroupShardedOptimizerStage2:
     def _stage1_args(self, found_inf, loss_scale, partials):
         """Argument block of the check + norm + clip-factor call over ALL gradients."""
         from ..nn.clip import _clip_by_global_norm_using_mp_type
-        opt, clip = self._optim, self._optim._grad_clip
+        clip = self._optim._grad_clip
         cfg = _lib.TailConfig()
         cfg.stage = 1
         cfg.use_amp = int(loss_scale is not None)
@@ -302,8 +304,7 @@ class GroupShardedOptimizerStage2:
             cfg.stage, cfg.param_to_grad_slot, cfg.write_back_grads, cfg.zero_grads = 2, 1, 0, 0
             self._stage1, self._stage2 = s1, (plan_key, s2)
         if self._stage1 is not None:
-            call = _lib.call
-            call("prb_dp_step_tail", *self._stage1[:16], stream)
+            _lib.call("prb_dp_step_tail", *self._stage1[:16], stream)
         lr = opt._global_lr().prb
         a = self._stage2[1]
         _lib.call("prb_dp_step_tail", a[0], a[1], a[2], C.byref(lr), *a[4:16], stream)
@@ -314,7 +315,6 @@ class GroupShardedOptimizerStage2:
             self._first = False
             if needs_pass1:
                 chunk = _lib.lib.prb_grad_chunk_elems()
-                import numpy as np
                 base = np.zeros(len(self._all_params), np.int32)
                 at = 0
                 for i, p in enumerate(self._all_params):   # == dp._parameters order

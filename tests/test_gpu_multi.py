@@ -15,7 +15,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _wait_all(procs, timeout_s):
     """Wait for every rank; as soon as ONE rank fails the others (now stuck in a collective it left) are killed, so a
     failed assertion on one rank is reported at once instead of after the whole time limit."""
-    import tempfile
     import time
     t0 = time.time()
     while time.time() - t0 < timeout_s:
